@@ -1,0 +1,189 @@
+/*
+ * dibr_b200.h — C ABI of libdibr_b200.so: the B200 (sm_100a) implementation of Kaolin's DIB-R
+ * differentiable rasterization hot path.
+ *
+ * This is the drop-in boundary.  It replaces the four pybind functions the reference exposes as
+ * kaolin._C.render.mesh.* (kaolin/csrc/bindings.cpp:75-80, C++ signatures in
+ * kaolin/csrc/render/mesh/rasterization.h:23-41 and dibr_soft_mask.h:23-40) and, in the `_fused`
+ * entry points, also the torch glue the reference runs around them (kaolin/render/mesh/
+ * rasterization.py:299-363, dibr.py:31-39).
+ *
+ * Conventions
+ *   - extern "C", plain device pointers + sizes, no torch types.  All pointers are DEVICE pointers
+ *     on the CURRENT device unless stated otherwise; tensors are dense row-major ("contiguous").
+ *   - `stream` is a cudaStream_t (passed as void*); every call is asynchronous w.r.t. the host and
+ *     enqueues work only on that stream.  The library never synchronises, never allocates device
+ *     memory and keeps no mutable global state: it is re-entrant (forward runs on the Python
+ *     thread, backward on the autograd thread — SURVEY.md §8b).
+ *   - The caller allocates every output and the scratch workspace (`ws`, at least
+ *     dibr_workspace_bytes(...) bytes, 256-byte aligned).  Outputs need NOT be pre-initialised:
+ *     the kernels write every element (the reference's at::zeros/at::full fills,
+ *     rasterization.cpp:87-93, dibr_soft_mask.cpp:84-97, are fused away).  Gradient outputs are
+ *     zero-filled by the library itself (reference: at::zeros_like, rasterization.cpp:156-157).
+ *   - `_f32` / `_f64` twins mirror the reference's AT_DISPATCH_FLOATING_TYPES instantiations.
+ *   - Scalars keep the reference's C types: `float multiplier, eps, sigmainv` in the kernels
+ *     (rasterization.h:31-32).  The `_fused` entry points additionally take `multiplier` and
+ *     `boxlen` as double because there they stand for the PYTHON scalars of
+ *     `face_vertices_image * multiplier` and `boxlen * multiplier` (dibr.py:32,37-38).
+ *   - Return value: DIBR_OK (0) or an error code; dibr_error_string() gives the text.  No C++
+ *     exception crosses the boundary.  The Python shim raises RuntimeError on non-zero, which is the
+ *     reference's error behaviour (c10::Error -> RuntimeError).
+ *   - face_idx semantics are the reference's: int64, index of the face inside its mesh, -1 = none;
+ *     ties in depth go to the lowest face index (rasterization_cuda.cu:162-169).
+ */
+#ifndef DIBR_B200_H_
+#define DIBR_B200_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define DIBR_ABI_VERSION 1
+
+enum {
+  DIBR_OK = 0,
+  DIBR_ERR_INVALID_ARGUMENT = 1, /* null pointer, negative size, unsupported value */
+  DIBR_ERR_WORKSPACE = 2,        /* ws == NULL or ws_bytes too small */
+  DIBR_ERR_CUDA = 3,             /* a CUDA runtime call / kernel launch failed (dibr_last_cuda_error) */
+  DIBR_ERR_TOO_LARGE = 4         /* a dimension exceeds what the kernels index (H, W <= 32768; B*F < 2^31) */
+};
+
+int dibr_abi_version(void);
+const char* dibr_error_string(int code);
+/* text of the last CUDA error seen by the calling thread inside this library ("" if none) */
+const char* dibr_last_cuda_error(void);
+
+/* Scratch bytes needed by any entry point below for these sizes (a pure function of the sizes).
+ * `total_faces` = B*F for the batched layouts, N for the packed one. */
+size_t dibr_workspace_bytes(int batch_size, int64_t total_faces, int height, int width);
+
+/* ---------------------------------------------------------------------------------------------
+ * rasterize forward, fused layout.
+ * Replaces RasterizeCuda.forward end to end (rasterization.py:290-369): valid-face packing,
+ * x multiplier, bbox, packed_rasterize_forward_cuda, packed->original index mapping and the -1 fix-up.
+ *   z      (B,F,3)   img (B,F,3,2) NDC coords (NOT multiplied)   feat (B,F,3,C)
+ *   valid  (B,F) uint8/bool or NULL (= all faces valid)
+ *   out_feat (B,H,W,C)   out_face_idx (B,H,W) int64 ORIGINAL face index   out_weights (B,H,W,3) or NULL
+ */
+int dibr_rasterize_fwd_fused_f32(const float* z, const float* img, const float* feat, const uint8_t* valid,
+                                 int B, int F, int C, int H, int W, double multiplier, float eps,
+                                 float* out_feat, int64_t* out_face_idx, float* out_weights,
+                                 void* ws, size_t ws_bytes, void* stream);
+int dibr_rasterize_fwd_fused_f64(const double* z, const double* img, const double* feat, const uint8_t* valid,
+                                 int B, int F, int C, int H, int W, double multiplier, float eps,
+                                 double* out_feat, int64_t* out_face_idx, double* out_weights,
+                                 void* ws, size_t ws_bytes, void* stream);
+
+/* ---------------------------------------------------------------------------------------------
+ * packed_rasterize_forward_cuda — reference-shaped (rasterization.h:23-32, rasterization.cpp:49-104).
+ *   z (N,3)  img_mult (N,3,2) ALREADY multiplied  bboxes (N,4) [xmin,ymin,xmax,ymax]  feat (N,3,C)
+ *   first_idx (B+1) int64 ON DEVICE
+ *   out_selected_face_idx (B,H,W): index LOCAL to the mesh's packed range, -1 = none.
+ */
+int dibr_packed_rasterize_forward_f32(int H, int W, const float* z, const float* img_mult, const float* bboxes,
+                                      const float* feat, const int64_t* first_idx, int B, int64_t N, int C,
+                                      float multiplier, float eps, float* out_feat,
+                                      int64_t* out_selected_face_idx, float* out_weights,
+                                      void* ws, size_t ws_bytes, void* stream);
+int dibr_packed_rasterize_forward_f64(int H, int W, const double* z, const double* img_mult, const double* bboxes,
+                                      const double* feat, const int64_t* first_idx, int B, int64_t N, int C,
+                                      float multiplier, float eps, double* out_feat,
+                                      int64_t* out_selected_face_idx, double* out_weights,
+                                      void* ws, size_t ws_bytes, void* stream);
+
+/* ---------------------------------------------------------------------------------------------
+ * rasterize_backward_cuda (rasterization.h:34-41, rasterization.cpp:106-168, kernel
+ * rasterization_cuda.cu:238-402).  `interpolated_features` of the reference signature is unused
+ * there and is not part of this ABI.
+ *   grad_out (B,H,W,C)  face_idx (B,H,W) int64  img (B,F,3,2) NOT multiplied  feat (B,F,3,C)
+ *   weights (B,H,W,3), or NULL: the kernel then recomputes them bit-exactly from (pixel, face) with
+ *   the forward arithmetic, which needs `multiplier` (ignored when weights != NULL).
+ *   grad_img (B,F,3,2), grad_feat (B,F,3,C): zero-filled and accumulated by the library.
+ */
+int dibr_rasterize_backward_f32(const float* grad_out, const int64_t* face_idx, const float* weights,
+                                const float* img, const float* feat, int B, int F, int C, int H, int W,
+                                double multiplier, float eps, float* grad_img, float* grad_feat, void* stream);
+int dibr_rasterize_backward_f64(const double* grad_out, const int64_t* face_idx, const double* weights,
+                                const double* img, const double* feat, int B, int F, int C, int H, int W,
+                                double multiplier, float eps, double* grad_img, double* grad_feat, void* stream);
+
+/* ---------------------------------------------------------------------------------------------
+ * dibr_soft_mask forward.
+ *  _fused   : replaces DibrSoftMaskCuda.forward (dibr.py:29-55): x multiplier, enlarged bboxes, kernel.
+ *             img (B,F,3,2) NOT multiplied.
+ *  reference-shaped dibr_soft_mask_forward_cuda (dibr_soft_mask.h:23-29): img_mult ALREADY multiplied,
+ *             large_bboxes (B,F,4) given.
+ *  Outputs: soft (B,H,W); the k-list side buffers prob (B,H,W,K), close_idx (B,H,W,K) int64,
+ *  dist_type (B,H,W,K) uint8 are written only when all three are non-NULL (all NULL = skip them;
+ *  the backward then recomputes).
+ */
+int dibr_soft_mask_fwd_fused_f32(const float* img, const int64_t* face_idx, int B, int F, int H, int W,
+                                 float sigmainv, double boxlen, int knum, double multiplier, float* soft,
+                                 float* prob, int64_t* close_idx, uint8_t* dist_type,
+                                 void* ws, size_t ws_bytes, void* stream);
+int dibr_soft_mask_fwd_fused_f64(const double* img, const int64_t* face_idx, int B, int F, int H, int W,
+                                 float sigmainv, double boxlen, int knum, double multiplier, double* soft,
+                                 double* prob, int64_t* close_idx, uint8_t* dist_type,
+                                 void* ws, size_t ws_bytes, void* stream);
+int dibr_soft_mask_forward_f32(const float* img_mult, const float* large_bboxes, const int64_t* face_idx,
+                               int B, int F, int H, int W, float sigmainv, int knum, float multiplier,
+                               float* soft, float* prob, int64_t* close_idx, uint8_t* dist_type,
+                               void* ws, size_t ws_bytes, void* stream);
+int dibr_soft_mask_forward_f64(const double* img_mult, const double* large_bboxes, const int64_t* face_idx,
+                               int B, int F, int H, int W, float sigmainv, int knum, float multiplier,
+                               double* soft, double* prob, int64_t* close_idx, uint8_t* dist_type,
+                               void* ws, size_t ws_bytes, void* stream);
+
+/* ---------------------------------------------------------------------------------------------
+ * dibr_soft_mask backward.
+ *  reference-shaped dibr_soft_mask_backward_cuda (dibr_soft_mask.h:31-40; kernel
+ *  dibr_soft_mask_cuda.cu:230-353): consumes the k-list side buffers; img_mult ALREADY multiplied.
+ *  _fused (recompute): no side buffers; re-derives each uncovered pixel's first-knum faces, their
+ *  probabilities and distance types with the forward arithmetic.  img NOT multiplied.
+ *  grad_img (B,F,3,2) is zero-filled and accumulated by the library; it is the gradient w.r.t. the
+ *  UN-multiplied coordinates in both variants (the /multiplier is in-kernel, :299-302).
+ */
+int dibr_soft_mask_backward_f32(const float* grad_soft, const float* soft, const int64_t* face_idx,
+                                const float* prob, const int64_t* close_idx, const uint8_t* dist_type,
+                                const float* img_mult, int B, int F, int H, int W, int knum, float sigmainv,
+                                float multiplier, float* grad_img, void* stream);
+int dibr_soft_mask_backward_f64(const double* grad_soft, const double* soft, const int64_t* face_idx,
+                                const double* prob, const int64_t* close_idx, const uint8_t* dist_type,
+                                const double* img_mult, int B, int F, int H, int W, int knum, float sigmainv,
+                                float multiplier, double* grad_img, void* stream);
+int dibr_soft_mask_bwd_fused_f32(const float* grad_soft, const float* soft, const int64_t* face_idx,
+                                 const float* img, int B, int F, int H, int W, float sigmainv, double boxlen,
+                                 int knum, double multiplier, float* grad_img,
+                                 void* ws, size_t ws_bytes, void* stream);
+int dibr_soft_mask_bwd_fused_f64(const double* grad_soft, const double* soft, const int64_t* face_idx,
+                                 const double* img, int B, int F, int H, int W, float sigmainv, double boxlen,
+                                 int knum, double multiplier, double* grad_img,
+                                 void* ws, size_t ws_bytes, void* stream);
+
+/* Counters for bench.py's `gpu_launches`: number of kernels this library has launched from the
+ * calling process since load / since the last reset (relaxed atomic; diagnostics only). */
+uint64_t dibr_kernel_launch_count(void);
+void dibr_reset_kernel_launch_count(void);
+
+/* Measurement hook (bench.py roofline leg).  Brackets the calling thread's NEXT launch of kernel
+ * `kernel_id` with cudaEventRecord(start_event) / cudaEventRecord(stop_event) on the launch stream, then
+ * disarms itself.  kernel_id < 0 disarms.  The events are cudaEvent_t handles owned by the caller. */
+enum {
+  DIBR_KERNEL_SETUP_COUNT = 0,
+  DIBR_KERNEL_SCAN = 1,
+  DIBR_KERNEL_FILL = 2,
+  DIBR_KERNEL_RASTER_FWD = 3,
+  DIBR_KERNEL_RASTER_BWD = 4,
+  DIBR_KERNEL_SOFT_FWD = 5,
+  DIBR_KERNEL_SOFT_BWD = 6,
+  DIBR_KERNEL_COUNT = 7
+};
+int dibr_profile_next_launch(int kernel_id, void* start_event, void* stop_event);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* DIBR_B200_H_ */

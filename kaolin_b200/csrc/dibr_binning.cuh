@@ -1,0 +1,223 @@
+// dibr_binning.cuh — per-face setup (K0) and tile binning (K1) shared by the rasterizer and the
+// soft-mask kernels.
+//
+// K0/K1a  setup_count : one thread per face.  Replaces the torch glue of the reference
+//         (rasterization.py:309-344 valid-face packing + x multiplier + bbox; dibr.py:32-39 enlarged bbox)
+//         with one coalesced pass: multiplied coordinates -> bbox -> EXACT inclusive pixel range of the
+//         reference's half-open float test (rasterization_cuda.cu:115) -> 8-byte range record, and
+//         counts the face into every 16x16 tile it can touch.
+// K1b     scan        : per-view exclusive scan of the tile counters, segment base by one atomic.
+// K1c     fill        : scatter face ids into the per-tile lists.
+//
+// Faces spanning more than MAX_SPAN x MAX_SPAN tiles go to a per-view "large" list that every tile
+// of the view filters (ballot + prefix-scan compaction in the consumer), so the per-tile storage is
+// bounded by PAIRS_PER_FACE * faces and cannot overflow.  Lists are UNORDERED; consumers that need
+// face order (depth ties, soft-mask "first knum faces") use order-independent rules or sort in smem.
+#pragma once
+#include "dibr_common.cuh"
+
+namespace dibr {
+
+struct BinLists {
+  uint2* ranges;      // [Ntot]  packed inclusive pixel range per face (empty_range() = contributes nothing)
+  int* tile_count;    // [B*T]
+  int* tile_offset;   // [B*T]
+  int* tile_cursor;   // [B*T]   fill cursor (absolute position)
+  int* pairs;         // [PAIRS_PER_FACE * Ntot] face ids local to their view
+  int* large_list;    // [Ntot]  view b's entries start at view_base(b)
+  int* large_count;   // [B]
+  int* alloc_cursor;  // [1]
+};
+
+struct FaceLayout {   // batched (B,F) layout or packed layout with first_idx (B+1) on device
+  const int64_t* first_idx;   // nullptr => batched
+  int F;
+  int64_t Ntot;
+  int B;
+  __device__ __forceinline__ int64_t base(int b) const { return first_idx ? first_idx[b] : (int64_t)b * F; }
+  __device__ __forceinline__ int view_of(int64_t g) const {
+    if (!first_idx) return (int)(g / F);
+    int lo = 0, hi = B;                // largest b with first_idx[b] <= g
+    while (hi - lo > 1) {
+      const int mid = (lo + hi) >> 1;
+      if (first_idx[mid] <= g) lo = mid; else hi = mid;
+    }
+    return lo;
+  }
+};
+
+template <typename T>
+struct SetupParams {
+  const T* img;            // (Ntot,3,2)
+  const T* bbox_in;        // (Ntot,4) already multiplied/enlarged, or nullptr => computed here
+  const uint8_t* valid;    // (Ntot) or nullptr
+  T coord_mult;            // img is multiplied by this (1 when already multiplied)
+  int premultiplied;
+  T margin;                // bbox enlargement in multiplied units (0 for the rasterizer)
+  float pix_mult;          // the kernel-side `float multiplier` of the pixel centres
+};
+
+template <typename T>
+__device__ __forceinline__ void load_face_xy(const T* img, int64_t g, T coord_mult, int premultiplied, T* p) {
+  const T* s = img + g * 6;
+#pragma unroll
+  for (int k = 0; k < 6; ++k) p[k] = premultiplied ? s[k] : RN<T>::mul(s[k], coord_mult);
+}
+template <>
+__device__ __forceinline__ void load_face_xy<float>(const float* img, int64_t g, float coord_mult,
+                                                    int premultiplied, float* p) {
+  const float2* s = reinterpret_cast<const float2*>(img + g * 6);     // 24-byte records: 8-byte aligned
+  const float2 a = __ldg(s), b = __ldg(s + 1), c = __ldg(s + 2);
+  p[0] = a.x; p[1] = a.y; p[2] = b.x; p[3] = b.y; p[4] = c.x; p[5] = c.y;
+  if (!premultiplied) {
+#pragma unroll
+    for (int k = 0; k < 6; ++k) p[k] = __fmul_rn(p[k], coord_mult);
+  }
+}
+
+template <typename T>
+__global__ void __launch_bounds__(256) setup_count_kernel(SetupParams<T> sp, FaceLayout fl, Geometry geo,
+                                                          BinLists L) {
+  const int64_t g = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (g >= fl.Ntot) return;
+  uint2 rec = empty_range();
+  const bool is_valid = sp.valid ? (sp.valid[g] != 0) : true;
+  int b = 0;
+  if (is_valid) {
+    T xmin, ymin, xmax, ymax;
+    if (sp.bbox_in) {
+      const T* bb = sp.bbox_in + g * 4;
+      xmin = bb[0]; ymin = bb[1]; xmax = bb[2]; ymax = bb[3];
+    } else {
+      T p[6];
+      load_face_xy<T>(sp.img, g, sp.coord_mult, sp.premultiplied, p);
+      xmin = min_nan(min_nan(p[0], p[2]), p[4]);
+      xmax = max_nan(max_nan(p[0], p[2]), p[4]);
+      ymin = min_nan(min_nan(p[1], p[3]), p[5]);
+      ymax = max_nan(max_nan(p[1], p[3]), p[5]);
+      // dibr.py:36-38: points_min - boxlen*multiplier, points_max + boxlen*multiplier
+      xmin = RN<T>::sub(xmin, sp.margin); ymin = RN<T>::sub(ymin, sp.margin);
+      xmax = RN<T>::add(xmax, sp.margin); ymax = RN<T>::add(ymax, sp.margin);
+    }
+    const float sx = pix_scale(sp.pix_mult, geo.W), sy = pix_scale(sp.pix_mult, geo.H);
+    int ix0, ix1, ky0, ky1;
+    pass_range<T>(sx, geo.W, xmin, xmax, ix0, ix1);
+    pass_range<T>(sy, geo.H, ymin, ymax, ky0, ky1);      // k counts rows from the bottom
+    if (ix0 <= ix1 && ky0 <= ky1) {
+      const int jy0 = geo.H - 1 - ky1, jy1 = geo.H - 1 - ky0;
+      rec = pack_range(ix0, ix1, jy0, jy1);
+      b = fl.view_of(g);
+      const int tx0 = ix0 / TILE, tx1 = ix1 / TILE, ty0 = jy0 / TILE, ty1 = jy1 / TILE;
+      if (tx1 - tx0 < MAX_SPAN && ty1 - ty0 < MAX_SPAN) {
+        int* cnt = L.tile_count + (int64_t)b * geo.tiles_per_view;
+        for (int ty = ty0; ty <= ty1; ++ty)
+          for (int tx = tx0; tx <= tx1; ++tx) atomicAdd(cnt + ty * geo.tiles_x + tx, 1);
+      } else {
+        const int64_t vb = fl.base(b);
+        const int pos = atomicAdd(L.large_count + b, 1);
+        L.large_list[vb + pos] = (int)(g - vb);
+      }
+    }
+  }
+  L.ranges[g] = rec;
+}
+
+// one CTA per view
+__global__ void __launch_bounds__(1024) scan_kernel(Geometry geo, BinLists L) {
+  __shared__ int warp_sums[32];
+  __shared__ int s_base;
+  const int b = blockIdx.x;
+  const int T = geo.tiles_per_view;
+  const int* cnt = L.tile_count + (int64_t)b * T;
+  int* off = L.tile_offset + (int64_t)b * T;
+  int* cur = L.tile_cursor + (int64_t)b * T;
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  // pass 1: view total
+  int local = 0;
+  for (int t = threadIdx.x; t < T; t += blockDim.x) local += cnt[t];
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) local += __shfl_xor_sync(0xffffffffu, local, o);
+  if (lane == 0) warp_sums[warp] = local;
+  __syncthreads();
+  if (warp == 0) {
+    int v = warp_sums[lane];
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+    if (lane == 0) s_base = atomicAdd(L.alloc_cursor, v);
+  }
+  __syncthreads();
+  int running = s_base;
+  // pass 2: exclusive scan in chunks of blockDim.x
+  for (int t0 = 0; t0 < T; t0 += blockDim.x) {
+    const int t = t0 + threadIdx.x;
+    const int c = (t < T) ? cnt[t] : 0;
+    int incl = c;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+      const int n = __shfl_up_sync(0xffffffffu, incl, o);
+      if (lane >= o) incl += n;
+    }
+    __syncthreads();                       // warp_sums reuse
+    if (lane == 31) warp_sums[warp] = incl;
+    __syncthreads();
+    int wprefix = 0, total = 0;
+    {
+      const int v = warp_sums[lane];
+      int wi = v;
+#pragma unroll
+      for (int o = 1; o < 32; o <<= 1) {
+        const int n = __shfl_up_sync(0xffffffffu, wi, o);
+        if (lane >= o) wi += n;
+      }
+      wprefix = __shfl_sync(0xffffffffu, wi - v, warp);
+      total = __shfl_sync(0xffffffffu, wi, 31);
+    }
+    if (t < T) {
+      const int o = running + wprefix + incl - c;
+      off[t] = o;
+      cur[t] = o;
+    }
+    running += total;
+  }
+}
+
+__global__ void __launch_bounds__(256) fill_kernel(FaceLayout fl, Geometry geo, BinLists L) {
+  const int64_t g = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (g >= fl.Ntot) return;
+  const uint2 r = L.ranges[g];
+  if (range_empty(r)) return;
+  const int tx0 = (int)(r.x & 0xffffu) / TILE, tx1 = (int)(r.x >> 16) / TILE;
+  const int ty0 = (int)(r.y & 0xffffu) / TILE, ty1 = (int)(r.y >> 16) / TILE;
+  if (!(tx1 - tx0 < MAX_SPAN && ty1 - ty0 < MAX_SPAN)) return;      // in the large list
+  const int b = fl.view_of(g);
+  const int local = (int)(g - fl.base(b));
+  int* cur = L.tile_cursor + (int64_t)b * geo.tiles_per_view;
+  for (int ty = ty0; ty <= ty1; ++ty)
+    for (int tx = tx0; tx <= tx1; ++tx) {
+      const int pos = atomicAdd(cur + ty * geo.tiles_x + tx, 1);
+      L.pairs[pos] = local;
+    }
+}
+
+// ---------------------------------------------------------------- block-level ordered compaction
+// Every thread of a 256-thread CTA passes `flag`; returns the thread's slot among the flagged threads
+// (in thread order) and the block total.  `scratch` = 9 ints of shared memory.
+__device__ __forceinline__ int block_compact_256(bool flag, int* scratch, int& total) {
+  const unsigned m = __ballot_sync(0xffffffffu, flag);
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int in_warp = __popc(m & ((1u << lane) - 1u));
+  __syncthreads();
+  if (lane == 0) scratch[warp] = __popc(m);
+  __syncthreads();
+  int pre = 0, tot = 0;
+#pragma unroll
+  for (int w = 0; w < 8; ++w) {
+    const int c = scratch[w];
+    if (w < warp) pre += c;
+    tot += c;
+  }
+  total = tot;
+  return pre + in_warp;
+}
+
+}  // namespace dibr

@@ -1,0 +1,335 @@
+// dibr_c_abi.cu — extern "C" entry points of libdibr_b200.so (declared in include/dibr_b200.h).
+// Host logic only: argument checks, workspace carving, kernel launches on the caller's stream.
+#include "../../include/dibr_b200.h"
+#include "dibr_binning.cuh"
+#include "dibr_raster_fwd.cuh"
+#include "dibr_raster_bwd.cuh"
+#include "dibr_soft_mask.cuh"
+
+#include <atomic>
+#include <cstdio>
+#include <cstring>
+
+using namespace dibr;
+
+namespace {
+
+std::atomic<uint64_t> g_launches{0};
+thread_local char t_cuda_err[256] = {0};
+
+inline int cuda_fail(cudaError_t e, const char* where) {
+  snprintf(t_cuda_err, sizeof(t_cuda_err), "%s: %s", where, cudaGetErrorString(e));
+  return DIBR_ERR_CUDA;
+}
+#define CUDA_TRY(expr)                                  \
+  do {                                                  \
+    cudaError_t _e = (expr);                            \
+    if (_e != cudaSuccess) return cuda_fail(_e, #expr); \
+  } while (0)
+#define LAUNCH_CHECK(name)                                  \
+  do {                                                      \
+    g_launches.fetch_add(1, std::memory_order_relaxed);     \
+    cudaError_t _e = cudaGetLastError();                    \
+    if (_e != cudaSuccess) return cuda_fail(_e, name);      \
+  } while (0)
+
+// Optional per-kernel timing hook (bench.py's roofline leg): the calling thread names ONE kernel id and a
+// pair of CUDA events; the next launch of that kernel on this thread is bracketed by the two events on
+// the launch stream.  Off by default; costs nothing when unset.
+thread_local int t_prof_kernel = -1;
+thread_local cudaEvent_t t_prof_start = nullptr, t_prof_stop = nullptr;
+struct ProfScope {
+  bool on; cudaStream_t s;
+  ProfScope(int id, cudaStream_t st) : on(id == t_prof_kernel && t_prof_start), s(st) {
+    if (on) cudaEventRecord(t_prof_start, s);
+  }
+  ~ProfScope() { if (on) { cudaEventRecord(t_prof_stop, s); t_prof_kernel = -1; } }
+};
+
+inline size_t align_up(size_t v, size_t a = 256) { return (v + a - 1) / a * a; }
+
+// Workspace carving: two BinLists (index 0 = rasterizer, 1 = soft mask) — each entry point uses one.
+struct WsLayout {
+  size_t ranges, tile_count, tile_offset, tile_cursor, pairs, large_list, large_count, alloc_cursor;
+  size_t zero_begin, zero_end;     // [tile_count | large_count | alloc_cursor] are contiguous => one memset
+  size_t total;
+};
+WsLayout ws_layout(int B, int64_t Ntot, const Geometry& geo) {
+  WsLayout w;
+  const size_t bt = (size_t)B * geo.tiles_per_view;
+  size_t o = 0;
+  w.zero_begin = o;
+  w.tile_count = o;  o = align_up(o + bt * sizeof(int));
+  w.large_count = o; o = align_up(o + (size_t)B * sizeof(int));
+  w.alloc_cursor = o; o = align_up(o + sizeof(int));
+  w.zero_end = o;
+  w.tile_offset = o; o = align_up(o + bt * sizeof(int));
+  w.tile_cursor = o; o = align_up(o + bt * sizeof(int));
+  w.ranges = o;      o = align_up(o + (size_t)Ntot * sizeof(uint2));
+  w.large_list = o;  o = align_up(o + (size_t)Ntot * sizeof(int));
+  w.pairs = o;       o = align_up(o + (size_t)Ntot * PAIRS_PER_FACE * sizeof(int));
+  w.total = o;
+  return w;
+}
+BinLists carve(void* ws, const WsLayout& w) {
+  unsigned char* p = static_cast<unsigned char*>(ws);
+  BinLists L;
+  L.ranges = reinterpret_cast<uint2*>(p + w.ranges);
+  L.tile_count = reinterpret_cast<int*>(p + w.tile_count);
+  L.tile_offset = reinterpret_cast<int*>(p + w.tile_offset);
+  L.tile_cursor = reinterpret_cast<int*>(p + w.tile_cursor);
+  L.pairs = reinterpret_cast<int*>(p + w.pairs);
+  L.large_list = reinterpret_cast<int*>(p + w.large_list);
+  L.large_count = reinterpret_cast<int*>(p + w.large_count);
+  L.alloc_cursor = reinterpret_cast<int*>(p + w.alloc_cursor);
+  return L;
+}
+
+int check_dims(int B, int64_t Ntot, int H, int W) {
+  if (B < 0 || Ntot < 0 || H < 0 || W < 0) return DIBR_ERR_INVALID_ARGUMENT;
+  if (H > 32768 || W > 32768) return DIBR_ERR_TOO_LARGE;
+  if (Ntot >= (int64_t)1 << 31 || (int64_t)B * H * W >= (int64_t)1 << 40) return DIBR_ERR_TOO_LARGE;
+  const Geometry geo = make_geometry(B, H, W);
+  if ((int64_t)B * geo.tiles_per_view >= (int64_t)1 << 31) return DIBR_ERR_TOO_LARGE;
+  return DIBR_OK;
+}
+
+// K0 + K1: ranges, counts, scan, fill.  3 kernels + 1 memset.
+template <typename T>
+int run_binning(const SetupParams<T>& sp, const FaceLayout& fl, const Geometry& geo, void* ws, size_t ws_bytes,
+                cudaStream_t s, BinLists& L) {
+  const WsLayout w = ws_layout(geo.B, fl.Ntot, geo);
+  if (!ws || ws_bytes < w.total) return DIBR_ERR_WORKSPACE;
+  L = carve(ws, w);
+  CUDA_TRY(cudaMemsetAsync(static_cast<unsigned char*>(ws) + w.zero_begin, 0, w.zero_end - w.zero_begin, s));
+  const unsigned nb = (unsigned)((fl.Ntot + 255) / 256);
+  if (nb > 0) {
+    { ProfScope ps(DIBR_KERNEL_SETUP_COUNT, s); setup_count_kernel<T><<<nb, 256, 0, s>>>(sp, fl, geo, L); }
+    LAUNCH_CHECK("setup_count_kernel");
+  }
+  { ProfScope ps(DIBR_KERNEL_SCAN, s); scan_kernel<<<geo.B, 1024, 0, s>>>(geo, L); }
+  LAUNCH_CHECK("scan_kernel");
+  if (nb > 0) {
+    { ProfScope ps(DIBR_KERNEL_FILL, s); fill_kernel<<<nb, 256, 0, s>>>(fl, geo, L); }
+    LAUNCH_CHECK("fill_kernel");
+  }
+  return DIBR_OK;
+}
+
+template <typename T>
+int rasterize_fwd_impl(const T* z, const T* img, const T* bbox_in, const T* feat, const uint8_t* valid,
+                       const int64_t* first_idx, int B, int F, int64_t Ntot, int C, int H, int W,
+                       T coord_mult, int premultiplied, float pix_mult, float eps, T* out_feat,
+                       int64_t* out_idx, T* out_w, void* ws, size_t ws_bytes, void* stream) {
+  if (int e = check_dims(B, Ntot, H, W)) return e;
+  if (C < 0 || !(pix_mult > 0.0f)) return DIBR_ERR_INVALID_ARGUMENT;
+  if (B == 0 || H == 0 || W == 0) return DIBR_OK;
+  if ((Ntot > 0 && (!z || !img || (C > 0 && !feat))) || !out_idx || (C > 0 && !out_feat))
+    return DIBR_ERR_INVALID_ARGUMENT;
+  cudaStream_t s = static_cast<cudaStream_t>(stream);
+  const Geometry geo = make_geometry(B, H, W);
+  FaceLayout fl; fl.first_idx = first_idx; fl.F = F; fl.Ntot = Ntot; fl.B = B;
+  SetupParams<T> sp;
+  sp.img = img; sp.bbox_in = bbox_in; sp.valid = valid; sp.coord_mult = coord_mult;
+  sp.premultiplied = premultiplied; sp.margin = (T)0; sp.pix_mult = pix_mult;
+  BinLists L;
+  if (int e = run_binning<T>(sp, fl, geo, ws, ws_bytes, s, L)) return e;
+  RasterFwdParams<T> rp;
+  rp.z = z; rp.img = img; rp.feat = feat; rp.coord_mult = coord_mult; rp.premultiplied = premultiplied;
+  rp.pix_mult = pix_mult; rp.eps = eps; rp.C = C; rp.out_feat = out_feat; rp.out_idx = out_idx; rp.out_w = out_w;
+  {
+    ProfScope ps(DIBR_KERNEL_RASTER_FWD, s);
+    raster_fwd_kernel<T><<<(unsigned)(B * geo.tiles_per_view), 256, 0, s>>>(rp, fl, geo, L);
+  }
+  LAUNCH_CHECK("raster_fwd_kernel");
+  return DIBR_OK;
+}
+
+template <typename T>
+int rasterize_bwd_impl(const T* grad_out, const int64_t* face_idx, const T* weights, const T* img, const T* feat,
+                       int B, int F, int C, int H, int W, double multiplier, float eps, T* grad_img,
+                       T* grad_feat, void* stream) {
+  if (int e = check_dims(B, (int64_t)B * F, H, W)) return e;
+  if (C < 0 || F < 0) return DIBR_ERR_INVALID_ARGUMENT;
+  if (!weights && !((float)multiplier > 0.0f)) return DIBR_ERR_INVALID_ARGUMENT;
+  cudaStream_t s = static_cast<cudaStream_t>(stream);
+  const size_t nf = (size_t)B * F;
+  if (nf > 0) {
+    if (!grad_img || (C > 0 && !grad_feat)) return DIBR_ERR_INVALID_ARGUMENT;
+    CUDA_TRY(cudaMemsetAsync(grad_img, 0, nf * 6 * sizeof(T), s));
+    if (C > 0) CUDA_TRY(cudaMemsetAsync(grad_feat, 0, nf * 3 * C * sizeof(T), s));
+  }
+  if (B == 0 || H == 0 || W == 0 || nf == 0) return DIBR_OK;
+  if (!grad_out && C > 0) return DIBR_ERR_INVALID_ARGUMENT;
+  if (!face_idx || !img || (C > 0 && !feat)) return DIBR_ERR_INVALID_ARGUMENT;
+  const Geometry geo = make_geometry(B, H, W);
+  RasterBwdParams<T> bp;
+  bp.grad_out = grad_out; bp.face_idx = face_idx; bp.weights = weights; bp.img = img; bp.feat = feat;
+  bp.coord_mult = (T)multiplier; bp.pix_mult = (float)multiplier; bp.eps = eps; bp.F = F; bp.C = C;
+  bp.grad_img = grad_img; bp.grad_feat = grad_feat;
+  {
+    ProfScope ps(DIBR_KERNEL_RASTER_BWD, s);
+    raster_bwd_kernel<T><<<(unsigned)(B * geo.tiles_per_view), 256, 0, s>>>(bp, geo);
+  }
+  LAUNCH_CHECK("raster_bwd_kernel");
+  return DIBR_OK;
+}
+
+template <typename T, int MODE>
+int soft_mask_impl(const T* img, const T* bbox_in, const int64_t* face_idx, int B, int F, int H, int W,
+                   float sigmainv, int knum, T coord_mult, int premultiplied, T margin, float pix_mult,
+                   T* soft, T* prob, int64_t* close_idx, uint8_t* dist_type, const T* grad_soft, const T* soft_in,
+                   T* grad_img, void* ws, size_t ws_bytes, void* stream) {
+  if (int e = check_dims(B, (int64_t)B * F, H, W)) return e;
+  if (F < 0 || knum < 0 || !(pix_mult > 0.0f)) return DIBR_ERR_INVALID_ARGUMENT;
+  const bool side = prob || close_idx || dist_type;
+  if (side && !(prob && close_idx && dist_type)) return DIBR_ERR_INVALID_ARGUMENT;
+  cudaStream_t s = static_cast<cudaStream_t>(stream);
+  const size_t nf = (size_t)B * F;
+  if (MODE == MODE_BWD && nf > 0) {
+    if (!grad_img) return DIBR_ERR_INVALID_ARGUMENT;
+    CUDA_TRY(cudaMemsetAsync(grad_img, 0, nf * 6 * sizeof(T), s));
+  }
+  if (B == 0 || H == 0 || W == 0) return DIBR_OK;
+  if (!face_idx || (nf > 0 && !img)) return DIBR_ERR_INVALID_ARGUMENT;
+  if (MODE == MODE_FWD && !soft) return DIBR_ERR_INVALID_ARGUMENT;
+  if (MODE == MODE_BWD && (!grad_soft || !soft_in)) return DIBR_ERR_INVALID_ARGUMENT;
+  const Geometry geo = make_geometry(B, H, W);
+  FaceLayout fl; fl.first_idx = nullptr; fl.F = F; fl.Ntot = (int64_t)nf; fl.B = B;
+  SetupParams<T> sp;
+  sp.img = img; sp.bbox_in = bbox_in; sp.valid = nullptr; sp.coord_mult = coord_mult;
+  sp.premultiplied = premultiplied; sp.margin = margin; sp.pix_mult = pix_mult;
+  BinLists L;
+  if (int e = run_binning<T>(sp, fl, geo, ws, ws_bytes, s, L)) return e;
+  SoftParams<T> p;
+  p.img = img; p.coord_mult = coord_mult; p.premultiplied = premultiplied; p.pix_mult = pix_mult;
+  p.sigmainv = sigmainv; p.F = F; p.knum = knum; p.face_idx = face_idx; p.soft = soft; p.prob = prob;
+  p.close_idx = close_idx; p.dist_type = dist_type; p.grad_soft = grad_soft; p.soft_in = soft_in;
+  p.grad_img = grad_img;
+  const size_t smem = SOFT_CAP * (sizeof(int) + sizeof(uint2));
+  CUDA_TRY(cudaFuncSetAttribute(soft_mask_kernel<T, MODE>, cudaFuncAttributeMaxDynamicSharedMemorySize, 65536));
+  {
+    ProfScope ps(MODE == MODE_FWD ? DIBR_KERNEL_SOFT_FWD : DIBR_KERNEL_SOFT_BWD, s);
+    soft_mask_kernel<T, MODE><<<(unsigned)(B * geo.tiles_per_view), 256, smem, s>>>(p, fl, geo, L);
+  }
+  LAUNCH_CHECK("soft_mask_kernel");
+  return DIBR_OK;
+}
+
+template <typename T>
+int soft_mask_bwd_sidebuf_impl(const T* grad_soft, const T* soft, const int64_t* face_idx, const T* prob,
+                               const int64_t* close_idx, const uint8_t* dist_type, const T* img_mult, int B, int F,
+                               int H, int W, int knum, float sigmainv, float multiplier, T* grad_img, void* stream) {
+  if (int e = check_dims(B, (int64_t)B * F, H, W)) return e;
+  if (F < 0 || knum < 0) return DIBR_ERR_INVALID_ARGUMENT;
+  cudaStream_t s = static_cast<cudaStream_t>(stream);
+  const size_t nf = (size_t)B * F;
+  if (nf > 0) {
+    if (!grad_img) return DIBR_ERR_INVALID_ARGUMENT;
+    CUDA_TRY(cudaMemsetAsync(grad_img, 0, nf * 6 * sizeof(T), s));
+  }
+  const int64_t P = (int64_t)B * H * W;
+  if (P == 0 || nf == 0 || knum == 0) return DIBR_OK;
+  if (!grad_soft || !soft || !face_idx || !prob || !close_idx || !dist_type || !img_mult)
+    return DIBR_ERR_INVALID_ARGUMENT;
+  soft_mask_bwd_sidebuf_kernel<T><<<(unsigned)((P + 255) / 256), 256, 0, s>>>(
+      grad_soft, soft, face_idx, prob, close_idx, dist_type, img_mult, grad_img, B, H, W, F, knum, sigmainv,
+      multiplier);
+  LAUNCH_CHECK("soft_mask_bwd_sidebuf_kernel");
+  return DIBR_OK;
+}
+
+}  // namespace
+
+#define DIBR_API extern "C" __attribute__((visibility("default")))
+
+DIBR_API int dibr_abi_version(void) { return DIBR_ABI_VERSION; }
+DIBR_API const char* dibr_error_string(int code) {
+  switch (code) {
+    case DIBR_OK: return "ok";
+    case DIBR_ERR_INVALID_ARGUMENT: return "invalid argument (null pointer, negative size or unsupported value)";
+    case DIBR_ERR_WORKSPACE: return "workspace missing or smaller than dibr_workspace_bytes()";
+    case DIBR_ERR_CUDA: return "CUDA error (see dibr_last_cuda_error)";
+    case DIBR_ERR_TOO_LARGE: return "dimension too large for the kernels' index types";
+    default: return "unknown error code";
+  }
+}
+DIBR_API const char* dibr_last_cuda_error(void) { return t_cuda_err; }
+DIBR_API uint64_t dibr_kernel_launch_count(void) { return g_launches.load(std::memory_order_relaxed); }
+DIBR_API void dibr_reset_kernel_launch_count(void) { g_launches.store(0, std::memory_order_relaxed); }
+DIBR_API int dibr_profile_next_launch(int kernel_id, void* start_event, void* stop_event) {
+  if (kernel_id >= 0 && (!start_event || !stop_event)) return DIBR_ERR_INVALID_ARGUMENT;
+  t_prof_kernel = kernel_id;
+  t_prof_start = static_cast<cudaEvent_t>(start_event);
+  t_prof_stop = static_cast<cudaEvent_t>(stop_event);
+  return DIBR_OK;
+}
+
+DIBR_API size_t dibr_workspace_bytes(int batch_size, int64_t total_faces, int height, int width) {
+  if (batch_size < 0 || total_faces < 0 || height < 0 || width < 0) return 0;
+  return ws_layout(batch_size, total_faces, make_geometry(batch_size, height, width)).total;
+}
+
+#define DEFINE_ENTRY_POINTS(SUF, T)                                                                           \
+  DIBR_API int dibr_rasterize_fwd_fused_##SUF(const T* z, const T* img, const T* feat, const uint8_t* valid, \
+                                              int B, int F, int C, int H, int W, double multiplier,         \
+                                              float eps, T* out_feat, int64_t* out_face_idx,                \
+                                              T* out_weights, void* ws, size_t ws_bytes, void* stream) {    \
+    if (F < 0) return DIBR_ERR_INVALID_ARGUMENT;                                                              \
+    return rasterize_fwd_impl<T>(z, img, nullptr, feat, valid, nullptr, B, F, (int64_t)B * F, C, H, W,      \
+                                 (T)multiplier, 0, (float)multiplier, eps, out_feat, out_face_idx,           \
+                                 out_weights, ws, ws_bytes, stream);                                          \
+  }                                                                                                           \
+  DIBR_API int dibr_packed_rasterize_forward_##SUF(                                                          \
+      int H, int W, const T* z, const T* img_mult, const T* bboxes, const T* feat, const int64_t* first_idx, \
+      int B, int64_t N, int C, float multiplier, float eps, T* out_feat, int64_t* out_selected_face_idx,     \
+      T* out_weights, void* ws, size_t ws_bytes, void* stream) {                                             \
+    if (!first_idx || (N > 0 && !bboxes)) return DIBR_ERR_INVALID_ARGUMENT;                                  \
+    return rasterize_fwd_impl<T>(z, img_mult, bboxes, feat, nullptr, first_idx, B, 0, N, C, H, W, (T)1, 1,   \
+                                 multiplier, eps, out_feat, out_selected_face_idx, out_weights, ws,          \
+                                 ws_bytes, stream);                                                           \
+  }                                                                                                           \
+  DIBR_API int dibr_rasterize_backward_##SUF(const T* grad_out, const int64_t* face_idx, const T* weights,   \
+                                             const T* img, const T* feat, int B, int F, int C, int H,       \
+                                             int W, double multiplier, float eps, T* grad_img,              \
+                                             T* grad_feat, void* stream) {                                   \
+    return rasterize_bwd_impl<T>(grad_out, face_idx, weights, img, feat, B, F, C, H, W, multiplier, eps,     \
+                                 grad_img, grad_feat, stream);                                                \
+  }                                                                                                           \
+  DIBR_API int dibr_soft_mask_fwd_fused_##SUF(const T* img, const int64_t* face_idx, int B, int F, int H,    \
+                                              int W, float sigmainv, double boxlen, int knum,               \
+                                              double multiplier, T* soft, T* prob, int64_t* close_idx,      \
+                                              uint8_t* dist_type, void* ws, size_t ws_bytes, void* stream) { \
+    return soft_mask_impl<T, MODE_FWD>(img, nullptr, face_idx, B, F, H, W, sigmainv, knum, (T)multiplier, 0, \
+                                       (T)(boxlen * multiplier), (float)multiplier, soft, prob, close_idx,   \
+                                       dist_type, nullptr, nullptr, nullptr, ws, ws_bytes, stream);           \
+  }                                                                                                           \
+  DIBR_API int dibr_soft_mask_forward_##SUF(const T* img_mult, const T* large_bboxes,                        \
+                                            const int64_t* face_idx, int B, int F, int H, int W,            \
+                                            float sigmainv, int knum, float multiplier, T* soft, T* prob,   \
+                                            int64_t* close_idx, uint8_t* dist_type, void* ws,               \
+                                            size_t ws_bytes, void* stream) {                                 \
+    if ((int64_t)B * F > 0 && !large_bboxes) return DIBR_ERR_INVALID_ARGUMENT;                               \
+    return soft_mask_impl<T, MODE_FWD>(img_mult, large_bboxes, face_idx, B, F, H, W, sigmainv, knum, (T)1,  \
+                                       1, (T)0, multiplier, soft, prob, close_idx, dist_type, nullptr,      \
+                                       nullptr, nullptr, ws, ws_bytes, stream);                               \
+  }                                                                                                           \
+  DIBR_API int dibr_soft_mask_backward_##SUF(const T* grad_soft, const T* soft, const int64_t* face_idx,     \
+                                             const T* prob, const int64_t* close_idx,                        \
+                                             const uint8_t* dist_type, const T* img_mult, int B, int F,     \
+                                             int H, int W, int knum, float sigmainv, float multiplier,      \
+                                             T* grad_img, void* stream) {                                    \
+    return soft_mask_bwd_sidebuf_impl<T>(grad_soft, soft, face_idx, prob, close_idx, dist_type, img_mult, B, \
+                                         F, H, W, knum, sigmainv, multiplier, grad_img, stream);             \
+  }                                                                                                           \
+  DIBR_API int dibr_soft_mask_bwd_fused_##SUF(const T* grad_soft, const T* soft, const int64_t* face_idx,    \
+                                              const T* img, int B, int F, int H, int W, float sigmainv,     \
+                                              double boxlen, int knum, double multiplier, T* grad_img,      \
+                                              void* ws, size_t ws_bytes, void* stream) {                     \
+    return soft_mask_impl<T, MODE_BWD>(img, nullptr, face_idx, B, F, H, W, sigmainv, knum, (T)multiplier, 0, \
+                                       (T)(boxlen * multiplier), (float)multiplier, nullptr, nullptr,        \
+                                       nullptr, nullptr, grad_soft, soft, grad_img, ws, ws_bytes, stream);    \
+  }
+
+DEFINE_ENTRY_POINTS(f32, float)
+DEFINE_ENTRY_POINTS(f64, double)

@@ -1,0 +1,253 @@
+// dibr_soft_mask.cuh — K3/K5: DIB-R soft mask forward and backward (reference:
+// dibr_soft_mask_cuda.cu:27-184 and :230-353).
+//
+// One CTA = one 16x16 tile.  Only tiles with at least one uncovered pixel do any work beyond the
+// face_idx read / soft write.  The tile's candidate faces (enlarged-bbox tile list + filtered "large"
+// faces) are gathered into shared memory, bitonic-sorted by face index — the reference keeps the FIRST
+// `knum` faces in face order whose enlarged bbox contains the pixel (:80-171), so order is semantic —
+// and their pixel ranges are staged next to them.  Each uncovered pixel then walks the sorted list.
+//
+// MODE_FWD writes soft (+ optional k-list side buffers, API-visible through
+// _C.render.mesh.dibr_soft_mask_forward_cuda).  MODE_BWD re-derives the same k-list with the same
+// arithmetic instead of reading 13*knum bytes per pixel of side buffers, and accumulates the vertex
+// gradients with red.global.add.
+#pragma once
+#include "dibr_binning.cuh"
+
+namespace dibr {
+
+constexpr int SOFT_CAP = 4096;      // candidate faces per tile held in shared memory
+constexpr int MODE_FWD = 0;
+constexpr int MODE_BWD = 1;
+
+template <typename T>
+struct SoftParams {
+  const T* img;               // (B,F,3,2)
+  T coord_mult;
+  int premultiplied;
+  float pix_mult;             // kernel-side float multiplier
+  float sigmainv;
+  int F, knum;
+  const int64_t* face_idx;    // (B,H,W)
+  // forward
+  T* soft;                    // (B,H,W)
+  T* prob;                    // (B,H,W,K) or nullptr
+  int64_t* close_idx;         // (B,H,W,K) or nullptr
+  uint8_t* dist_type;         // (B,H,W,K) or nullptr
+  // backward
+  const T* grad_soft;         // (B,H,W)
+  const T* soft_in;           // (B,H,W)
+  T* grad_img;                // (B,F,3,2)
+};
+
+// dibr_soft_mask_cuda.cu:283-347 for one (pixel, face) pair; p = multiplied coordinates.
+template <typename T>
+__device__ __forceinline__ void soft_backward_pair(const T* p, const T x0, const T y0, const T prob,
+                                                   const int edgeid, const T dLdp, const T allprob,
+                                                   const float sigmainv, const float multiplier, T* gi) {
+  const double EPS = 1e-7;
+  const T dLdz = (T)(-1.0 * (double)sigmainv * (double)dLdp * (1.0 - (double)allprob) /
+                     (1.0 - (double)prob + EPS) * (double)prob);
+  if (edgeid >= 3) {
+    const int o = (edgeid - 3) * 2;
+    const T x1 = p[o], y1 = p[o + 1];
+    atomicAdd(gi + o, dLdz * 2 * (x1 - x0) / (T)multiplier);
+    atomicAdd(gi + o + 1, dLdz * 2 * (y1 - y0) / (T)multiplier);
+  } else {
+    const int o = edgeid * 2, o2 = ((edgeid + 1) % 3) * 2;
+    const T x1 = p[o], y1 = p[o + 1], x2 = p[o2], y2 = p[o2 + 1];
+    const T A = y2 - y1, Bc = x1 - x2, Cc = x2 * y1 - x1 * y2;
+    const T up = A * x0 + Bc * y0 + Cc;
+    const T down = A * A + Bc * Bc;
+    const double den = (double)down + EPS;
+    const T dissquare = (T)((double)(up * up) / den);
+    const T dzdA = (T)((double)(2 * (x0 * up - dissquare * A)) / den);
+    const T dzdB = (T)((double)(2 * (y0 * up - dissquare * Bc)) / den);
+    const T dzdC = (T)((double)(2 * up) / den);
+    atomicAdd(gi + o, dLdz * (dzdB - y2 * dzdC) / (T)multiplier);
+    atomicAdd(gi + o + 1, dLdz * (x2 * dzdC - dzdA) / (T)multiplier);
+    atomicAdd(gi + o2, dLdz * (y1 * dzdC - dzdB) / (T)multiplier);
+    atomicAdd(gi + o2 + 1, dLdz * (dzdA - x1 * dzdC) / (T)multiplier);
+  }
+}
+
+template <typename T, int MODE>
+struct SoftPixel {            // per-pixel running state of the k-list walk
+  T x0, y0;
+  int kid;
+  T allprob;                  // forward: running product of (1 - prob)
+  T dLdp, soft;               // backward inputs
+  int64_t pix;
+};
+
+template <typename T, int MODE>
+__device__ __forceinline__ void soft_visit(const SoftParams<T>& sp, SoftPixel<T, MODE>& st, const int64_t vbase,
+                                           const int f) {
+  T p[6];
+  load_face_xy<T>(sp.img, vbase + f, sp.coord_mult, sp.premultiplied, p);
+  int edgeid;
+  const T d = soft_distance<T>(p, st.x0, st.y0, sp.pix_mult, edgeid);
+  const T prob = soft_prob<T>(d, sp.sigmainv, sp.pix_mult);
+  if (MODE == MODE_FWD) {
+    if (sp.prob) {
+      const int64_t o = st.pix * sp.knum + st.kid;
+      sp.prob[o] = prob;
+      sp.close_idx[o] = (int64_t)f;
+      sp.dist_type[o] = (uint8_t)(edgeid + 1);
+    }
+    st.allprob = (T)((double)st.allprob * (1.0 - (double)prob));     // :174-178, same order
+  } else {
+    soft_backward_pair<T>(p, st.x0, st.y0, prob, edgeid, st.dLdp, st.soft, sp.sigmainv, sp.pix_mult,
+                          sp.grad_img + (vbase + f) * 6);
+  }
+  ++st.kid;
+}
+
+template <typename T, int MODE>
+__global__ void __launch_bounds__(256) soft_mask_kernel(SoftParams<T> sp, FaceLayout fl, Geometry geo,
+                                                        BinLists L) {
+  extern __shared__ __align__(16) unsigned char smem_raw[];
+  int* s_ids = reinterpret_cast<int*>(smem_raw);                          // [SOFT_CAP]
+  uint2* s_rng = reinterpret_cast<uint2*>(smem_raw + SOFT_CAP * sizeof(int));   // [SOFT_CAP]
+  __shared__ int scratch[9];
+  __shared__ int s_count;
+
+  const int tile = blockIdx.x % geo.tiles_per_view;
+  const int b = blockIdx.x / geo.tiles_per_view;
+  const int tx = tile % geo.tiles_x, ty = tile / geo.tiles_x;
+  const int px = tx * TILE + (threadIdx.x & (TILE - 1));
+  const int py = ty * TILE + (threadIdx.x / TILE);
+  const bool in_image = px < geo.W && py < geo.H;
+  const int64_t vbase = fl.base(b);
+
+  SoftPixel<T, MODE> st;
+  st.pix = ((int64_t)b * geo.H + py) * geo.W + px;
+  st.kid = 0;
+  st.allprob = (T)1.0;
+  const bool uncovered = in_image && (sp.face_idx[st.pix] < 0);
+  const int K = sp.knum;
+
+  if (MODE == MODE_FWD && in_image && !uncovered) {
+    sp.soft[st.pix] = (T)1.0;                                           // :68-70
+    if (sp.prob) {                                                      // dibr_soft_mask.cpp:86-96 defaults
+      for (int k = 0; k < K; ++k) {
+        sp.prob[st.pix * K + k] = (T)0;
+        sp.close_idx[st.pix * K + k] = -1;
+        sp.dist_type[st.pix * K + k] = 0;
+      }
+    }
+  }
+  if (!__syncthreads_or(uncovered)) return;
+
+  if (uncovered) {
+    st.x0 = (T)pix_coord(pix_scale(sp.pix_mult, geo.W), geo.W, px);
+    st.y0 = (T)pix_coord(pix_scale(sp.pix_mult, geo.H), geo.H, geo.H - 1 - py);
+    if (MODE == MODE_BWD) {
+      st.dLdp = sp.grad_soft[st.pix];
+      st.soft = sp.soft_in[st.pix];
+    }
+  }
+
+  // ---- gather the candidates
+  const int n_tile = L.tile_count[blockIdx.x];
+  const int* tile_list = L.pairs + L.tile_offset[blockIdx.x];
+  const int n_large = L.large_count[b];
+  const int* large_list = L.large_list + vbase;
+  const int rx0 = tx * TILE, ry0 = ty * TILE, rx1 = rx0 + TILE - 1, ry1 = ry0 + TILE - 1;
+  bool overflow = n_tile > SOFT_CAP;
+  int count = 0;
+  if (!overflow) {
+    for (int k = threadIdx.x; k < n_tile; k += 256) s_ids[k] = tile_list[k];
+    count = n_tile;
+    for (int base = 0; base < n_large; base += 256) {                  // n_large is CTA-uniform
+      const int k = base + threadIdx.x;
+      int f = -1;
+      if (k < n_large) {
+        f = large_list[k];
+        if (!range_hits_rect(L.ranges[vbase + f], rx0, ry0, rx1, ry1)) f = -1;
+      }
+      int add;
+      const int slot = block_compact_256(f >= 0, scratch, add);
+      if (count + add > SOFT_CAP) { overflow = true; break; }          // uniform
+      if (f >= 0) s_ids[count + slot] = f;
+      count += add;
+    }
+  }
+
+  if (!overflow) {
+    // ---- bitonic sort by face index (pad with INT_MAX)
+    int n2 = 1;
+    while (n2 < count) n2 <<= 1;
+    for (int k = count + threadIdx.x; k < n2; k += 256) s_ids[k] = 0x7fffffff;
+    __syncthreads();
+    for (int size = 2; size <= n2; size <<= 1) {
+      for (int stride = size >> 1; stride > 0; stride >>= 1) {
+        for (int t = threadIdx.x; t < (n2 >> 1); t += 256) {
+          const int lo = ((t / stride) * stride * 2) + (t % stride);
+          const int hi = lo + stride;
+          const bool up = ((lo & size) == 0);
+          const int a = s_ids[lo], c = s_ids[hi];
+          if ((a > c) == up) { s_ids[lo] = c; s_ids[hi] = a; }
+        }
+        __syncthreads();
+      }
+    }
+    for (int k = threadIdx.x; k < count; k += 256) s_rng[k] = L.ranges[vbase + s_ids[k]];
+    __syncthreads();
+    if (uncovered) {
+      for (int s = 0; s < count && st.kid < K; ++s) {
+        if (!range_hits_pixel(s_rng[s], px, py)) continue;
+        soft_visit<T, MODE>(sp, st, vbase, s_ids[s]);
+      }
+    }
+  } else if (uncovered) {
+    // ---- more candidates than shared memory holds: the reference's in-order scan over every face
+    const int nf = (int)(fl.base(b + 1) - vbase);
+    for (int f = 0; f < nf && st.kid < K; ++f) {
+      if (!range_hits_pixel(L.ranges[vbase + f], px, py)) continue;
+      soft_visit<T, MODE>(sp, st, vbase, f);
+    }
+  }
+
+  if (MODE == MODE_FWD && uncovered) {
+    sp.soft[st.pix] = (T)(1.0 - (double)st.allprob);                    // :181-182
+    if (sp.prob) {
+      for (int k = st.kid; k < K; ++k) {
+        sp.prob[st.pix * K + k] = (T)0;
+        sp.close_idx[st.pix * K + k] = -1;
+        sp.dist_type[st.pix * K + k] = 0;
+      }
+    }
+  }
+}
+
+// ---------------------------------------------------------------- reference-shaped backward from side buffers
+template <typename T>
+__global__ void __launch_bounds__(256) soft_mask_bwd_sidebuf_kernel(
+    const T* __restrict__ grad_soft, const T* __restrict__ soft, const int64_t* __restrict__ face_idx,
+    const T* __restrict__ prob, const int64_t* __restrict__ close_idx, const uint8_t* __restrict__ dist_type,
+    const T* __restrict__ img_mult, T* grad_img, int B, int H, int W, int F, int K, float sigmainv,
+    float multiplier) {
+  const int64_t pix = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (pix >= (int64_t)B * H * W) return;
+  if (face_idx[pix] >= 0) return;                                       // :266
+  const int px = (int)(pix % W);
+  const int py = (int)((pix / W) % H);
+  const int b = (int)(pix / ((int64_t)W * H));
+  const T x0 = (T)pix_coord(pix_scale(multiplier, W), W, px);
+  const T y0 = (T)pix_coord(pix_scale(multiplier, H), H, H - 1 - py);
+  const T dLdp = grad_soft[pix], allprob = soft[pix];
+  for (int k = 0; k < K; ++k) {                                         // :271-276
+    const int64_t f = close_idx[pix * K + k];
+    if (f < 0) break;
+    if (f >= F) continue;
+    const int64_t s6 = ((int64_t)b * F + f) * 6;
+    T p[6];
+#pragma unroll
+    for (int q = 0; q < 6; ++q) p[q] = img_mult[s6 + q];
+    soft_backward_pair<T>(p, x0, y0, prob[pix * K + k], (int)dist_type[pix * K + k] - 1, dLdp, allprob,
+                          sigmainv, multiplier, grad_img + s6);
+  }
+}
+
+}  // namespace dibr

@@ -1,0 +1,121 @@
+"""Mirror of kaolin/render/mesh/dibr.py (``dibr_soft_mask``, ``dibr_rasterization``, ``DibrSoftMaskCuda``),
+backed by libdibr_b200.so.
+
+``DibrSoftMaskCuda.forward`` of the reference multiplies the coordinates, builds enlarged bboxes with five
+torch kernels and saves three (B,H,W,knum) side buffers (13*knum bytes per pixel) for backward
+(dibr.py:31-54).  Here one C-ABI call does setup + binning + the soft-mask kernel, writes only ``soft_mask``,
+and backward re-derives each uncovered pixel's k-list with the forward arithmetic.
+"""
+import torch
+from torch.autograd import Function
+
+from ... import _C  # noqa: F401
+from ... import _lib
+from .rasterization import rasterize, _legacy_to_opengl, nvdiff, _get_nvdiff_glctx, _require_cuda  # noqa: F401
+
+__all__ = [
+    "dibr_soft_mask",
+    "dibr_rasterization",
+]
+
+
+class DibrSoftMaskCuda(Function):
+    """forward(ctx, face_vertices_image, selected_face_idx, sigmainv, boxlen, knum, multiplier) -> soft_mask;
+    backward(ctx, grad_soft_mask) -> (grad_face_vertices_image, None x5)   (reference: dibr.py:27-73)."""
+    @staticmethod
+    def forward(ctx, face_vertices_image, selected_face_idx, sigmainv, boxlen, knum, multiplier):
+        fn = "dibr_soft_mask_forward_cuda"
+        dev = _require_cuda(fn, face_vertices_image=face_vertices_image, selected_face_idx=selected_face_idx)
+        face_vertices_image = face_vertices_image.contiguous()
+        selected_face_idx = selected_face_idx.contiguous()
+        if face_vertices_image.dim() != 4 or tuple(face_vertices_image.shape[2:]) != (3, 2):
+            raise RuntimeError(f"{fn}: face_vertices_image must be of shape (B,F,3,2)")
+        b, f = face_vertices_image.shape[0], face_vertices_image.shape[1]
+        if selected_face_idx.dim() != 3 or selected_face_idx.shape[0] != b or selected_face_idx.dtype != torch.long:
+            raise RuntimeError(f"{fn}: selected_face_idx must be a LongTensor of shape (B,H,W)")
+        h, w = selected_face_idx.shape[1], selected_face_idx.shape[2]
+        suf = _lib.suffix(face_vertices_image.dtype, fn)
+        soft_mask = torch.empty((b, h, w), dtype=face_vertices_image.dtype, device=dev)
+        with torch.cuda.device(dev):
+            ws, nbytes = _lib.workspace(b, b * f, h, w, dev)
+            code = getattr(_lib.load(), "dibr_soft_mask_fwd_fused_" + suf)(
+                _lib.ptr(face_vertices_image), _lib.ptr(selected_face_idx), b, f, h, w, float(sigmainv),
+                float(boxlen), int(knum), float(multiplier), _lib.ptr(soft_mask), 0, 0, 0, _lib.ptr(ws), nbytes,
+                _lib.current_stream(dev))
+        _lib.check(code, fn)
+        ctx.multiplier = multiplier
+        ctx.sigmainv = sigmainv
+        ctx.boxlen = boxlen
+        ctx.knum = knum
+        ctx.save_for_backward(soft_mask, face_vertices_image, selected_face_idx)
+        return soft_mask
+
+    @staticmethod
+    def backward(ctx, grad_soft_mask):
+        fn = "dibr_soft_mask_backward_cuda"
+        soft_mask, face_vertices_image, selected_face_idx = ctx.saved_tensors
+        dev = face_vertices_image.device
+        b, f = face_vertices_image.shape[0], face_vertices_image.shape[1]
+        h, w = selected_face_idx.shape[1], selected_face_idx.shape[2]
+        suf = _lib.suffix(face_vertices_image.dtype, fn)
+        grad_soft_mask = grad_soft_mask.contiguous()
+        grad_face_vertices_image = torch.empty_like(face_vertices_image)
+        with torch.cuda.device(dev):
+            ws, nbytes = _lib.workspace(b, b * f, h, w, dev)
+            code = getattr(_lib.load(), "dibr_soft_mask_bwd_fused_" + suf)(
+                _lib.ptr(grad_soft_mask), _lib.ptr(soft_mask), _lib.ptr(selected_face_idx),
+                _lib.ptr(face_vertices_image), b, f, h, w, float(ctx.sigmainv), float(ctx.boxlen), int(ctx.knum),
+                float(ctx.multiplier), _lib.ptr(grad_face_vertices_image), _lib.ptr(ws), nbytes,
+                _lib.current_stream(dev))
+        _lib.check(code, fn)
+        return grad_face_vertices_image, None, None, None, None, None
+
+
+def dibr_soft_mask(face_vertices_image, selected_face_idx,
+                   sigmainv=7000, boxlen=0.02, knum=30, multiplier=1000.):
+    r"""Soft foreground mask of DIB-R (reference: kaolin/render/mesh/dibr.py:75-117).
+
+    Args:
+        face_vertices_image (torch.Tensor): 2D positions of the face vertices in [-1, 1], (B, F, 3, 2).
+        selected_face_idx (torch.LongTensor): rendered face index (B, H, W), 2nd output of ``rasterize``.
+        sigmainv (float): smoothness term, the higher the sharper. Default: 7000.
+        boxlen (float): margin over the face bounding boxes deciding which pixels a face influences. Default: 0.02.
+        knum (int): maximum number of faces influencing one pixel. Default: 30.
+        multiplier (float): internal enlargement of the 2D coordinates. Default: 1000.
+    Returns:
+        (torch.FloatTensor): the soft mask, (B, H, W).
+    """
+    return DibrSoftMaskCuda.apply(face_vertices_image, selected_face_idx,
+                                  sigmainv, boxlen, knum, multiplier)
+
+
+def dibr_rasterization(height, width, face_vertices_z, face_vertices_image,
+                       face_features, face_normals_z, sigmainv=7000,
+                       boxlen=0.02, knum=30, multiplier=None, eps=None,
+                       rast_backend='cuda'):
+    r"""DIB-R renderer: feature images, soft masks and face index maps
+    (reference: kaolin/render/mesh/dibr.py:119-209; only faces with ``face_normals_z >= 0`` are drawn).
+
+    Returns:
+        (features (B,H,W,C) or tuple of tensors, soft_mask (B,H,W), face_idx (B,H,W) int64, -1 = none)
+    """
+    interpolated_features, face_idx = rasterize(
+        height, width,
+        face_vertices_z,
+        face_vertices_image,
+        face_features,
+        face_normals_z >= 0.,
+        multiplier,
+        eps,
+        rast_backend
+    )
+    _multiplier = 1000. if multiplier is None else multiplier
+    soft_mask = dibr_soft_mask(
+        face_vertices_image,
+        face_idx,
+        sigmainv,
+        boxlen,
+        knum,
+        _multiplier
+    )
+    return interpolated_features, soft_mask, face_idx

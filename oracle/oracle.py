@@ -150,9 +150,24 @@ OracleC = types.SimpleNamespace(render=types.SimpleNamespace(mesh=_mesh))
 
 
 # ------------------------------------------------------------------ torch glue restated on CPU
+def load_ref_C():
+    """The reference's own CUDA ops built by oracle/build.py (oracle/_ref/ref_C.so); None if absent."""
+    import importlib.util
+    path = os.path.join(_HERE, "_ref", "ref_C.so")
+    if not os.path.exists(path):
+        return None
+    spec = importlib.util.spec_from_file_location("ref_C", path)
+    mod = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(mod)
+    return mod
+
+
 def rasterize_forward(height, width, face_vertices_z, face_vertices_image, face_features,
-                      valid_faces=None, multiplier=None, eps=None, rows=None):
-    """RasterizeCuda.forward, rasterization.py:290-369 (returns features, face_idx, weights)."""
+                      valid_faces=None, multiplier=None, eps=None, rows=None, backend=None):
+    """RasterizeCuda.forward, rasterization.py:290-369 (returns features, face_idx, weights).
+    ``backend`` = an object with ``render.mesh.packed_rasterize_forward_cuda`` (default: the C++ oracle;
+    pass ``load_ref_C()`` with CUDA tensors to run the reference's own kernels through the same glue)."""
+    dev = face_vertices_z.device
     multiplier = 1000 if multiplier is None else multiplier       # rasterization.py:469-475
     eps = 1e-8 if eps is None else eps
     if isinstance(face_features, (list, tuple)):
@@ -162,27 +177,32 @@ def rasterize_forward(height, width, face_vertices_z, face_vertices_image, face_
     face_features = face_features.contiguous()
     face_vertices_image = face_vertices_image.contiguous()
     if valid_faces is None:                                        # :309-323
-        vi = (torch.arange(b).reshape(-1, 1).repeat(1, f).reshape(-1),
-              torch.arange(f).reshape(1, -1).repeat(b, 1).reshape(-1))
+        vi = (torch.arange(b, device=dev).reshape(-1, 1).repeat(1, f).reshape(-1),
+              torch.arange(f, device=dev).reshape(1, -1).repeat(b, 1).reshape(-1))
         v_img = face_vertices_image.reshape(b * f, 3, 2)
         v_z = face_vertices_z.reshape(b * f, 3)
         v_feat = face_features.reshape(b * f, 3, c)
-        nfm = torch.full((b,), f, dtype=torch.long)
+        nfm = torch.full((b,), f, dtype=torch.long, device=dev)
     else:                                                          # :324-332
         vi = torch.where(valid_faces)
         v_img = face_vertices_image[vi[0], vi[1]]
         v_z = face_vertices_z[vi[0], vi[1]]
         v_feat = face_features[vi[0], vi[1]]
         nfm = torch.sum(valid_faces.reshape(b, -1), dim=1)
-    first = torch.zeros(b + 1, dtype=torch.long)                   # :333-334
+    first = torch.zeros(b + 1, dtype=torch.long, device=dev)       # :333-334
     torch.cumsum(nfm, dim=0, out=first[1:])
     v_img = v_img * multiplier                                     # :337
     pmin = torch.min(v_img, dim=1)[0]                              # :342-344
     pmax = torch.max(v_img, dim=1)[0]
     bboxes = torch.cat((pmin, pmax), dim=1)
-    feat, sel, w = packed_rasterize_forward_cuda(
-        height, width, v_z.contiguous(), v_img.contiguous(), bboxes.contiguous(),
-        v_feat.contiguous(), first.contiguous(), multiplier, eps, rows=rows)
+    if backend is None:
+        feat, sel, w = packed_rasterize_forward_cuda(
+            height, width, v_z.contiguous(), v_img.contiguous(), bboxes.contiguous(),
+            v_feat.contiguous(), first.contiguous(), multiplier, eps, rows=rows)
+    else:
+        feat, sel, w = backend.render.mesh.packed_rasterize_forward_cuda(
+            height, width, v_z.contiguous(), v_img.contiguous(), bboxes.contiguous(),
+            v_feat.contiguous(), first.contiguous(), multiplier, eps)
     if vi[1].numel() > 0:                                          # :357-363
         face_idx = vi[1][(sel + first[:-1].reshape(-1, 1, 1)).reshape(-1).clamp(min=0, max=vi[1].numel() - 1)]
         face_idx = face_idx.reshape(sel.shape).contiguous()
@@ -193,11 +213,15 @@ def rasterize_forward(height, width, face_vertices_z, face_vertices_image, face_
 
 
 def rasterize_backward(grad_features, face_idx, weights, face_vertices_image, face_features, eps=None,
-                       rows=None):
+                       rows=None, backend=None, interpolated_features=None):
     """RasterizeCuda.backward, rasterization.py:371-388."""
     eps = 1e-8 if eps is None else eps
     if isinstance(face_features, (list, tuple)):
         face_features = torch.cat(face_features, dim=-1)
+    if backend is not None:
+        return backend.render.mesh.rasterize_backward_cuda(
+            grad_features.contiguous(), interpolated_features, face_idx, weights,
+            face_vertices_image.contiguous(), face_features.contiguous(), eps)
     return rasterize_backward_cuda(grad_features.contiguous(), None, face_idx, weights,
                                    face_vertices_image.contiguous(), face_features.contiguous(), eps,
                                    rows=rows)
@@ -213,9 +237,13 @@ def soft_mask_bboxes(face_vertices_image, boxlen, multiplier):
 
 
 def dibr_soft_mask_forward(face_vertices_image, selected_face_idx, sigmainv=7000, boxlen=0.02, knum=30,
-                           multiplier=1000., rows=None, side_buffers=True):
+                           multiplier=1000., rows=None, side_buffers=True, backend=None):
     """DibrSoftMaskCuda.forward, dibr.py:29-55.  Returns (soft, multiplied img, prob, idx, type)."""
     img, bb = soft_mask_bboxes(face_vertices_image, boxlen, multiplier)
+    if backend is not None:
+        soft, prob, cidx, ctype = backend.render.mesh.dibr_soft_mask_forward_cuda(
+            img, bb, selected_face_idx.contiguous(), sigmainv, knum, multiplier)
+        return soft, img, prob, cidx, ctype
     soft, prob, cidx, ctype = dibr_soft_mask_forward_cuda(
         img, bb, selected_face_idx.contiguous(), sigmainv, knum, multiplier, rows=rows,
         side_buffers=side_buffers)
@@ -223,8 +251,11 @@ def dibr_soft_mask_forward(face_vertices_image, selected_face_idx, sigmainv=7000
 
 
 def dibr_soft_mask_backward(grad_soft, soft, img_mult, selected_face_idx, prob, cidx, ctype, sigmainv,
-                            multiplier, rows=None):
+                            multiplier, rows=None, backend=None):
     """DibrSoftMaskCuda.backward, dibr.py:57-73."""
+    if backend is not None:
+        return backend.render.mesh.dibr_soft_mask_backward_cuda(
+            grad_soft.contiguous(), soft, selected_face_idx, prob, cidx, ctype, img_mult, sigmainv, multiplier)
     return dibr_soft_mask_backward_cuda(grad_soft.contiguous(), soft, selected_face_idx, prob, cidx,
                                         ctype, img_mult, sigmainv, multiplier, rows=rows)
 

@@ -1,0 +1,247 @@
+"""GPU parity against (1) the reference's own CUDA kernels (ref_C) and (2) the C++ oracle, on synthetic
+workloads of BASELINE.json `configs`, random soups and edge cases.  All calls go through the C-ABI.
+
+Tolerances (BASELINE.json north_star): face_idx bit-exact; features 1e-5 relative; soft mask and gradients
+1e-4 relative."""
+import math
+
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module")
+def kal():
+    import kaolin_b200
+    return kaolin_b200
+
+
+@pytest.fixture(scope="module")
+def O():
+    from oracle import oracle
+    return oracle
+
+
+@pytest.fixture(scope="module")
+def ref_C(O):
+    m = O.load_ref_C()
+    if m is None:
+        pytest.skip("oracle/_ref/ref_C.so not built")
+    return m
+
+
+def rel_close(a, b, rel, name=""):
+    a, b = a.double(), b.double()
+    if b.numel() == 0:
+        assert a.numel() == 0
+        return
+    scale = max(1.0, float(b.abs().max()))
+    err = float((a - b).abs().max())
+    assert err <= rel * scale, f"{name}: max abs err {err:.3e} > {rel} * {scale:.3e}"
+
+
+def to_dev(d, dtype=torch.float32):
+    out = dict(d)
+    out["face_vertices_z"] = d["face_vertices_z"].to("cuda", dtype)
+    out["face_vertices_image"] = d["face_vertices_image"].to("cuda", dtype)
+    out["face_features"] = [f.to("cuda", dtype) for f in d["face_features"]]
+    out["face_normals_z"] = None if d["face_normals_z"] is None else d["face_normals_z"].to("cuda", dtype)
+    return out
+
+
+def full_pipeline_check(kal, O, backend, d, knum=30, boxlen=0.02, sigmainv=7000., multiplier=1000., eps=1e-8,
+                        check_side_buffers=True, grad_rel=1e-4):
+    """Forward + backward of rasterize and dibr_soft_mask vs `backend` (ref_C on GPU tensors, or the CPU
+    oracle when backend is None) on identical inputs."""
+    Hh, Ww = d["H"], d["W"]
+    z, img = d["face_vertices_z"], d["face_vertices_image"]
+    feats = torch.cat(d["face_features"], -1).contiguous()
+    valid = None if d["face_normals_z"] is None else (d["face_normals_z"] >= 0.)
+    img_l = img.clone().requires_grad_(True)
+    feats_l = feats.clone().requires_grad_(True)
+    out_feat, face_idx = kal.render.mesh.rasterize(Hh, Ww, z, img_l, feats_l, valid, multiplier, eps)
+    soft = kal.render.mesh.dibr_soft_mask(img_l, face_idx, sigmainv, boxlen, knum, multiplier)
+    g = torch.Generator(device="cpu").manual_seed(77)
+    g_feat = torch.rand(out_feat.shape, generator=g, dtype=torch.float64).to(out_feat)
+    g_soft = torch.rand(soft.shape, generator=g, dtype=torch.float64).to(soft)
+    # ---- reference
+    cpu = backend is None
+    mv = (lambda t: t.detach().cpu()) if cpu else (lambda t: t.detach())
+    r_feat, r_idx, r_w = O.rasterize_forward(Hh, Ww, mv(z), mv(img), mv(feats), None if valid is None else mv(valid),
+                                             multiplier, eps, backend=backend)
+    r_soft, r_img_m, r_prob, r_cidx, r_ctype = O.dibr_soft_mask_forward(mv(img), r_idx, sigmainv, boxlen, knum,
+                                                                         multiplier, backend=backend)
+    assert torch.equal(face_idx.cpu(), r_idx.cpu()), \
+        f"face_idx mismatch on {(face_idx.cpu() != r_idx.cpu()).sum().item()} pixels"
+    rel_close(out_feat.cpu(), r_feat.cpu(), 1e-5, "features")
+    rel_close(soft.cpu(), r_soft.cpu(), 1e-4, "soft_mask")
+    # ---- backward: raster and soft-mask gradients separately, then through autograd together
+    r_gi, r_gf = O.rasterize_backward(mv(g_feat), r_idx, r_w, mv(img), mv(feats), eps, backend=backend,
+                                      interpolated_features=r_feat)
+    r_gs = O.dibr_soft_mask_backward(mv(g_soft), r_soft, r_img_m, r_idx, r_prob, r_cidx, r_ctype, sigmainv,
+                                     multiplier, backend=backend)
+    (gi_r, gf_r) = torch.autograd.grad(out_feat, (img_l, feats_l), g_feat, retain_graph=True)
+    (gi_s,) = torch.autograd.grad(soft, (img_l,), g_soft, retain_graph=True)
+    rel_close(gf_r.cpu(), r_gf.cpu(), grad_rel, "grad_face_features")
+    rel_close(gi_r.cpu(), r_gi.cpu(), grad_rel, "grad_face_vertices_image (raster)")
+    rel_close(gi_s.cpu(), r_gs.cpu(), grad_rel, "grad_face_vertices_image (soft mask)")
+    if check_side_buffers:
+        img_m = (img * multiplier).contiguous()
+        pmin, pmax = img_m.min(dim=-2)[0], img_m.max(dim=-2)[0]
+        bb = torch.cat([pmin - boxlen * multiplier, pmax + boxlen * multiplier], -1).contiguous()
+        s2, p2, c2, t2 = kal._C.render.mesh.dibr_soft_mask_forward_cuda(img_m, bb, face_idx, sigmainv, knum, multiplier)
+        assert torch.equal(s2, soft)
+        assert torch.equal(c2.cpu(), r_cidx.cpu()), "close_face_idx mismatch"
+        rel_close(p2.cpu(), r_prob.cpu(), 1e-5, "close_face_prob")
+        mism = (t2.cpu() != r_ctype.cpu()).float().mean().item()
+        assert mism <= (0.0 if not cpu else 0.01), f"dist_type mismatch fraction {mism}"
+    return face_idx, soft
+
+
+# ----------------------------------------------------------------------------- vs ref_C (same GPU)
+def test_c1_vs_ref_C(kal, O, ref_C):
+    """config 1: icosphere 1280 faces, B=1, 256x256, C=3, culling."""
+    from kaolin_b200 import synth
+    full_pipeline_check(kal, O, ref_C, to_dev(synth.make_inputs("c1")))
+
+
+def test_c2_vs_ref_C(kal, O, ref_C):
+    """config 2 at full size: 20k-face soups, B=16, 512x512, C=9, no culling."""
+    from kaolin_b200 import synth
+    full_pipeline_check(kal, O, ref_C, to_dev(synth.make_inputs("c2")))
+
+
+def test_c3_two_views_vs_ref_C(kal, O, ref_C):
+    """config 3 shape (100k faces, 1024x1024) on 2 of the 64 views — the brute-force reference needs
+    ~1e11 pixel-face tests per view."""
+    from kaolin_b200 import synth
+    full_pipeline_check(kal, O, ref_C, to_dev(synth.make_inputs("c3", batch=2, views=[0, 37])))
+
+
+def test_c1_double_vs_ref_C(kal, O, ref_C):
+    from kaolin_b200 import synth
+    full_pipeline_check(kal, O, ref_C, to_dev(synth.make_inputs("c1"), torch.float64), grad_rel=1e-9)
+
+
+def random_soup(B, F, scale, seed, dtype=torch.float32):
+    g = torch.Generator().manual_seed(seed)
+    ctr = torch.rand(B, F, 1, 2, generator=g) * 2.2 - 1.1          # some faces off-screen
+    img = ctr + (torch.rand(B, F, 3, 2, generator=g) - 0.5) * scale
+    z = -1.0 - 2 * torch.rand(B, F, 3, generator=g)
+    feat = torch.rand(B, F, 3, 4, generator=g)
+    nz = torch.rand(B, F, generator=g) - 0.3
+    return dict(face_vertices_z=z.to("cuda", dtype), face_vertices_image=img.to("cuda", dtype),
+                face_features=[feat.to("cuda", dtype)], face_normals_z=nz.to("cuda", dtype))
+
+
+@pytest.mark.parametrize("Hh,Ww", [(64, 64), (37, 53), (16, 240), (1, 1), (130, 17)])
+@pytest.mark.parametrize("scale", [0.05, 0.6, 3.0])
+def test_random_soups_vs_ref_C(kal, O, ref_C, Hh, Ww, scale):
+    """ragged image sizes (not multiples of the 16x16 tile), tiny to screen-filling faces (the latter
+    exercise the 'large face' lists), valid_faces masks, knum truncation (knum=5)."""
+    if Hh * Ww * 3 < 512:
+        pytest.skip("reference backward launches 0 blocks when B*H*W < 512 (rasterization_cuda.cu:422-424)")
+    d = random_soup(3, 300, scale, seed=Hh * 1000 + Ww)
+    d.update(H=Hh, W=Ww)
+    full_pipeline_check(kal, O, ref_C, d, knum=5, boxlen=0.05)
+
+
+# ----------------------------------------------------------------------------- vs the C++ oracle
+@pytest.mark.parametrize("dtype", [torch.float32, torch.float64])
+def test_random_soup_vs_oracle_bit_exact(kal, O, dtype):
+    """face_idx AND barycentric weights bit-exact against the CPU restatement (fp32 and fp64)."""
+    d = random_soup(2, 500, 0.4, seed=5, dtype=dtype)
+    Hh, Ww = 48, 40
+    z, img, feat = d["face_vertices_z"], d["face_vertices_image"], d["face_features"][0]
+    valid = d["face_normals_z"] >= 0
+    o_feat, o_idx, o_w = O.rasterize_forward(Hh, Ww, z.cpu(), img.cpu(), feat.cpu(), valid.cpu())
+    img_m = (img * 1000).contiguous()
+    # reference-shaped packed entry point (valid faces packed by the caller, as RasterizeCuda.forward does)
+    vi = torch.where(valid)
+    first = torch.zeros(3, dtype=torch.long, device="cuda")
+    first[1:] = torch.cumsum(valid.sum(1), 0)
+    v_img = img_m[vi[0], vi[1]].contiguous()
+    bb = torch.cat([v_img.min(1)[0], v_img.max(1)[0]], 1).contiguous()
+    p_feat, p_sel, p_w = kal._C.render.mesh.packed_rasterize_forward_cuda(
+        Hh, Ww, z[vi[0], vi[1]].contiguous(), v_img, bb, feat[vi[0], vi[1]].contiguous(), first, 1000, 1e-8)
+    f_feat, f_idx = kal.render.mesh.rasterize(Hh, Ww, z, img, feat, valid)
+    assert torch.equal(f_idx.cpu(), o_idx)
+    assert torch.equal(p_w.cpu(), o_w), "barycentric weights not bit-exact"
+    assert torch.equal(f_feat.cpu(), o_feat) and torch.equal(p_feat.cpu(), o_feat)
+    # packed-local index -> original index (rasterization.py:357-363)
+    mapped = vi[1][(p_sel + first[:-1].reshape(-1, 1, 1)).reshape(-1).clamp(min=0)].reshape(p_sel.shape)
+    mapped[p_sel == -1] = -1
+    assert torch.equal(mapped, f_idx)
+
+
+def test_small_image_backward_works(kal, O):
+    """B*H*W < 512: the reference launch fails (floor-division grid); the replacement simply works."""
+    d = random_soup(1, 50, 0.8, seed=9)
+    z, img, feat = d["face_vertices_z"], d["face_vertices_image"].requires_grad_(True), d["face_features"][0]
+    out, idx = kal.render.mesh.rasterize(8, 8, z, img, feat)
+    g = torch.rand_like(out)
+    out.backward(g)
+    o_feat, o_idx, o_w = O.rasterize_forward(8, 8, z.cpu(), img.detach().cpu(), feat.cpu())
+    o_gi, o_gf = O.rasterize_backward(g.cpu(), o_idx, o_w, img.detach().cpu(), feat.cpu())
+    assert torch.equal(idx.cpu(), o_idx)
+    rel_close(img.grad.cpu(), o_gi, 1e-4, "grad img")
+
+
+def test_edge_cases(kal, O):
+    dev = "cuda"
+    # no faces at all
+    z = torch.zeros(2, 0, 3, device=dev); img = torch.zeros(2, 0, 3, 2, device=dev); feat = torch.zeros(2, 0, 3, 3, device=dev)
+    out, idx = kal.render.mesh.rasterize(20, 30, z, img, feat)
+    assert out.shape == (2, 20, 30, 3) and torch.all(out == 0) and torch.all(idx == -1)
+    soft = kal.render.mesh.dibr_soft_mask(img, idx)
+    assert torch.all(soft == 0)
+    # all faces invalid
+    d = random_soup(2, 40, 0.5, seed=3)
+    out, idx = kal.render.mesh.rasterize(33, 33, d["face_vertices_z"], d["face_vertices_image"], d["face_features"][0],
+                                         torch.zeros(2, 40, dtype=torch.bool, device=dev))
+    assert torch.all(idx == -1) and torch.all(out == 0)
+    # degenerate (zero-area) and duplicated faces: lowest index wins exact depth ties
+    img = torch.tensor([[[[-.5, -.5], [.5, -.5], [0., .5]]]], device=dev).repeat(1, 4, 1, 1)
+    img[0, 3] = 0.25                                          # zero-area face
+    z = torch.full((1, 4, 3), -2., device=dev)
+    feat = torch.arange(4, device=dev, dtype=torch.float32).view(1, 4, 1, 1).expand(1, 4, 3, 1).contiguous()
+    out, idx = kal.render.mesh.rasterize(32, 32, z, img, feat)
+    o_feat, o_idx, _ = O.rasterize_forward(32, 32, z.cpu(), img.cpu(), feat.cpu())
+    assert torch.equal(idx.cpu(), o_idx) and int(idx.max()) == 0
+    # NaN / inf depths and coordinates follow the reference's in-order semantics
+    d = random_soup(1, 60, 0.7, seed=11)
+    z = d["face_vertices_z"].clone(); img = d["face_vertices_image"].clone()
+    z[0, 7, 1] = float("nan"); z[0, 20] = float("inf"); z[0, 31] = -float("inf"); img[0, 44, 2, 0] = float("nan")
+    out, idx = kal.render.mesh.rasterize(40, 40, z, img, d["face_features"][0])
+    o_feat, o_idx, _ = O.rasterize_forward(40, 40, z.cpu(), img.cpu(), d["face_features"][0].cpu())
+    assert torch.equal(idx.cpu(), o_idx)
+
+
+def test_error_behaviour(kal):
+    z = torch.zeros(1, 2, 3); img = torch.zeros(1, 2, 3, 2); feat = torch.zeros(1, 2, 3, 1)
+    with pytest.raises(RuntimeError):
+        kal.render.mesh.rasterize(8, 8, z, img, feat)                    # CPU tensors -> RuntimeError
+    with pytest.raises(ValueError):
+        kal.render.mesh.rasterize(8, 8, z.cuda(), img.cuda(), feat.cuda(), backend="opengl")
+    with pytest.raises(ValueError):
+        kal.render.mesh.rasterize(8, 8, z.cuda(), img.cuda(), feat.cuda(), backend="nvdiffrast")
+    with pytest.raises(RuntimeError):
+        kal.render.mesh.rasterize(8, 8, z.cuda().half(), img.cuda().half(), feat.cuda().half())
+    with pytest.raises(RuntimeError):
+        kal._C.render.mesh.dibr_soft_mask_forward_cuda(img.cuda()[:, :, :, :1], torch.zeros(1, 2, 4).cuda(),
+                                                        torch.zeros(1, 8, 8, dtype=torch.long).cuda(), 7000, 30, 1000)
+    with pytest.warns(UserWarning):
+        try:
+            kal.render.mesh.rasterize(8, 8, z.cuda(), img.cuda(), feat.cuda(), multiplier=100, backend="nvdiffrast")
+        except ValueError:
+            pass
+
+
+def test_knum_truncation_dense(kal, O, ref_C):
+    """many faces around uncovered pixels: the first `knum` faces BY INDEX are kept (order semantics)."""
+    from kaolin_b200 import synth
+    d = to_dev(synth.make_inputs("c2", batch=1))
+    d["face_vertices_image"] = (d["face_vertices_image"] * 0.5).contiguous()     # crowd the centre, empty border
+    for knum in (1, 7, 30):
+        full_pipeline_check(kal, O, ref_C, d, knum=knum, boxlen=0.05)
