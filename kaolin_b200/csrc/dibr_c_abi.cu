@@ -33,17 +33,23 @@ inline int cuda_fail(cudaError_t e, const char* where) {
     if (_e != cudaSuccess) return cuda_fail(_e, name);      \
   } while (0)
 
-// Optional per-kernel timing hook (bench.py's roofline leg): the calling thread names ONE kernel id and a
-// pair of CUDA events; the next launch of that kernel on this thread is bracketed by the two events on
+// Optional per-kernel timing hook (bench.py's roofline leg): the caller names ONE kernel id and a
+// pair of CUDA events; the next launch of that kernel (from any thread) is bracketed by the two events on
 // the launch stream.  Off by default; costs nothing when unset.
-thread_local int t_prof_kernel = -1;
-thread_local cudaEvent_t t_prof_start = nullptr, t_prof_stop = nullptr;
+// Process-wide (forward runs on the Python thread, backward on the autograd thread); measurement only.
+std::atomic<int> g_prof_kernel{-1};
+std::atomic<cudaEvent_t> g_prof_start{nullptr}, g_prof_stop{nullptr};
 struct ProfScope {
   bool on; cudaStream_t s;
-  ProfScope(int id, cudaStream_t st) : on(id == t_prof_kernel && t_prof_start), s(st) {
-    if (on) cudaEventRecord(t_prof_start, s);
+  ProfScope(int id, cudaStream_t st) : on(false), s(st) {
+    int expect = id;
+    if (g_prof_kernel.load(std::memory_order_acquire) == id &&
+        g_prof_kernel.compare_exchange_strong(expect, -2)) {          // claim it (one launch only)
+      on = true;
+      cudaEventRecord(g_prof_start.load(), s);
+    }
   }
-  ~ProfScope() { if (on) { cudaEventRecord(t_prof_stop, s); t_prof_kernel = -1; } }
+  ~ProfScope() { if (on) { cudaEventRecord(g_prof_stop.load(), s); g_prof_kernel.store(-1, std::memory_order_release); } }
 };
 
 inline size_t align_up(size_t v, size_t a = 256) { return (v + a - 1) / a * a; }
@@ -206,8 +212,9 @@ int soft_mask_impl(const T* img, const T* bbox_in, const int64_t* face_idx, int 
   p.sigmainv = sigmainv; p.F = F; p.knum = knum; p.face_idx = face_idx; p.soft = soft; p.prob = prob;
   p.close_idx = close_idx; p.dist_type = dist_type; p.grad_soft = grad_soft; p.soft_in = soft_in;
   p.grad_img = grad_img;
-  const size_t smem = SOFT_CAP * (sizeof(int) + sizeof(uint2));
-  CUDA_TRY(cudaFuncSetAttribute(soft_mask_kernel<T, MODE>, cudaFuncAttributeMaxDynamicSharedMemorySize, 65536));
+  const size_t smem = SoftSmem<T>::total;
+  CUDA_TRY(cudaFuncSetAttribute(soft_mask_kernel<T, MODE>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                (int)smem));
   {
     ProfScope ps(MODE == MODE_FWD ? DIBR_KERNEL_SOFT_FWD : DIBR_KERNEL_SOFT_BWD, s);
     soft_mask_kernel<T, MODE><<<(unsigned)(B * geo.tiles_per_view), 256, smem, s>>>(p, fl, geo, L);
@@ -259,9 +266,9 @@ DIBR_API uint64_t dibr_kernel_launch_count(void) { return g_launches.load(std::m
 DIBR_API void dibr_reset_kernel_launch_count(void) { g_launches.store(0, std::memory_order_relaxed); }
 DIBR_API int dibr_profile_next_launch(int kernel_id, void* start_event, void* stop_event) {
   if (kernel_id >= 0 && (!start_event || !stop_event)) return DIBR_ERR_INVALID_ARGUMENT;
-  t_prof_kernel = kernel_id;
-  t_prof_start = static_cast<cudaEvent_t>(start_event);
-  t_prof_stop = static_cast<cudaEvent_t>(stop_event);
+  g_prof_start.store(static_cast<cudaEvent_t>(start_event));
+  g_prof_stop.store(static_cast<cudaEvent_t>(stop_event));
+  g_prof_kernel.store(kernel_id < 0 ? -1 : kernel_id, std::memory_order_release);
   return DIBR_OK;
 }
 

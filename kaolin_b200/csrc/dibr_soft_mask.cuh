@@ -7,6 +7,11 @@
 // `knum` faces in face order whose enlarged bbox contains the pixel (:80-171), so order is semantic —
 // and their pixel ranges are staged next to them.  Each uncovered pixel then walks the sorted list.
 //
+// The walk is split in phases so that the expensive part runs with full lanes even when only a few
+// pixels of the tile are uncovered: (A) compact the uncovered pixels, (B) one warp per pixel builds its
+// k-list with ballot/popc over 32 candidates at a time, (C) all (pixel, k) pairs are evaluated in
+// parallel, (D) one thread per pixel multiplies the probabilities in face order.
+//
 // MODE_FWD writes soft (+ optional k-list side buffers, API-visible through
 // _C.render.mesh.dibr_soft_mask_forward_cuda).  MODE_BWD re-derives the same k-list with the same
 // arithmetic instead of reading 13*knum bytes per pixel of side buffers, and accumulates the vertex
@@ -16,7 +21,7 @@
 
 namespace dibr {
 
-constexpr int SOFT_CAP = 4096;      // candidate faces per tile held in shared memory
+constexpr int SOFT_CAP = 2048;      // candidate faces per tile held in shared memory
 constexpr int MODE_FWD = 0;
 constexpr int MODE_BWD = 1;
 
@@ -103,14 +108,31 @@ __device__ __forceinline__ void soft_visit(const SoftParams<T>& sp, SoftPixel<T,
   ++st.kid;
 }
 
+// Shared-memory plan (dynamic): candidates (ids + ranges), the compacted uncovered pixels, and the
+// per-pixel k-lists of the current pixel chunk (PAIR_CAP (pixel, k) slots).
+constexpr int PAIR_CAP = 6144;
+template <typename T>
+struct SoftSmem {
+  static constexpr size_t ids = 0;
+  static constexpr size_t rng = ids + SOFT_CAP * sizeof(int);
+  static constexpr size_t hit = rng + SOFT_CAP * sizeof(uint2);
+  static constexpr size_t prob = hit + PAIR_CAP * sizeof(int);
+  static constexpr size_t upix = prob + PAIR_CAP * sizeof(T);
+  static constexpr size_t kid = upix + 256 * sizeof(int);
+  static constexpr size_t total = kid + 256 * sizeof(int);
+};
+
 template <typename T, int MODE>
 __global__ void __launch_bounds__(256) soft_mask_kernel(SoftParams<T> sp, FaceLayout fl, Geometry geo,
                                                         BinLists L) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
-  int* s_ids = reinterpret_cast<int*>(smem_raw);                          // [SOFT_CAP]
-  uint2* s_rng = reinterpret_cast<uint2*>(smem_raw + SOFT_CAP * sizeof(int));   // [SOFT_CAP]
+  int* s_ids = reinterpret_cast<int*>(smem_raw + SoftSmem<T>::ids);      // [SOFT_CAP] sorted candidate faces
+  uint2* s_rng = reinterpret_cast<uint2*>(smem_raw + SoftSmem<T>::rng);  // [SOFT_CAP] their pixel ranges
+  int* s_hit = reinterpret_cast<int*>(smem_raw + SoftSmem<T>::hit);      // [PAIR_CAP] k-lists, [u*K + k]
+  T* s_prob = reinterpret_cast<T*>(smem_raw + SoftSmem<T>::prob);        // [PAIR_CAP] forward probabilities
+  int* s_upix = reinterpret_cast<int*>(smem_raw + SoftSmem<T>::upix);    // [256] thread index of uncovered px
+  int* s_kid = reinterpret_cast<int*>(smem_raw + SoftSmem<T>::kid);      // [256] k-list lengths
   __shared__ int scratch[9];
-  __shared__ int s_count;
 
   const int tile = blockIdx.x % geo.tiles_per_view;
   const int b = blockIdx.x / geo.tiles_per_view;
@@ -119,42 +141,34 @@ __global__ void __launch_bounds__(256) soft_mask_kernel(SoftParams<T> sp, FaceLa
   const int py = ty * TILE + (threadIdx.x / TILE);
   const bool in_image = px < geo.W && py < geo.H;
   const int64_t vbase = fl.base(b);
-
-  SoftPixel<T, MODE> st;
-  st.pix = ((int64_t)b * geo.H + py) * geo.W + px;
-  st.kid = 0;
-  st.allprob = (T)1.0;
-  const bool uncovered = in_image && (sp.face_idx[st.pix] < 0);
+  const int64_t pix = ((int64_t)b * geo.H + py) * geo.W + px;
+  const bool uncovered = in_image && (sp.face_idx[pix] < 0);
   const int K = sp.knum;
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
 
   if (MODE == MODE_FWD && in_image && !uncovered) {
-    sp.soft[st.pix] = (T)1.0;                                           // :68-70
+    sp.soft[pix] = (T)1.0;                                              // :68-70
     if (sp.prob) {                                                      // dibr_soft_mask.cpp:86-96 defaults
       for (int k = 0; k < K; ++k) {
-        sp.prob[st.pix * K + k] = (T)0;
-        sp.close_idx[st.pix * K + k] = -1;
-        sp.dist_type[st.pix * K + k] = 0;
+        sp.prob[pix * K + k] = (T)0;
+        sp.close_idx[pix * K + k] = -1;
+        sp.dist_type[pix * K + k] = 0;
       }
     }
   }
-  if (!__syncthreads_or(uncovered)) return;
+  // ---- phase A: compact the uncovered pixels of the tile
+  int U;
+  const int uslot = block_compact_256(uncovered, scratch, U);
+  if (U == 0) return;
+  if (uncovered) s_upix[uslot] = threadIdx.x;
 
-  if (uncovered) {
-    st.x0 = (T)pix_coord(pix_scale(sp.pix_mult, geo.W), geo.W, px);
-    st.y0 = (T)pix_coord(pix_scale(sp.pix_mult, geo.H), geo.H, geo.H - 1 - py);
-    if (MODE == MODE_BWD) {
-      st.dLdp = sp.grad_soft[st.pix];
-      st.soft = sp.soft_in[st.pix];
-    }
-  }
-
-  // ---- gather the candidates
+  // ---- gather the candidates: tile list + filtered large faces
   const int n_tile = L.tile_count[blockIdx.x];
   const int* tile_list = L.pairs + L.tile_offset[blockIdx.x];
   const int n_large = L.large_count[b];
   const int* large_list = L.large_list + vbase;
   const int rx0 = tx * TILE, ry0 = ty * TILE, rx1 = rx0 + TILE - 1, ry1 = ry0 + TILE - 1;
-  bool overflow = n_tile > SOFT_CAP;
+  bool overflow = n_tile > SOFT_CAP || K > PAIR_CAP;
   int count = 0;
   if (!overflow) {
     for (int k = threadIdx.x; k < n_tile; k += 256) s_ids[k] = tile_list[k];
@@ -174,50 +188,115 @@ __global__ void __launch_bounds__(256) soft_mask_kernel(SoftParams<T> sp, FaceLa
     }
   }
 
-  if (!overflow) {
-    // ---- bitonic sort by face index (pad with INT_MAX)
-    int n2 = 1;
-    while (n2 < count) n2 <<= 1;
-    for (int k = count + threadIdx.x; k < n2; k += 256) s_ids[k] = 0x7fffffff;
-    __syncthreads();
-    for (int size = 2; size <= n2; size <<= 1) {
-      for (int stride = size >> 1; stride > 0; stride >>= 1) {
-        for (int t = threadIdx.x; t < (n2 >> 1); t += 256) {
-          const int lo = ((t / stride) * stride * 2) + (t % stride);
-          const int hi = lo + stride;
-          const bool up = ((lo & size) == 0);
-          const int a = s_ids[lo], c = s_ids[hi];
-          if ((a > c) == up) { s_ids[lo] = c; s_ids[hi] = a; }
-        }
-        __syncthreads();
-      }
-    }
-    for (int k = threadIdx.x; k < count; k += 256) s_rng[k] = L.ranges[vbase + s_ids[k]];
-    __syncthreads();
+  if (overflow) {
+    // ---- rare: more candidates than shared memory holds -> the reference's in-order scan over every face
     if (uncovered) {
-      for (int s = 0; s < count && st.kid < K; ++s) {
-        if (!range_hits_pixel(s_rng[s], px, py)) continue;
-        soft_visit<T, MODE>(sp, st, vbase, s_ids[s]);
+      SoftPixel<T, MODE> st;
+      st.pix = pix; st.kid = 0; st.allprob = (T)1.0;
+      st.x0 = (T)pix_coord(pix_scale(sp.pix_mult, geo.W), geo.W, px);
+      st.y0 = (T)pix_coord(pix_scale(sp.pix_mult, geo.H), geo.H, geo.H - 1 - py);
+      if (MODE == MODE_BWD) { st.dLdp = sp.grad_soft[pix]; st.soft = sp.soft_in[pix]; }
+      const int nf = (int)(fl.base(b + 1) - vbase);
+      for (int f = 0; f < nf && st.kid < K; ++f) {
+        if (!range_hits_pixel(L.ranges[vbase + f], px, py)) continue;
+        soft_visit<T, MODE>(sp, st, vbase, f);
+      }
+      if (MODE == MODE_FWD) {
+        sp.soft[pix] = (T)(1.0 - (double)st.allprob);
+        if (sp.prob)
+          for (int k = st.kid; k < K; ++k) {
+            sp.prob[pix * K + k] = (T)0; sp.close_idx[pix * K + k] = -1; sp.dist_type[pix * K + k] = 0;
+          }
       }
     }
-  } else if (uncovered) {
-    // ---- more candidates than shared memory holds: the reference's in-order scan over every face
-    const int nf = (int)(fl.base(b + 1) - vbase);
-    for (int f = 0; f < nf && st.kid < K; ++f) {
-      if (!range_hits_pixel(L.ranges[vbase + f], px, py)) continue;
-      soft_visit<T, MODE>(sp, st, vbase, f);
-    }
+    return;
   }
 
-  if (MODE == MODE_FWD && uncovered) {
-    sp.soft[st.pix] = (T)(1.0 - (double)st.allprob);                    // :181-182
-    if (sp.prob) {
-      for (int k = st.kid; k < K; ++k) {
-        sp.prob[st.pix * K + k] = (T)0;
-        sp.close_idx[st.pix * K + k] = -1;
-        sp.dist_type[st.pix * K + k] = 0;
+  // ---- bitonic sort by face index (pad with INT_MAX); order is semantic (first knum faces in face order)
+  int n2 = 1;
+  while (n2 < count) n2 <<= 1;
+  for (int k = count + threadIdx.x; k < n2; k += 256) s_ids[k] = 0x7fffffff;
+  __syncthreads();
+  for (int size = 2; size <= n2; size <<= 1) {
+    for (int stride = size >> 1; stride > 0; stride >>= 1) {
+      for (int t = threadIdx.x; t < (n2 >> 1); t += 256) {
+        const int lo = ((t / stride) * stride * 2) + (t % stride);
+        const int hi = lo + stride;
+        const bool up = ((lo & size) == 0);
+        const int a = s_ids[lo], c = s_ids[hi];
+        if ((a > c) == up) { s_ids[lo] = c; s_ids[hi] = a; }
+      }
+      __syncthreads();
+    }
+  }
+  for (int k = threadIdx.x; k < count; k += 256) s_rng[k] = L.ranges[vbase + s_ids[k]];
+  __syncthreads();
+
+  const float sx = pix_scale(sp.pix_mult, geo.W), sy = pix_scale(sp.pix_mult, geo.H);
+  const int UC = (K > 0) ? min(256, PAIR_CAP / K) : 256;                // uncovered pixels per chunk
+  for (int u0 = 0; u0 < U; u0 += UC) {
+    const int Uc = min(UC, U - u0);
+    // ---- phase B: one warp per uncovered pixel builds its k-list (first K hits in face order)
+    for (int u = warp; u < Uc; u += 8) {
+      const int t = s_upix[u0 + u];
+      const int qx = tx * TILE + (t & (TILE - 1)), qy = ty * TILE + (t / TILE);
+      int kid = 0;
+      for (int base = 0; base < count && kid < K; base += 32) {
+        const int c = base + lane;
+        const bool hit = c < count && range_hits_pixel(s_rng[c], qx, qy);
+        const unsigned m = __ballot_sync(0xffffffffu, hit);
+        const int r = kid + __popc(m & ((1u << lane) - 1u));
+        if (hit && r < K) s_hit[u * K + r] = s_ids[c];
+        kid = min(K, kid + __popc(m));
+      }
+      if (lane == 0) s_kid[u] = kid;
+    }
+    __syncthreads();
+    // ---- phase C: every (pixel, k) pair in parallel — the expensive distance / probability evaluation
+    for (int idx = threadIdx.x; idx < Uc * K; idx += 256) {
+      const int u = idx / K, k = idx - u * K;
+      if (k >= s_kid[u]) continue;
+      const int t = s_upix[u0 + u];
+      const int qx = tx * TILE + (t & (TILE - 1)), qy = ty * TILE + (t / TILE);
+      const T x0 = (T)pix_coord(sx, geo.W, qx);
+      const T y0 = (T)pix_coord(sy, geo.H, geo.H - 1 - qy);
+      const int f = s_hit[idx];
+      T p[6];
+      load_face_xy<T>(sp.img, vbase + f, sp.coord_mult, sp.premultiplied, p);
+      int edgeid;
+      const T d = soft_distance<T>(p, x0, y0, sp.pix_mult, edgeid);
+      const T prob = soft_prob<T>(d, sp.sigmainv, sp.pix_mult);
+      const int64_t qpix = ((int64_t)b * geo.H + qy) * geo.W + qx;
+      if (MODE == MODE_FWD) {
+        s_prob[idx] = prob;
+        if (sp.prob) {
+          const int64_t o = qpix * K + k;
+          sp.prob[o] = prob; sp.close_idx[o] = (int64_t)f; sp.dist_type[o] = (uint8_t)(edgeid + 1);
+        }
+      } else {
+        soft_backward_pair<T>(p, x0, y0, prob, edgeid, sp.grad_soft[qpix], sp.soft_in[qpix], sp.sigmainv,
+                              sp.pix_mult, sp.grad_img + (vbase + f) * 6);
       }
     }
+    if (MODE == MODE_FWD) {
+      __syncthreads();
+      // ---- phase D: in-order product per pixel (:174-182)
+      if (threadIdx.x < Uc) {
+        const int u = threadIdx.x;
+        const int t = s_upix[u0 + u];
+        const int qx = tx * TILE + (t & (TILE - 1)), qy = ty * TILE + (t / TILE);
+        const int64_t qpix = ((int64_t)b * geo.H + qy) * geo.W + qx;
+        const int kid = s_kid[u];
+        T allprob = (T)1.0;
+        for (int k = 0; k < kid; ++k) allprob = (T)((double)allprob * (1.0 - (double)s_prob[u * K + k]));
+        sp.soft[qpix] = (T)(1.0 - (double)allprob);
+        if (sp.prob)
+          for (int k = kid; k < K; ++k) {
+            sp.prob[qpix * K + k] = (T)0; sp.close_idx[qpix * K + k] = -1; sp.dist_type[qpix * K + k] = 0;
+          }
+      }
+    }
+    __syncthreads();
   }
 }
 
