@@ -161,29 +161,33 @@ def gpu_run(args):
     # pinned host copies (the e2e leg copies these every step) and resident device copies (the `value` leg)
     h_z = d["face_vertices_z"].pin_memory()
     h_img = d["face_vertices_image"].pin_memory()
-    h_feat = torch.cat(d["face_features"], -1).contiguous().pin_memory()
+    h_feat = [f.contiguous().pin_memory() for f in d["face_features"]]
     h_nz = None if d["face_normals_z"] is None else d["face_normals_z"].pin_memory()
-    B, F, C = h_z.shape[0], h_z.shape[1], h_feat.shape[-1]
+    B, F, C = h_z.shape[0], h_z.shape[1], sum(f.shape[-1] for f in h_feat)
     P = B * H * W
     splits = [f.shape[-1] for f in d["face_features"]]
     g = torch.Generator().manual_seed(4242 + rank)
-    g_feat = torch.rand(B, H, W, C, generator=g).to(dev)
+    g_feats = [torch.rand(B, H, W, c, generator=g).to(dev) for c in splits]
     g_soft = torch.rand(B, H, W, generator=g).to(dev)
-    d_z, d_img, d_feat = h_z.to(dev), h_img.to(dev), h_feat.to(dev)
+    d_z, d_img, d_feat = h_z.to(dev), h_img.to(dev), [f.to(dev) for f in h_feat]
     d_nz = None if h_nz is None else h_nz.to(dev)
     flush = torch.empty(512 * 1024 * 1024, dtype=torch.uint8, device=dev)     # > 126 MB L2
 
     def step(z, img, feat, nz, loss=False):
         img = img.detach().requires_grad_(True)
-        feat = feat.detach().requires_grad_(True)
-        feats = list(torch.split(feat, splits, dim=-1)) if len(splits) > 1 else feat
+        if isinstance(feat, list):
+            feats = [f.detach().requires_grad_(True) for f in feat]
+            feats = feats if len(feats) > 1 else feats[0]
+        else:
+            feats = feat.detach().requires_grad_(True)
         valid = None if nz is None else (nz >= 0.)
         out, face_idx = kal.render.mesh.rasterize(H, W, z, img, feats, valid, d["multiplier"], d["eps"])
         soft = kal.render.mesh.dibr_soft_mask(img, face_idx, d["sigmainv"], d["boxlen"], d["knum"], d["multiplier"])
-        out = torch.cat(out, -1) if isinstance(out, tuple) else out
-        torch.autograd.backward([out, soft], [g_feat, g_soft])
+        outs = list(out) if isinstance(out, tuple) else [out]
+        torch.autograd.backward(outs + [soft], g_feats + [g_soft])
         if loss:
-            return (img.grad.sum() + feat.grad.sum() + soft.sum()).reshape(1)
+            fl = feats if isinstance(feats, list) else [feats]
+            return (img.grad.sum() + sum(f.grad.sum() for f in fl) + soft.sum()).reshape(1)
         return None
 
     def barrier():
@@ -221,10 +225,12 @@ def gpu_run(args):
     h_loss = torch.zeros(1).pin_memory()
 
     def e2e_step():
-        z, img, feat = h_z.to(dev, non_blocking=True), h_img.to(dev, non_blocking=True), h_feat.to(dev, non_blocking=True)
+        z, img = h_z.to(dev, non_blocking=True), h_img.to(dev, non_blocking=True)
+        feat = [f.to(dev, non_blocking=True) for f in h_feat]
         nz = None if h_nz is None else h_nz.to(dev, non_blocking=True)
         h_loss.copy_(step(z, img, feat, nz, loss=True), non_blocking=True)
-    h2d = h_z.numel() * 4 + h_img.numel() * 4 + h_feat.numel() * 4 + (0 if h_nz is None else h_nz.numel() * 4)
+    h2d = h_z.numel() * 4 + h_img.numel() * 4 + sum(f.numel() for f in h_feat) * 4 + \
+        (0 if h_nz is None else h_nz.numel() * 4)
 
     # ---- warm-up (also: which kernel dominates?)
     for _ in range(max(args.warmup, 3)):

@@ -111,6 +111,32 @@ int dibr_rasterize_backward_f64(const double* grad_out, const int64_t* face_idx,
                                 double multiplier, float eps, double* grad_img, double* grad_feat, void* stream);
 
 /* ---------------------------------------------------------------------------------------------
+ * List-of-features variants.  `rasterize(face_features=[t0, t1, ...])` of the reference concatenates the
+ * list (rasterization.py:480-481) and slices the output (:499-505); these entry points consume the n_feat
+ * tensors in place and write n_feat separate outputs, so neither the concatenation nor autograd's
+ * slice-backward (zero-fill + copy + add per tensor) ever runs.  `feats`, `out_feats`, `grad_outs`,
+ * `grad_feats` are HOST arrays of n_feat device pointers, `channels` a HOST array of n_feat ints
+ * (n_feat <= 8); tensor t has shape (B,F,3,channels[t]) / (B,H,W,channels[t]).
+ */
+int dibr_rasterize_fwd_multi_f32(const float* z, const float* img, const float* const* feats, const int* channels,
+                                 int n_feat, const uint8_t* valid, int B, int F, int H, int W, double multiplier,
+                                 float eps, float* const* out_feats, int64_t* out_face_idx, float* out_weights,
+                                 void* ws, size_t ws_bytes, void* stream);
+int dibr_rasterize_fwd_multi_f64(const double* z, const double* img, const double* const* feats,
+                                 const int* channels, int n_feat, const uint8_t* valid, int B, int F, int H, int W,
+                                 double multiplier, float eps, double* const* out_feats, int64_t* out_face_idx,
+                                 double* out_weights, void* ws, size_t ws_bytes, void* stream);
+int dibr_rasterize_backward_multi_f32(const float* const* grad_outs, const int64_t* face_idx, const float* weights,
+                                      const float* img, const float* const* feats, const int* channels, int n_feat,
+                                      int B, int F, int H, int W, double multiplier, float eps, float* grad_img,
+                                      float* const* grad_feats, void* stream);
+int dibr_rasterize_backward_multi_f64(const double* const* grad_outs, const int64_t* face_idx,
+                                      const double* weights, const double* img, const double* const* feats,
+                                      const int* channels, int n_feat, int B, int F, int H, int W,
+                                      double multiplier, float eps, double* grad_img, double* const* grad_feats,
+                                      void* stream);
+
+/* ---------------------------------------------------------------------------------------------
  * dibr_soft_mask forward.
  *  _fused   : replaces DibrSoftMaskCuda.forward (dibr.py:29-55): x multiplier, enlarged bboxes, kernel.
  *             img (B,F,3,2) NOT multiplied.

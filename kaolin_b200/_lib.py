@@ -33,6 +33,8 @@ _TYPED = {
     "dibr_packed_rasterize_forward": [c_i, c_i, c_p, c_p, c_p, c_p, c_p, c_i, c_i64, c_i, c_f, c_f, c_p, c_p, c_p,
                                       c_p, c_sz, c_p],
     "dibr_rasterize_backward": [c_p, c_p, c_p, c_p, c_p, c_i, c_i, c_i, c_i, c_i, c_d, c_f, c_p, c_p, c_p],
+    "dibr_rasterize_fwd_multi": [c_p, c_p, c_p, c_p, c_i, c_p, c_i, c_i, c_i, c_i, c_d, c_f, c_p, c_p, c_p, c_p, c_sz, c_p],
+    "dibr_rasterize_backward_multi": [c_p, c_p, c_p, c_p, c_p, c_p, c_i, c_i, c_i, c_i, c_i, c_d, c_f, c_p, c_p, c_p],
     "dibr_soft_mask_fwd_fused": [c_p, c_p, c_i, c_i, c_i, c_i, c_f, c_d, c_i, c_d, c_p, c_p, c_p, c_p, c_p, c_sz, c_p],
     "dibr_soft_mask_forward": [c_p, c_p, c_p, c_i, c_i, c_i, c_i, c_f, c_i, c_f, c_p, c_p, c_p, c_p, c_p, c_sz, c_p],
     "dibr_soft_mask_backward": [c_p, c_p, c_p, c_p, c_p, c_p, c_p, c_i, c_i, c_i, c_i, c_i, c_f, c_f, c_p, c_p],
@@ -120,6 +122,15 @@ def suffix(dtype, func_name):
 
 def ptr(t):
     return 0 if t is None else t.data_ptr()
+
+
+def ptr_array(tensors):
+    """HOST array of device pointers (for the *_multi entry points)."""
+    return (ctypes.c_void_p * len(tensors))(*[t.data_ptr() for t in tensors])
+
+
+def int_array(values):
+    return (ctypes.c_int * len(values))(*[int(v) for v in values])
 
 
 def workspace(batch_size, total_faces, height, width, device):

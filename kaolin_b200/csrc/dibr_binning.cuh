@@ -29,6 +29,14 @@ struct BinLists {
   int* alloc_cursor;  // [1]
 };
 
+constexpr int MAX_FEATS = 8;
+template <typename T>
+struct FeatSet {      // up to MAX_FEATS feature tensors with the same leading dims, C_t channels each
+  T* ptr[MAX_FEATS];
+  int ch[MAX_FEATS];
+  int n;
+};
+
 struct FaceLayout {   // batched (B,F) layout or packed layout with first_idx (B+1) on device
   const int64_t* first_idx;   // nullptr => batched
   int F;

@@ -123,15 +123,30 @@ int run_binning(const SetupParams<T>& sp, const FaceLayout& fl, const Geometry& 
 }
 
 template <typename T>
-int rasterize_fwd_impl(const T* z, const T* img, const T* bbox_in, const T* feat, const uint8_t* valid,
-                       const int64_t* first_idx, int B, int F, int64_t Ntot, int C, int H, int W,
-                       T coord_mult, int premultiplied, float pix_mult, float eps, T* out_feat,
-                       int64_t* out_idx, T* out_w, void* ws, size_t ws_bytes, void* stream) {
+int make_featsets(const T* const* in, T* const* out, const int* channels, int n, bool need_in,
+                  FeatSet<const T>& fi, FeatSet<T>& fo) {
+  if (n < 0 || n > MAX_FEATS || (n > 0 && (!channels || !out || !in))) return DIBR_ERR_INVALID_ARGUMENT;
+  fi.n = fo.n = n;
+  for (int t = 0; t < MAX_FEATS; ++t) { fi.ptr[t] = nullptr; fo.ptr[t] = nullptr; fi.ch[t] = fo.ch[t] = 0; }
+  for (int t = 0; t < n; ++t) {
+    if (channels[t] < 0) return DIBR_ERR_INVALID_ARGUMENT;
+    if (channels[t] > 0 && (!out[t] || (need_in && !in[t]))) return DIBR_ERR_INVALID_ARGUMENT;
+    fi.ptr[t] = in[t]; fo.ptr[t] = out[t]; fi.ch[t] = fo.ch[t] = channels[t];
+  }
+  return DIBR_OK;
+}
+
+template <typename T>
+int rasterize_fwd_impl(const T* z, const T* img, const T* bbox_in, const T* const* feats, const int* channels,
+                       int n_feat, const uint8_t* valid, const int64_t* first_idx, int B, int F, int64_t Ntot,
+                       int H, int W, T coord_mult, int premultiplied, float pix_mult, float eps,
+                       T* const* out_feats, int64_t* out_idx, T* out_w, void* ws, size_t ws_bytes, void* stream) {
   if (int e = check_dims(B, Ntot, H, W)) return e;
-  if (C < 0 || !(pix_mult > 0.0f)) return DIBR_ERR_INVALID_ARGUMENT;
+  if (!(pix_mult > 0.0f)) return DIBR_ERR_INVALID_ARGUMENT;
   if (B == 0 || H == 0 || W == 0) return DIBR_OK;
-  if ((Ntot > 0 && (!z || !img || (C > 0 && !feat))) || !out_idx || (C > 0 && !out_feat))
-    return DIBR_ERR_INVALID_ARGUMENT;
+  if ((Ntot > 0 && (!z || !img)) || !out_idx) return DIBR_ERR_INVALID_ARGUMENT;
+  FeatSet<const T> fin; FeatSet<T> fout;
+  if (int e = make_featsets<T>(feats, out_feats, channels, n_feat, Ntot > 0, fin, fout)) return e;
   cudaStream_t s = static_cast<cudaStream_t>(stream);
   const Geometry geo = make_geometry(B, H, W);
   FaceLayout fl; fl.first_idx = first_idx; fl.F = F; fl.Ntot = Ntot; fl.B = B;
@@ -141,8 +156,8 @@ int rasterize_fwd_impl(const T* z, const T* img, const T* bbox_in, const T* feat
   BinLists L;
   if (int e = run_binning<T>(sp, fl, geo, ws, ws_bytes, s, L)) return e;
   RasterFwdParams<T> rp;
-  rp.z = z; rp.img = img; rp.feat = feat; rp.coord_mult = coord_mult; rp.premultiplied = premultiplied;
-  rp.pix_mult = pix_mult; rp.eps = eps; rp.C = C; rp.out_feat = out_feat; rp.out_idx = out_idx; rp.out_w = out_w;
+  rp.z = z; rp.img = img; rp.feat = fin; rp.coord_mult = coord_mult; rp.premultiplied = premultiplied;
+  rp.pix_mult = pix_mult; rp.eps = eps; rp.out_feat = fout; rp.out_idx = out_idx; rp.out_w = out_w;
   {
     ProfScope ps(DIBR_KERNEL_RASTER_FWD, s);
     raster_fwd_kernel<T><<<(unsigned)(B * geo.tiles_per_view), 256, 0, s>>>(rp, fl, geo, L);
@@ -152,27 +167,34 @@ int rasterize_fwd_impl(const T* z, const T* img, const T* bbox_in, const T* feat
 }
 
 template <typename T>
-int rasterize_bwd_impl(const T* grad_out, const int64_t* face_idx, const T* weights, const T* img, const T* feat,
-                       int B, int F, int C, int H, int W, double multiplier, float eps, T* grad_img,
-                       T* grad_feat, void* stream) {
+int rasterize_bwd_impl(const T* const* grad_outs, const int64_t* face_idx, const T* weights, const T* img,
+                       const T* const* feats, const int* channels, int n_feat, int B, int F, int H, int W,
+                       double multiplier, float eps, T* grad_img, T* const* grad_feats, void* stream) {
   if (int e = check_dims(B, (int64_t)B * F, H, W)) return e;
-  if (C < 0 || F < 0) return DIBR_ERR_INVALID_ARGUMENT;
+  if (F < 0) return DIBR_ERR_INVALID_ARGUMENT;
   if (!weights && !((float)multiplier > 0.0f)) return DIBR_ERR_INVALID_ARGUMENT;
   cudaStream_t s = static_cast<cudaStream_t>(stream);
   const size_t nf = (size_t)B * F;
+  FeatSet<const T> fin; FeatSet<T> gout;
+  if (int e = make_featsets<T>(feats, grad_feats, channels, n_feat, nf > 0, fin, gout)) return e;
+  FeatSet<const T> gin = fin;
+  for (int t = 0; t < n_feat; ++t) {
+    if (channels[t] > 0 && (int64_t)B * H * W > 0 && (!grad_outs || !grad_outs[t])) return DIBR_ERR_INVALID_ARGUMENT;
+    gin.ptr[t] = grad_outs ? grad_outs[t] : nullptr;
+  }
   if (nf > 0) {
-    if (!grad_img || (C > 0 && !grad_feat)) return DIBR_ERR_INVALID_ARGUMENT;
+    if (!grad_img) return DIBR_ERR_INVALID_ARGUMENT;
     CUDA_TRY(cudaMemsetAsync(grad_img, 0, nf * 6 * sizeof(T), s));
-    if (C > 0) CUDA_TRY(cudaMemsetAsync(grad_feat, 0, nf * 3 * C * sizeof(T), s));
+    for (int t = 0; t < n_feat; ++t)
+      if (channels[t] > 0) CUDA_TRY(cudaMemsetAsync(grad_feats[t], 0, nf * 3 * channels[t] * sizeof(T), s));
   }
   if (B == 0 || H == 0 || W == 0 || nf == 0) return DIBR_OK;
-  if (!grad_out && C > 0) return DIBR_ERR_INVALID_ARGUMENT;
-  if (!face_idx || !img || (C > 0 && !feat)) return DIBR_ERR_INVALID_ARGUMENT;
+  if (!face_idx || !img) return DIBR_ERR_INVALID_ARGUMENT;
   const Geometry geo = make_geometry(B, H, W);
   RasterBwdParams<T> bp;
-  bp.grad_out = grad_out; bp.face_idx = face_idx; bp.weights = weights; bp.img = img; bp.feat = feat;
-  bp.coord_mult = (T)multiplier; bp.pix_mult = (float)multiplier; bp.eps = eps; bp.F = F; bp.C = C;
-  bp.grad_img = grad_img; bp.grad_feat = grad_feat;
+  bp.grad_out = gin; bp.face_idx = face_idx; bp.weights = weights; bp.img = img; bp.feat = fin;
+  bp.coord_mult = (T)multiplier; bp.pix_mult = (float)multiplier; bp.eps = eps; bp.F = F;
+  bp.grad_img = grad_img; bp.grad_feat = gout;
   {
     ProfScope ps(DIBR_KERNEL_RASTER_BWD, s);
     raster_bwd_kernel<T><<<(unsigned)(B * geo.tiles_per_view), 256, 0, s>>>(bp, geo);
@@ -282,26 +304,44 @@ DIBR_API size_t dibr_workspace_bytes(int batch_size, int64_t total_faces, int he
                                               int B, int F, int C, int H, int W, double multiplier,         \
                                               float eps, T* out_feat, int64_t* out_face_idx,                \
                                               T* out_weights, void* ws, size_t ws_bytes, void* stream) {    \
-    if (F < 0) return DIBR_ERR_INVALID_ARGUMENT;                                                              \
-    return rasterize_fwd_impl<T>(z, img, nullptr, feat, valid, nullptr, B, F, (int64_t)B * F, C, H, W,      \
-                                 (T)multiplier, 0, (float)multiplier, eps, out_feat, out_face_idx,           \
+    if (F < 0 || C < 0) return DIBR_ERR_INVALID_ARGUMENT;                                                     \
+    return rasterize_fwd_impl<T>(z, img, nullptr, &feat, &C, 1, valid, nullptr, B, F, (int64_t)B * F, H, W, \
+                                 (T)multiplier, 0, (float)multiplier, eps, &out_feat, out_face_idx,          \
                                  out_weights, ws, ws_bytes, stream);                                          \
+  }                                                                                                           \
+  DIBR_API int dibr_rasterize_fwd_multi_##SUF(const T* z, const T* img, const T* const* feats,               \
+                                              const int* channels, int n_feat, const uint8_t* valid, int B, \
+                                              int F, int H, int W, double multiplier, float eps,            \
+                                              T* const* out_feats, int64_t* out_face_idx, T* out_weights,   \
+                                              void* ws, size_t ws_bytes, void* stream) {                     \
+    if (F < 0) return DIBR_ERR_INVALID_ARGUMENT;                                                              \
+    return rasterize_fwd_impl<T>(z, img, nullptr, feats, channels, n_feat, valid, nullptr, B, F,            \
+                                 (int64_t)B * F, H, W, (T)multiplier, 0, (float)multiplier, eps, out_feats,  \
+                                 out_face_idx, out_weights, ws, ws_bytes, stream);                            \
+  }                                                                                                           \
+  DIBR_API int dibr_rasterize_backward_multi_##SUF(                                                          \
+      const T* const* grad_outs, const int64_t* face_idx, const T* weights, const T* img,                    \
+      const T* const* feats, const int* channels, int n_feat, int B, int F, int H, int W, double multiplier, \
+      float eps, T* grad_img, T* const* grad_feats, void* stream) {                                          \
+    return rasterize_bwd_impl<T>(grad_outs, face_idx, weights, img, feats, channels, n_feat, B, F, H, W,     \
+                                 multiplier, eps, grad_img, grad_feats, stream);                              \
   }                                                                                                           \
   DIBR_API int dibr_packed_rasterize_forward_##SUF(                                                          \
       int H, int W, const T* z, const T* img_mult, const T* bboxes, const T* feat, const int64_t* first_idx, \
       int B, int64_t N, int C, float multiplier, float eps, T* out_feat, int64_t* out_selected_face_idx,     \
       T* out_weights, void* ws, size_t ws_bytes, void* stream) {                                             \
-    if (!first_idx || (N > 0 && !bboxes)) return DIBR_ERR_INVALID_ARGUMENT;                                  \
-    return rasterize_fwd_impl<T>(z, img_mult, bboxes, feat, nullptr, first_idx, B, 0, N, C, H, W, (T)1, 1,   \
-                                 multiplier, eps, out_feat, out_selected_face_idx, out_weights, ws,          \
+    if (!first_idx || (N > 0 && !bboxes) || C < 0) return DIBR_ERR_INVALID_ARGUMENT;                         \
+    return rasterize_fwd_impl<T>(z, img_mult, bboxes, &feat, &C, 1, nullptr, first_idx, B, 0, N, H, W, (T)1, \
+                                 1, multiplier, eps, &out_feat, out_selected_face_idx, out_weights, ws,      \
                                  ws_bytes, stream);                                                           \
   }                                                                                                           \
   DIBR_API int dibr_rasterize_backward_##SUF(const T* grad_out, const int64_t* face_idx, const T* weights,   \
                                              const T* img, const T* feat, int B, int F, int C, int H,       \
                                              int W, double multiplier, float eps, T* grad_img,              \
                                              T* grad_feat, void* stream) {                                   \
-    return rasterize_bwd_impl<T>(grad_out, face_idx, weights, img, feat, B, F, C, H, W, multiplier, eps,     \
-                                 grad_img, grad_feat, stream);                                                \
+    if (C < 0) return DIBR_ERR_INVALID_ARGUMENT;                                                              \
+    return rasterize_bwd_impl<T>(&grad_out, face_idx, weights, img, &feat, &C, 1, B, F, H, W, multiplier,    \
+                                 eps, grad_img, &grad_feat, stream);                                          \
   }                                                                                                           \
   DIBR_API int dibr_soft_mask_fwd_fused_##SUF(const T* img, const int64_t* face_idx, int B, int F, int H,    \
                                               int W, float sigmainv, double boxlen, int knum,               \

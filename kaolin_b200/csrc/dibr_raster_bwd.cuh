@@ -14,17 +14,17 @@ namespace dibr {
 
 template <typename T>
 struct RasterBwdParams {
-  const T* grad_out;       // (B,H,W,C)
+  FeatSet<const T> grad_out;   // n tensors (B,H,W,C_t)
   const int64_t* face_idx; // (B,H,W)
   const T* weights;        // (B,H,W,3) or nullptr => recompute
   const T* img;            // (B,F,3,2) NOT multiplied
-  const T* feat;           // (B,F,3,C)
+  FeatSet<const T> feat;   // n tensors (B,F,3,C_t)
   T coord_mult;
   float pix_mult;
   float eps;
-  int F, C;
+  int F;
   T* grad_img;             // (B,F,3,2)
-  T* grad_feat;            // (B,F,3,C)
+  FeatSet<T> grad_feat;    // n tensors (B,F,3,C_t)
 };
 
 // Sum `v` over the lanes of `peers` (every lane of the warp must call this with its own peers mask);
@@ -63,7 +63,6 @@ __global__ void __launch_bounds__(256) raster_bwd_kernel(RasterBwdParams<T> bp, 
   const int py = ty * TILE + (threadIdx.x / TILE);
   const bool in_image = px < geo.W && py < geo.H;
   const int64_t pix = ((int64_t)b * geo.H + py) * geo.W + px;
-  const int C = bp.C;
 
   long long f = -1;
   if (in_image) f = bp.face_idx[pix];
@@ -85,8 +84,6 @@ __global__ void __launch_bounds__(256) raster_bwd_kernel(RasterBwdParams<T> bp, 
   T w0 = 0, w1 = 0, w2 = 0;
   T gv[6] = {0, 0, 0, 0, 0, 0};
   const int64_t tf = (int64_t)b * bp.F + (covered ? f : 0);
-  const T* g = bp.grad_out + pix * C;
-  const T* ff = bp.feat + tf * 3 * C;
   T k3 = 1, dw1[6], dw2[6];
   if (covered) {
     const T* ps = bp.img + tf * 6;
@@ -120,7 +117,11 @@ __global__ void __launch_bounds__(256) raster_bwd_kernel(RasterBwdParams<T> bp, 
     dw2[2] = dw2dm; dw2[3] = dw2dp; dw2[4] = dw2dn; dw2[5] = dw2dq;
   }
   const T inv_k3sq_den = k3 * k3;
-  T* gf = bp.grad_feat + tf * 3 * C;
+  for (int ft = 0; ft < bp.feat.n; ++ft) {
+  const int C = bp.feat.ch[ft];
+  const T* g = bp.grad_out.ptr[ft] + pix * C;
+  const T* ff = bp.feat.ptr[ft] + tf * 3 * C;
+  T* gf = bp.grad_feat.ptr[ft] + tf * 3 * C;
   for (int d = 0; d < C; ++d) {                     // C is warp-uniform
     T gd = 0;
     if (covered) {
@@ -140,6 +141,7 @@ __global__ void __launch_bounds__(256) raster_bwd_kernel(RasterBwdParams<T> bp, 
       atomicAdd(gf + C + d, s1);
       atomicAdd(gf + 2 * C + d, s2);
     }
+  }
   }
   T* gi = bp.grad_img + tf * 6;
 #pragma unroll

@@ -19,13 +19,12 @@ template <typename T>
 struct RasterFwdParams {
   const T* z;              // (Ntot,3)
   const T* img;            // (Ntot,3,2)
-  const T* feat;           // (Ntot,3,C)
+  FeatSet<const T> feat;   // n tensors (Ntot,3,C_t): a list of feature tensors is consumed in place (no cat)
   T coord_mult;
   int premultiplied;
   float pix_mult;
   float eps;
-  int C;
-  T* out_feat;             // (B,H,W,C)
+  FeatSet<T> out_feat;     // n tensors (B,H,W,C_t)
   int64_t* out_idx;        // (B,H,W)
   T* out_w;                // (B,H,W,3) or nullptr
 };
@@ -127,13 +126,15 @@ __global__ void __launch_bounds__(256) raster_fwd_kernel(RasterFwdParams<T> rp, 
     T* w = rp.out_w + pix * 3;
     w[0] = bw0; w[1] = bw1; w[2] = bw2;
   }
-  T* o = rp.out_feat + pix * rp.C;
-  if (best_f >= 0) {
-    const T* ff = rp.feat + (vbase + best_f) * 3 * rp.C;
-    for (int d = 0; d < rp.C; ++d)
-      o[d] = interp3<T>(ff[d], ff[rp.C + d], ff[2 * rp.C + d], bw0, bw1, bw2);
-  } else {
-    for (int d = 0; d < rp.C; ++d) o[d] = (T)0;
+  for (int t = 0; t < rp.feat.n; ++t) {
+    const int C = rp.feat.ch[t];
+    T* o = rp.out_feat.ptr[t] + pix * C;
+    if (best_f >= 0) {
+      const T* ff = rp.feat.ptr[t] + (vbase + best_f) * 3 * C;
+      for (int d = 0; d < C; ++d) o[d] = interp3<T>(ff[d], ff[C + d], ff[2 * C + d], bw0, bw1, bw2);
+    } else {
+      for (int d = 0; d < C; ++d) o[d] = (T)0;
+    }
   }
 }
 

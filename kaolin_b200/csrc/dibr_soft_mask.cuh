@@ -8,9 +8,10 @@
 // and their pixel ranges are staged next to them.  Each uncovered pixel then walks the sorted list.
 //
 // The walk is split in phases so that the expensive part runs with full lanes even when only a few
-// pixels of the tile are uncovered: (A) compact the uncovered pixels, (B) one warp per pixel builds its
-// k-list with ballot/popc over 32 candidates at a time, (C) all (pixel, k) pairs are evaluated in
-// parallel, (D) one thread per pixel multiplies the probabilities in face order.
+// pixels of the tile are uncovered: (A) compact the uncovered pixels; then, warp-locally, each uncovered pixel
+// of a warp's batch (B) gets its k-list by ballot/popc over 32 candidates at a time, appended to the warp's
+// pair queue, (C) the queued (pixel, k) pairs are evaluated one per lane, (D) one lane per pixel
+// multiplies the probabilities in face order.
 //
 // MODE_FWD writes soft (+ optional k-list side buffers, API-visible through
 // _C.render.mesh.dibr_soft_mask_forward_cuda).  MODE_BWD re-derives the same k-list with the same
@@ -110,7 +111,8 @@ __device__ __forceinline__ void soft_visit(const SoftParams<T>& sp, SoftPixel<T,
 
 // Shared-memory plan (dynamic): candidates (ids + ranges), the compacted uncovered pixels, and the
 // per-pixel k-lists of the current pixel chunk (PAIR_CAP (pixel, k) slots).
-constexpr int PAIR_CAP = 6144;
+constexpr int PAIR_CAP = 2048;     // k-list slots: 8 warps x WARP_K
+constexpr int WARP_K = PAIR_CAP / 8; // largest knum served by the fast path
 template <typename T>
 struct SoftSmem {
   static constexpr size_t ids = 0;
@@ -118,8 +120,10 @@ struct SoftSmem {
   static constexpr size_t hit = rng + SOFT_CAP * sizeof(uint2);
   static constexpr size_t prob = hit + PAIR_CAP * sizeof(int);
   static constexpr size_t upix = prob + PAIR_CAP * sizeof(T);
-  static constexpr size_t kid = upix + 256 * sizeof(int);
-  static constexpr size_t total = kid + 256 * sizeof(int);
+  static constexpr size_t pt = upix + 256 * sizeof(int);
+  static constexpr size_t start = pt + 8 * 32 * sizeof(int);
+  static constexpr size_t own = start + 8 * 33 * sizeof(int);
+  static constexpr size_t total = own + PAIR_CAP;
 };
 
 template <typename T, int MODE>
@@ -131,7 +135,9 @@ __global__ void __launch_bounds__(256) soft_mask_kernel(SoftParams<T> sp, FaceLa
   int* s_hit = reinterpret_cast<int*>(smem_raw + SoftSmem<T>::hit);      // [PAIR_CAP] k-lists, [u*K + k]
   T* s_prob = reinterpret_cast<T*>(smem_raw + SoftSmem<T>::prob);        // [PAIR_CAP] forward probabilities
   int* s_upix = reinterpret_cast<int*>(smem_raw + SoftSmem<T>::upix);    // [256] thread index of uncovered px
-  int* s_kid = reinterpret_cast<int*>(smem_raw + SoftSmem<T>::kid);      // [256] k-list lengths
+  int* s_pt = reinterpret_cast<int*>(smem_raw + SoftSmem<T>::pt);
+  int* s_start = reinterpret_cast<int*>(smem_raw + SoftSmem<T>::start);
+  unsigned char* s_own = smem_raw + SoftSmem<T>::own;
   __shared__ int scratch[9];
 
   const int tile = blockIdx.x % geo.tiles_per_view;
@@ -168,7 +174,7 @@ __global__ void __launch_bounds__(256) soft_mask_kernel(SoftParams<T> sp, FaceLa
   const int n_large = L.large_count[b];
   const int* large_list = L.large_list + vbase;
   const int rx0 = tx * TILE, ry0 = ty * TILE, rx1 = rx0 + TILE - 1, ry1 = ry0 + TILE - 1;
-  bool overflow = n_tile > SOFT_CAP || K > PAIR_CAP;
+  bool overflow = n_tile > SOFT_CAP || K > WARP_K;
   int count = 0;
   if (!overflow) {
     for (int k = threadIdx.x; k < n_tile; k += 256) s_ids[k] = tile_list[k];
@@ -212,55 +218,94 @@ __global__ void __launch_bounds__(256) soft_mask_kernel(SoftParams<T> sp, FaceLa
     return;
   }
 
-  // ---- bitonic sort by face index (pad with INT_MAX); order is semantic (first knum faces in face order)
-  int n2 = 1;
-  while (n2 < count) n2 <<= 1;
-  for (int k = count + threadIdx.x; k < n2; k += 256) s_ids[k] = 0x7fffffff;
+  // ---- sort by face index; order is semantic (first knum faces in face order)
   __syncthreads();
-  for (int size = 2; size <= n2; size <<= 1) {
-    for (int stride = size >> 1; stride > 0; stride >>= 1) {
-      for (int t = threadIdx.x; t < (n2 >> 1); t += 256) {
-        const int lo = ((t / stride) * stride * 2) + (t % stride);
-        const int hi = lo + stride;
-        const bool up = ((lo & size) == 0);
-        const int a = s_ids[lo], c = s_ids[hi];
-        if ((a > c) == up) { s_ids[lo] = c; s_ids[hi] = a; }
+  if (count <= 1024) {
+    // rank sort: face ids are unique, so rank = number of smaller ids; one pass, one barrier
+    int mine[4], rank[4];
+#pragma unroll
+    for (int q = 0; q < 4; ++q) {
+      const int k = threadIdx.x + q * 256;
+      mine[q] = (k < count) ? s_ids[k] : 0x7fffffff;
+      rank[q] = 0;
+    }
+    for (int j = 0; j < count; ++j) {
+      const int v = s_ids[j];                                            // broadcast read
+#pragma unroll
+      for (int q = 0; q < 4; ++q) rank[q] += (v < mine[q]) ? 1 : 0;
+    }
+    __syncthreads();
+#pragma unroll
+    for (int q = 0; q < 4; ++q)
+      if (threadIdx.x + q * 256 < count) s_ids[rank[q]] = mine[q];
+    __syncthreads();
+  } else {
+    int n2 = 1;
+    while (n2 < count) n2 <<= 1;
+    for (int k = count + threadIdx.x; k < n2; k += 256) s_ids[k] = 0x7fffffff;
+    __syncthreads();
+    for (int size = 2; size <= n2; size <<= 1) {
+      for (int stride = size >> 1; stride > 0; stride >>= 1) {
+        for (int t = threadIdx.x; t < (n2 >> 1); t += 256) {
+          const int lo = ((t / stride) * stride * 2) + (t % stride);
+          const int hi = lo + stride;
+          const bool up = ((lo & size) == 0);
+          const int a = s_ids[lo], c = s_ids[hi];
+          if ((a > c) == up) { s_ids[lo] = c; s_ids[hi] = a; }
+        }
+        __syncthreads();
       }
-      __syncthreads();
     }
   }
   for (int k = threadIdx.x; k < count; k += 256) s_rng[k] = L.ranges[vbase + s_ids[k]];
   __syncthreads();
 
+  // ---- phases B-D are warp-local (no block barriers).  Each warp owns the uncovered pixels u = warp,
+  //      warp+8, ... and works in batches of up to 32 pixels / WARP_K (pixel, k) pairs:
+  //      B  per pixel, ballot/popc over 32 candidates at a time -> its k-list (first K hits in face
+  //         order) appended to the warp's pair queue
+  //      C  the queued pairs are evaluated one per lane with full lanes (distance, probability;
+  //         backward: gradients) — pixels with few hits share a warp pass
+  //      D  one lane per pixel multiplies its probabilities in face order (:174-182)
   const float sx = pix_scale(sp.pix_mult, geo.W), sy = pix_scale(sp.pix_mult, geo.H);
-  const int UC = (K > 0) ? min(256, PAIR_CAP / K) : 256;                // uncovered pixels per chunk
-  for (int u0 = 0; u0 < U; u0 += UC) {
-    const int Uc = min(UC, U - u0);
-    // ---- phase B: one warp per uncovered pixel builds its k-list (first K hits in face order)
-    for (int u = warp; u < Uc; u += 8) {
-      const int t = s_upix[u0 + u];
+  int* w_hit = s_hit + warp * WARP_K;                 // queued face ids
+  T* w_prob = s_prob + warp * WARP_K;                 // their probabilities (forward)
+  unsigned char* w_own = s_own + warp * WARP_K;       // batch-local pixel slot of each queued pair
+  int* w_pt = s_pt + warp * 32;                       // per batch pixel: thread index in the tile
+  int* w_start = s_start + warp * 33;                 // per batch pixel: first queue position (+ end)
+  int u = warp;
+  while (u < U) {
+    int npix = 0, nq = 0;
+    // -- B: fill the batch
+    while (u < U && npix < 32) {
+      const int t = s_upix[u];
       const int qx = tx * TILE + (t & (TILE - 1)), qy = ty * TILE + (t / TILE);
+      // stop if this pixel's list might not fit (its length is at most min(K, count))
+      if (nq + min(K, count) > WARP_K) break;
       int kid = 0;
       for (int base = 0; base < count && kid < K; base += 32) {
         const int c = base + lane;
         const bool hit = c < count && range_hits_pixel(s_rng[c], qx, qy);
         const unsigned m = __ballot_sync(0xffffffffu, hit);
         const int r = kid + __popc(m & ((1u << lane) - 1u));
-        if (hit && r < K) s_hit[u * K + r] = s_ids[c];
+        if (hit && r < K) { w_hit[nq + r] = s_ids[c]; w_own[nq + r] = (unsigned char)npix; }
         kid = min(K, kid + __popc(m));
       }
-      if (lane == 0) s_kid[u] = kid;
+      if (lane == 0) { w_pt[npix] = t; w_start[npix] = nq; }
+      nq += kid;
+      ++npix;
+      u += 8;
     }
-    __syncthreads();
-    // ---- phase C: every (pixel, k) pair in parallel — the expensive distance / probability evaluation
-    for (int idx = threadIdx.x; idx < Uc * K; idx += 256) {
-      const int u = idx / K, k = idx - u * K;
-      if (k >= s_kid[u]) continue;
-      const int t = s_upix[u0 + u];
+    if (lane == 0) w_start[npix] = nq;
+    __syncwarp();
+    // -- C: all queued pairs, one per lane
+    for (int q = lane; q < nq; q += 32) {
+      const int slot = w_own[q];
+      const int t = w_pt[slot];
       const int qx = tx * TILE + (t & (TILE - 1)), qy = ty * TILE + (t / TILE);
       const T x0 = (T)pix_coord(sx, geo.W, qx);
       const T y0 = (T)pix_coord(sy, geo.H, geo.H - 1 - qy);
-      const int f = s_hit[idx];
+      const int f = w_hit[q];
       T p[6];
       load_face_xy<T>(sp.img, vbase + f, sp.coord_mult, sp.premultiplied, p);
       int edgeid;
@@ -268,9 +313,9 @@ __global__ void __launch_bounds__(256) soft_mask_kernel(SoftParams<T> sp, FaceLa
       const T prob = soft_prob<T>(d, sp.sigmainv, sp.pix_mult);
       const int64_t qpix = ((int64_t)b * geo.H + qy) * geo.W + qx;
       if (MODE == MODE_FWD) {
-        s_prob[idx] = prob;
+        w_prob[q] = prob;
         if (sp.prob) {
-          const int64_t o = qpix * K + k;
+          const int64_t o = qpix * K + (q - w_start[slot]);
           sp.prob[o] = prob; sp.close_idx[o] = (int64_t)f; sp.dist_type[o] = (uint8_t)(edgeid + 1);
         }
       } else {
@@ -279,24 +324,23 @@ __global__ void __launch_bounds__(256) soft_mask_kernel(SoftParams<T> sp, FaceLa
       }
     }
     if (MODE == MODE_FWD) {
-      __syncthreads();
-      // ---- phase D: in-order product per pixel (:174-182)
-      if (threadIdx.x < Uc) {
-        const int u = threadIdx.x;
-        const int t = s_upix[u0 + u];
+      __syncwarp();
+      // -- D: one lane per pixel of the batch
+      if (lane < npix) {
+        const int t = w_pt[lane];
         const int qx = tx * TILE + (t & (TILE - 1)), qy = ty * TILE + (t / TILE);
         const int64_t qpix = ((int64_t)b * geo.H + qy) * geo.W + qx;
-        const int kid = s_kid[u];
+        const int q0 = w_start[lane], q1 = w_start[lane + 1];
         T allprob = (T)1.0;
-        for (int k = 0; k < kid; ++k) allprob = (T)((double)allprob * (1.0 - (double)s_prob[u * K + k]));
+        for (int q = q0; q < q1; ++q) allprob = (T)((double)allprob * (1.0 - (double)w_prob[q]));
         sp.soft[qpix] = (T)(1.0 - (double)allprob);
         if (sp.prob)
-          for (int k = kid; k < K; ++k) {
+          for (int k = q1 - q0; k < K; ++k) {
             sp.prob[qpix * K + k] = (T)0; sp.close_idx[qpix * K + k] = -1; sp.dist_type[qpix * K + k] = 0;
           }
       }
     }
-    __syncthreads();
+    __syncwarp();
   }
 }
 

@@ -193,6 +193,80 @@ class RasterizeCuda(Function):
         return None, None, None, gi, gf, None, None, None, None
 
 
+class RasterizeCudaList(Function):
+    """``rasterize`` with backend cuda for a LIST of feature tensors, without the reference's
+    ``torch.cat`` (rasterization.py:480-481) nor its output slicing (:499-505): the kernels read the n
+    tensors in place and write n separate outputs, and backward receives n gradients directly.
+    forward(ctx, height, width, z, img, valid_faces, multiplier, eps, *face_features) ->
+    (*interpolated_features, face_idx).  Values are identical to RasterizeCuda on the concatenation."""
+    @staticmethod
+    def forward(ctx, height, width, face_vertices_z, face_vertices_image, valid_faces, multiplier, eps,
+                *face_features):
+        fn = "packed_rasterize_forward_cuda"
+        dev = _require_cuda(fn, face_vertices_z=face_vertices_z, face_vertices_image=face_vertices_image,
+                            valid_faces=valid_faces, **{f"face_features[{i}]": f for i, f in enumerate(face_features)})
+        batch_size, num_faces = face_vertices_z.shape[0], face_vertices_z.shape[1]
+        dtype = face_vertices_z.dtype
+        suf = _lib.suffix(dtype, fn)
+        if len(face_features) > 8:
+            raise RuntimeError(f"{fn}: at most 8 feature tensors per call")
+        feats = []
+        for f in face_features:
+            if f.dtype != dtype or f.dim() != 4 or tuple(f.shape[:3]) != (batch_size, num_faces, 3):
+                raise RuntimeError(f"{fn}: every face_features tensor must be (B,F,3,C) of dtype {dtype}")
+            feats.append(f.contiguous())
+        if face_vertices_image.dtype != dtype or tuple(face_vertices_z.shape) != (batch_size, num_faces, 3) or \
+                tuple(face_vertices_image.shape) != (batch_size, num_faces, 3, 2):
+            raise RuntimeError(f"{fn}: expected face_vertices_z (B,F,3), face_vertices_image (B,F,3,2)")
+        face_vertices_image = face_vertices_image.contiguous()
+        face_vertices_z = face_vertices_z.contiguous()
+        valid_u8 = None
+        if valid_faces is not None:
+            if tuple(valid_faces.shape) != (batch_size, num_faces):
+                raise RuntimeError(f"{fn}: valid_faces must be of shape (B,F)")
+            valid_u8 = valid_faces.to(torch.bool).contiguous().view(torch.uint8)
+        chans = [f.shape[-1] for f in feats]
+        outs = [torch.empty((batch_size, height, width, c), dtype=dtype, device=dev) for c in chans]
+        face_idx = torch.empty((batch_size, height, width), dtype=torch.long, device=dev)
+        with torch.cuda.device(dev):
+            ws, nbytes = _lib.workspace(batch_size, batch_size * num_faces, height, width, dev)
+            code = getattr(_lib.load(), "dibr_rasterize_fwd_multi_" + suf)(
+                _lib.ptr(face_vertices_z), _lib.ptr(face_vertices_image), _lib.ptr_array(feats),
+                _lib.int_array(chans), len(feats), _lib.ptr(valid_u8), batch_size, num_faces, int(height),
+                int(width), float(multiplier), float(eps), _lib.ptr_array(outs), _lib.ptr(face_idx), 0,
+                _lib.ptr(ws), nbytes, _lib.current_stream(dev))
+        _lib.check(code, fn)
+        ctx.save_for_backward(face_idx, face_vertices_image, *feats)
+        ctx.mark_non_differentiable(face_idx)
+        ctx.eps = eps
+        ctx.multiplier = multiplier
+        ctx.out_shapes = [tuple(o.shape) for o in outs]
+        return (*outs, face_idx)
+
+    @staticmethod
+    def backward(ctx, *grads):
+        fn = "rasterize_backward_cuda"
+        face_idx, face_vertices_image = ctx.saved_tensors[:2]
+        feats = list(ctx.saved_tensors[2:])
+        dev = face_vertices_image.device
+        dtype = face_vertices_image.dtype
+        suf = _lib.suffix(dtype, fn)
+        gouts = [torch.zeros(shp, dtype=dtype, device=dev) if g is None else g.contiguous()
+                 for g, shp in zip(grads[:-1], ctx.out_shapes)]
+        b, f = face_vertices_image.shape[0], face_vertices_image.shape[1]
+        h, w = face_idx.shape[1], face_idx.shape[2]
+        gi = torch.empty_like(face_vertices_image)
+        gfs = [torch.empty_like(t) for t in feats]
+        chans = [t.shape[-1] for t in feats]
+        with torch.cuda.device(dev):
+            code = getattr(_lib.load(), "dibr_rasterize_backward_multi_" + suf)(
+                _lib.ptr_array(gouts), _lib.ptr(face_idx), 0, _lib.ptr(face_vertices_image), _lib.ptr_array(feats),
+                _lib.int_array(chans), len(feats), b, f, h, w, float(ctx.multiplier), float(ctx.eps), _lib.ptr(gi),
+                _lib.ptr_array(gfs), _lib.current_stream(dev))
+        _lib.check(code, fn)
+        return (None, None, None, gi, None, None, None, *gfs)
+
+
 def rasterize(height,
               width,
               face_vertices_z,
@@ -230,6 +304,11 @@ def rasterize(height,
         warnings.warn(f'in "rasterize": eps is ignored with backend "{backend}"',
                       UserWarning)
     batch_size, num_faces, _ = face_vertices_z.shape
+    if backend == 'cuda' and isinstance(face_features, (list, tuple)) and 0 < len(face_features) <= 8:
+        # list of features: consumed in place, no concatenation / slicing (see RasterizeCudaList)
+        *image_features, face_idx = RasterizeCudaList.apply(
+            height, width, face_vertices_z, face_vertices_image, valid_faces, multiplier, eps, *face_features)
+        return tuple(image_features), face_idx
     _face_features = torch.cat(face_features, dim=-1) \
         if isinstance(face_features, (list, tuple)) else face_features
 
