@@ -160,7 +160,7 @@ int rasterize_fwd_impl(const T* z, const T* img, const T* bbox_in, const T* cons
   rp.pix_mult = pix_mult; rp.eps = eps; rp.out_feat = fout; rp.out_idx = out_idx; rp.out_w = out_w;
   {
     ProfScope ps(DIBR_KERNEL_RASTER_FWD, s);
-    raster_fwd_kernel<T><<<(unsigned)(B * geo.tiles_per_view), 256, 0, s>>>(rp, fl, geo, L);
+    launch_raster_fwd(rp, fl, geo, L, (unsigned)(B * geo.tiles_per_view), s);
   }
   LAUNCH_CHECK("raster_fwd_kernel");
   return DIBR_OK;

@@ -116,7 +116,7 @@ constexpr int WARP_K = PAIR_CAP / 8; // largest knum served by the fast path
 template <typename T>
 struct SoftSmem {
   static constexpr size_t ids = 0;
-  static constexpr size_t rng = ids + SOFT_CAP * sizeof(int);
+  static constexpr size_t rng = ids + (SOFT_CAP + 8) * sizeof(int);   // + INT_MAX padding
   static constexpr size_t hit = rng + SOFT_CAP * sizeof(uint2);
   static constexpr size_t prob = hit + PAIR_CAP * sizeof(int);
   static constexpr size_t upix = prob + PAIR_CAP * sizeof(T);
@@ -125,6 +125,35 @@ struct SoftSmem {
   static constexpr size_t own = start + 8 * 33 * sizeof(int);
   static constexpr size_t total = own + PAIR_CAP;
 };
+
+// Each thread ranks Q of the ids (k = tid + q*256); see the call site.
+template <int Q>
+__device__ __forceinline__ void rank_sort(int* s_ids, const int count) {
+  int mine[Q], rank[Q];
+  bool any = false;
+#pragma unroll
+  for (int q = 0; q < Q; ++q) {
+    const int k = threadIdx.x + q * 256;
+    mine[q] = (k < count) ? s_ids[k] : 0x7fffffff;
+    rank[q] = 0;
+    any |= k < count;
+  }
+  if (any) {
+    const int4* v4 = reinterpret_cast<const int4*>(s_ids);
+    const int n4 = (count + 3) >> 2;
+    for (int j = 0; j < n4; ++j) {
+      const int4 v = v4[j];                                              // broadcast read
+#pragma unroll
+      for (int q = 0; q < Q; ++q)
+        rank[q] += (v.x < mine[q]) + (v.y < mine[q]) + (v.z < mine[q]) + (v.w < mine[q]);
+    }
+  }
+  __syncthreads();
+#pragma unroll
+  for (int q = 0; q < Q; ++q)
+    if (threadIdx.x + q * 256 < count) s_ids[rank[q]] = mine[q];
+  __syncthreads();
+}
 
 template <typename T, int MODE>
 __global__ void __launch_bounds__(256) soft_mask_kernel(SoftParams<T> sp, FaceLayout fl, Geometry geo,
@@ -221,24 +250,13 @@ __global__ void __launch_bounds__(256) soft_mask_kernel(SoftParams<T> sp, FaceLa
   // ---- sort by face index; order is semantic (first knum faces in face order)
   __syncthreads();
   if (count <= 1024) {
-    // rank sort: face ids are unique, so rank = number of smaller ids; one pass, one barrier
-    int mine[4], rank[4];
-#pragma unroll
-    for (int q = 0; q < 4; ++q) {
-      const int k = threadIdx.x + q * 256;
-      mine[q] = (k < count) ? s_ids[k] : 0x7fffffff;
-      rank[q] = 0;
-    }
-    for (int j = 0; j < count; ++j) {
-      const int v = s_ids[j];                                            // broadcast read
-#pragma unroll
-      for (int q = 0; q < 4; ++q) rank[q] += (v < mine[q]) ? 1 : 0;
-    }
+    // rank sort: face ids are unique, so rank = number of smaller ids; one pass, one barrier.  The list is
+    // padded to a multiple of 4 with INT_MAX (never smaller than anything) and read as int4 broadcasts.
+    if (threadIdx.x < 4) s_ids[count + threadIdx.x] = 0x7fffffff;       // SOFT_CAP + 4 slots are reserved
     __syncthreads();
-#pragma unroll
-    for (int q = 0; q < 4; ++q)
-      if (threadIdx.x + q * 256 < count) s_ids[rank[q]] = mine[q];
-    __syncthreads();
+    if (count <= 256) rank_sort<1>(s_ids, count);
+    else if (count <= 512) rank_sort<2>(s_ids, count);
+    else rank_sort<4>(s_ids, count);
   } else {
     int n2 = 1;
     while (n2 < count) n2 <<= 1;
