@@ -9,7 +9,7 @@
 // K1b     scan        : per-view exclusive scan of the tile counters, segment base by one atomic.
 // K1c     fill        : scatter face ids into the per-tile lists.
 //
-// Faces spanning more than MAX_SPAN x MAX_SPAN tiles go to a per-view "large" list that every tile
+// Faces touching more than PAIRS_PER_FACE (16) tiles go to a per-view "large" list that every tile
 // of the view filters (ballot + prefix-scan compaction in the consumer), so the per-tile storage is
 // bounded by PAIRS_PER_FACE * faces and cannot overflow.  Lists are UNORDERED; consumers that need
 // face order (depth ties, soft-mask "first knum faces") use order-independent rules or sort in smem.
@@ -116,7 +116,7 @@ __global__ void __launch_bounds__(256) setup_count_kernel(SetupParams<T> sp, Fac
       rec = pack_range(ix0, ix1, jy0, jy1);
       b = fl.view_of(g);
       const int tx0 = ix0 / TILE, tx1 = ix1 / TILE, ty0 = jy0 / TILE, ty1 = jy1 / TILE;
-      if (tx1 - tx0 < MAX_SPAN && ty1 - ty0 < MAX_SPAN) {
+      if ((tx1 - tx0 + 1) * (ty1 - ty0 + 1) <= PAIRS_PER_FACE) {
         int* cnt = L.tile_count + (int64_t)b * geo.tiles_per_view;
         for (int ty = ty0; ty <= ty1; ++ty)
           for (int tx = tx0; tx <= tx1; ++tx) atomicAdd(cnt + ty * geo.tiles_x + tx, 1);
@@ -196,7 +196,7 @@ __global__ void __launch_bounds__(256) fill_kernel(FaceLayout fl, Geometry geo, 
   if (range_empty(r)) return;
   const int tx0 = (int)(r.x & 0xffffu) / TILE, tx1 = (int)(r.x >> 16) / TILE;
   const int ty0 = (int)(r.y & 0xffffu) / TILE, ty1 = (int)(r.y >> 16) / TILE;
-  if (!(tx1 - tx0 < MAX_SPAN && ty1 - ty0 < MAX_SPAN)) return;      // in the large list
+  if ((tx1 - tx0 + 1) * (ty1 - ty0 + 1) > PAIRS_PER_FACE) return;   // in the large list
   const int b = fl.view_of(g);
   const int local = (int)(g - fl.base(b));
   int* cur = L.tile_cursor + (int64_t)b * geo.tiles_per_view;

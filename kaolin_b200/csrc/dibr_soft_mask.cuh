@@ -109,21 +109,21 @@ __device__ __forceinline__ void soft_visit(const SoftParams<T>& sp, SoftPixel<T,
   ++st.kid;
 }
 
-// Shared-memory plan (dynamic): candidates (ids + ranges), the compacted uncovered pixels, and the
-// per-pixel k-lists of the current pixel chunk (PAIR_CAP (pixel, k) slots).
-constexpr int PAIR_CAP = 2048;     // k-list slots: 8 warps x WARP_K
-constexpr int WARP_K = PAIR_CAP / 8; // largest knum served by the fast path
+// Shared-memory plan (dynamic): sorted candidate ids, their tile-local coverage masks, the compacted
+// uncovered pixels and, per warp, CELLS k-list cells (a cell first holds the candidate slot of a
+// (pixel, k) pair, then — forward — its probability) plus small per-batch tables.
+constexpr int CELLS = 1024;        // k-list cells per warp: a batch is min(32, CELLS / knum) pixels
+template <typename T> struct CellInt;
+template <> struct CellInt<float> { typedef unsigned type; };
+template <> struct CellInt<double> { typedef unsigned long long type; };
 template <typename T>
 struct SoftSmem {
   static constexpr size_t ids = 0;
-  static constexpr size_t rng = ids + (SOFT_CAP + 8) * sizeof(int);   // + INT_MAX padding
-  static constexpr size_t hit = rng + SOFT_CAP * sizeof(uint2);
-  static constexpr size_t prob = hit + PAIR_CAP * sizeof(int);
-  static constexpr size_t upix = prob + PAIR_CAP * sizeof(T);
-  static constexpr size_t pt = upix + 256 * sizeof(int);
-  static constexpr size_t start = pt + 8 * 32 * sizeof(int);
-  static constexpr size_t own = start + 8 * 33 * sizeof(int);
-  static constexpr size_t total = own + PAIR_CAP;
+  static constexpr size_t mask = ids + (SOFT_CAP + 8) * sizeof(int);   // + INT_MAX padding of the rank sort
+  static constexpr size_t cell = mask + (SOFT_CAP + 8) * sizeof(unsigned);
+  static constexpr size_t upix = cell + 8 * CELLS * sizeof(T);
+  static constexpr size_t wtab = upix + 256 * sizeof(int);
+  static constexpr size_t total = wtab + (256 + 8 * 32) * sizeof(int);
 };
 
 // Each thread ranks Q of the ids (k = tid + q*256); see the call site.
@@ -155,25 +155,28 @@ __device__ __forceinline__ void rank_sort(int* s_ids, const int count) {
   __syncthreads();
 }
 
+// bits lo..hi (inclusive, 0 <= lo <= hi <= 15)
+__device__ __forceinline__ unsigned bit_span16(int lo, int hi) { return ((2u << hi) - 1u) & ~((1u << lo) - 1u); }
+
 template <typename T, int MODE>
 __global__ void __launch_bounds__(256) soft_mask_kernel(SoftParams<T> sp, FaceLayout fl, Geometry geo,
                                                         BinLists L) {
+  typedef typename CellInt<T>::type cell_int;
   extern __shared__ __align__(16) unsigned char smem_raw[];
-  int* s_ids = reinterpret_cast<int*>(smem_raw + SoftSmem<T>::ids);      // [SOFT_CAP] sorted candidate faces
-  uint2* s_rng = reinterpret_cast<uint2*>(smem_raw + SoftSmem<T>::rng);  // [SOFT_CAP] their pixel ranges
-  int* s_hit = reinterpret_cast<int*>(smem_raw + SoftSmem<T>::hit);      // [PAIR_CAP] k-lists, [u*K + k]
-  T* s_prob = reinterpret_cast<T*>(smem_raw + SoftSmem<T>::prob);        // [PAIR_CAP] forward probabilities
-  int* s_upix = reinterpret_cast<int*>(smem_raw + SoftSmem<T>::upix);    // [256] thread index of uncovered px
-  int* s_pt = reinterpret_cast<int*>(smem_raw + SoftSmem<T>::pt);
-  int* s_start = reinterpret_cast<int*>(smem_raw + SoftSmem<T>::start);
-  unsigned char* s_own = smem_raw + SoftSmem<T>::own;
+  int* s_ids = reinterpret_cast<int*>(smem_raw + SoftSmem<T>::ids);            // [SOFT_CAP] sorted candidate faces
+  unsigned* s_mask = reinterpret_cast<unsigned*>(smem_raw + SoftSmem<T>::mask); // [SOFT_CAP] col bits | row bits << 16
+  T* s_cell = reinterpret_cast<T*>(smem_raw + SoftSmem<T>::cell);              // [8][CELLS]
+  int* s_upix = reinterpret_cast<int*>(smem_raw + SoftSmem<T>::upix);          // [256] thread index of uncovered px
+  int* s_wtab = reinterpret_cast<int*>(smem_raw + SoftSmem<T>::wtab);          // [256] list lengths + [8][32] per-warp tables
   __shared__ int scratch[9];
+  __shared__ float s_px[TILE], s_py[TILE];
 
   const int tile = blockIdx.x % geo.tiles_per_view;
   const int b = blockIdx.x / geo.tiles_per_view;
   const int tx = tile % geo.tiles_x, ty = tile / geo.tiles_x;
-  const int px = tx * TILE + (threadIdx.x & (TILE - 1));
-  const int py = ty * TILE + (threadIdx.x / TILE);
+  const int rx0 = tx * TILE, ry0 = ty * TILE, rx1 = rx0 + TILE - 1, ry1 = ry0 + TILE - 1;
+  const int px = rx0 + (threadIdx.x & (TILE - 1));
+  const int py = ry0 + (threadIdx.x / TILE);
   const bool in_image = px < geo.W && py < geo.H;
   const int64_t vbase = fl.base(b);
   const int64_t pix = ((int64_t)b * geo.H + py) * geo.W + px;
@@ -191,6 +194,12 @@ __global__ void __launch_bounds__(256) soft_mask_kernel(SoftParams<T> sp, FaceLa
       }
     }
   }
+  if (threadIdx.x < TILE) {
+    s_px[threadIdx.x] = pix_coord(pix_scale(sp.pix_mult, geo.W), geo.W, rx0 + threadIdx.x);
+  } else if (threadIdx.x < 2 * TILE) {
+    const int j = threadIdx.x - TILE;
+    s_py[j] = pix_coord(pix_scale(sp.pix_mult, geo.H), geo.H, geo.H - 1 - (ry0 + j));
+  }
   // ---- phase A: compact the uncovered pixels of the tile
   int U;
   const int uslot = block_compact_256(uncovered, scratch, U);
@@ -202,8 +211,7 @@ __global__ void __launch_bounds__(256) soft_mask_kernel(SoftParams<T> sp, FaceLa
   const int* tile_list = L.pairs + L.tile_offset[blockIdx.x];
   const int n_large = L.large_count[b];
   const int* large_list = L.large_list + vbase;
-  const int rx0 = tx * TILE, ry0 = ty * TILE, rx1 = rx0 + TILE - 1, ry1 = ry0 + TILE - 1;
-  bool overflow = n_tile > SOFT_CAP || K > WARP_K;
+  bool overflow = n_tile > SOFT_CAP || K > CELLS;
   int count = 0;
   if (!overflow) {
     for (int k = threadIdx.x; k < n_tile; k += 256) s_ids[k] = tile_list[k];
@@ -252,7 +260,7 @@ __global__ void __launch_bounds__(256) soft_mask_kernel(SoftParams<T> sp, FaceLa
   if (count <= 1024) {
     // rank sort: face ids are unique, so rank = number of smaller ids; one pass, one barrier.  The list is
     // padded to a multiple of 4 with INT_MAX (never smaller than anything) and read as int4 broadcasts.
-    if (threadIdx.x < 4) s_ids[count + threadIdx.x] = 0x7fffffff;       // SOFT_CAP + 4 slots are reserved
+    if (threadIdx.x < 4) s_ids[count + threadIdx.x] = 0x7fffffff;       // SOFT_CAP + 8 slots are reserved
     __syncthreads();
     if (count <= 256) rank_sort<1>(s_ids, count);
     else if (count <= 512) rank_sort<2>(s_ids, count);
@@ -275,90 +283,128 @@ __global__ void __launch_bounds__(256) soft_mask_kernel(SoftParams<T> sp, FaceLa
       }
     }
   }
-  for (int k = threadIdx.x; k < count; k += 256) s_rng[k] = L.ranges[vbase + s_ids[k]];
+  // ---- tile-local coverage mask of every candidate: bit x (columns) and bit 16 + y (rows) of the pixels
+  //      inside its enlarged bbox — the exact pixel range of the reference's float test (:89-97)
+  for (int k = threadIdx.x; k < count; k += 256) {
+    const uint2 r = L.ranges[vbase + s_ids[k]];
+    const int lx0 = max((int)(r.x & 0xffffu), rx0) - rx0, lx1 = min((int)(r.x >> 16), rx1) - rx0;
+    const int ly0 = max((int)(r.y & 0xffffu), ry0) - ry0, ly1 = min((int)(r.y >> 16), ry1) - ry0;
+    s_mask[k] = (lx0 <= lx1 && ly0 <= ly1) ? (bit_span16(lx0, lx1) | (bit_span16(ly0, ly1) << 16)) : 0u;
+  }
+  if (threadIdx.x < 4) s_mask[count + threadIdx.x] = 0u;
   __syncthreads();
 
-  // ---- phases B-D are warp-local (no block barriers).  Each warp owns the uncovered pixels u = warp,
-  //      warp+8, ... and works in batches of up to 32 pixels / WARP_K (pixel, k) pairs:
-  //      B  per pixel, ballot/popc over 32 candidates at a time -> its k-list (first K hits in face
-  //         order) appended to the warp's pair queue
-  //      C  the queued pairs are evaluated one per lane with full lanes (distance, probability;
-  //         backward: gradients) — pixels with few hits share a warp pass
-  //      D  one lane per pixel multiplies its probabilities in face order (:174-182)
-  const float sx = pix_scale(sp.pix_mult, geo.W), sy = pix_scale(sp.pix_mult, geo.H);
-  int* w_hit = s_hit + warp * WARP_K;                 // queued face ids
-  T* w_prob = s_prob + warp * WARP_K;                 // their probabilities (forward)
-  unsigned char* w_own = s_own + warp * WARP_K;       // batch-local pixel slot of each queued pair
-  int* w_pt = s_pt + warp * 32;                       // per batch pixel: thread index in the tile
-  int* w_start = s_start + warp * 33;                 // per batch pixel: first queue position (+ end)
-  int u = warp;
-  while (u < U) {
-    int npix = 0, nq = 0;
-    // -- B: fill the batch
-    while (u < U && npix < 32) {
-      const int t = s_upix[u];
-      const int qx = tx * TILE + (t & (TILE - 1)), qy = ty * TILE + (t / TILE);
-      // stop if this pixel's list might not fit (its length is at most min(K, count))
-      if (nq + min(K, count) > WARP_K) break;
+  // ---- phases B-D over super-batches of NPB uncovered pixels (usually the whole tile at once):
+  //      B  lane = pixel, 32 pixels per warp pass: one sweep over the candidate masks (uint4 broadcast reads)
+  //         appends the slots of the first K hits, in face order, to the pixel's cell row
+  //      C  each warp takes an equal slice of the super-batch's pixels; their (pixel, k) pairs are flattened
+  //         (prefix sum of the list lengths; owner by REDUX/ballot/popc) and evaluated one per lane with full
+  //         lanes: distance, probability (forward: stored back into the cell; backward: gradients)
+  //      D  forward, thread = pixel: multiplies its probabilities in face order (:174-182)
+  const int KS = K | 1;                                  // odd row stride: conflict-free cell rows
+  const int NPB = min(256, (8 * CELLS) / KS);
+  cell_int* s_celli = reinterpret_cast<cell_int*>(s_cell);
+  int* s_kid = s_wtab;                                   // [256] list length of each pixel of the super-batch
+  int* w_tab = s_wtab + 256 + warp * 32;
+  const unsigned lt_mask = (1u << lane) - 1u, le_mask = 0xffffffffu >> (31 - lane);
+  const int n4 = (count + 3) >> 2;
+  for (int sb0 = 0; sb0 < U; sb0 += NPB) {
+    const int nsb = min(NPB, U - sb0);
+    // -- B
+    for (int u0 = warp * 32; u0 < nsb; u0 += 256) {
+      const int u = u0 + lane;
+      const bool act = u < nsb;
+      const int t = act ? s_upix[sb0 + u] : 0;
+      const unsigned mybit = (1u << (t & 15)) | (0x10000u << (t >> 4));
+      cell_int* row = s_celli + u * KS;
       int kid = 0;
-      for (int base = 0; base < count && kid < K; base += 32) {
-        const int c = base + lane;
-        const bool hit = c < count && range_hits_pixel(s_rng[c], qx, qy);
-        const unsigned m = __ballot_sync(0xffffffffu, hit);
-        const int r = kid + __popc(m & ((1u << lane) - 1u));
-        if (hit && r < K) { w_hit[nq + r] = s_ids[c]; w_own[nq + r] = (unsigned char)npix; }
-        kid = min(K, kid + __popc(m));
+      for (int j = 0; j < n4; ++j) {
+        const uint4 m = reinterpret_cast<const uint4*>(s_mask)[j];
+        if (act && (m.x & mybit) == mybit && kid < K) { row[kid] = (cell_int)(4 * j); ++kid; }
+        if (act && (m.y & mybit) == mybit && kid < K) { row[kid] = (cell_int)(4 * j + 1); ++kid; }
+        if (act && (m.z & mybit) == mybit && kid < K) { row[kid] = (cell_int)(4 * j + 2); ++kid; }
+        if (act && (m.w & mybit) == mybit && kid < K) { row[kid] = (cell_int)(4 * j + 3); ++kid; }
+        if ((j & 7) == 7 && __all_sync(0xffffffffu, !act || kid >= K)) break;
       }
-      if (lane == 0) { w_pt[npix] = t; w_start[npix] = nq; }
-      nq += kid;
-      ++npix;
-      u += 8;
+      if (act) s_kid[u] = kid;
     }
-    if (lane == 0) w_start[npix] = nq;
-    __syncwarp();
-    // -- C: all queued pairs, one per lane
-    for (int q = lane; q < nq; q += 32) {
-      const int slot = w_own[q];
-      const int t = w_pt[slot];
-      const int qx = tx * TILE + (t & (TILE - 1)), qy = ty * TILE + (t / TILE);
-      const T x0 = (T)pix_coord(sx, geo.W, qx);
-      const T y0 = (T)pix_coord(sy, geo.H, geo.H - 1 - qy);
-      const int f = w_hit[q];
-      T p[6];
-      load_face_xy<T>(sp.img, vbase + f, sp.coord_mult, sp.premultiplied, p);
-      int edgeid;
-      const T d = soft_distance<T>(p, x0, y0, sp.pix_mult, edgeid);
-      const T prob = soft_prob<T>(d, sp.sigmainv, sp.pix_mult);
-      const int64_t qpix = ((int64_t)b * geo.H + qy) * geo.W + qx;
-      if (MODE == MODE_FWD) {
-        w_prob[q] = prob;
-        if (sp.prob) {
-          const int64_t o = qpix * K + (q - w_start[slot]);
-          sp.prob[o] = prob; sp.close_idx[o] = (int64_t)f; sp.dist_type[o] = (uint8_t)(edgeid + 1);
-        }
-      } else {
-        soft_backward_pair<T>(p, x0, y0, prob, edgeid, sp.grad_soft[qpix], sp.soft_in[qpix], sp.sigmainv,
-                              sp.pix_mult, sp.grad_img + (vbase + f) * 6);
+    __syncthreads();
+    // -- C
+    const int PW = (nsb + 7) >> 3;                       // pixels per warp (<= 32)
+    const int ubase = warp * PW;
+    if (ubase < nsb) {
+      const int npix = min(PW, nsb - ubase);
+      const bool act = lane < npix;
+      const int t = act ? s_upix[sb0 + ubase + lane] : 0;
+      const int kid = act ? s_kid[ubase + lane] : 0;
+      int incl = kid;
+#pragma unroll
+      for (int o = 1; o < 32; o <<= 1) {
+        const int v = __shfl_up_sync(0xffffffffu, incl, o);
+        if (lane >= o) incl += v;
       }
-    }
-    if (MODE == MODE_FWD) {
+      const int start = incl - kid;
+      const int nq = __shfl_sync(0xffffffffu, incl, 31);
+      const unsigned ne = __ballot_sync(0xffffffffu, kid > 0);
+      if (kid > 0) w_tab[__popc(ne & lt_mask)] = lane;
+      T g = 0, sft = 0;
+      if (MODE == MODE_BWD && act) {
+        const int64_t tpix = ((int64_t)b * geo.H + ry0 + (t >> 4)) * geo.W + rx0 + (t & 15);
+        g = sp.grad_soft[tpix]; sft = sp.soft_in[tpix];
+      }
       __syncwarp();
-      // -- D: one lane per pixel of the batch
-      if (lane < npix) {
-        const int t = w_pt[lane];
-        const int qx = tx * TILE + (t & (TILE - 1)), qy = ty * TILE + (t / TILE);
-        const int64_t qpix = ((int64_t)b * geo.H + qy) * geo.W + qx;
-        const int q0 = w_start[lane], q1 = w_start[lane + 1];
-        T allprob = (T)1.0;
-        for (int q = q0; q < q1; ++q) allprob = (T)((double)allprob * (1.0 - (double)w_prob[q]));
-        sp.soft[qpix] = (T)(1.0 - (double)allprob);
-        if (sp.prob)
-          for (int k = q1 - q0; k < K; ++k) {
-            sp.prob[qpix * K + k] = (T)0; sp.close_idx[qpix * K + k] = -1; sp.dist_type[qpix * K + k] = 0;
+      for (int q0 = 0; q0 < nq; q0 += 32) {
+        const unsigned rel = (unsigned)(start - q0);
+        const unsigned bit = (kid > 0 && rel < 32u) ? (1u << rel) : 0u;
+        const unsigned starts = __reduce_or_sync(0xffffffffu, bit);
+        const int before = __popc(__ballot_sync(0xffffffffu, kid > 0 && start < q0));
+        const int rank = before + __popc(starts & le_mask) - 1;        // rank among the pixels with hits
+        const int q = q0 + lane;
+        const bool valid = q < nq;
+        const int pl = valid ? w_tab[rank] : 0;
+        const int pstart = __shfl_sync(0xffffffffu, start, pl);
+        const int pt = __shfl_sync(0xffffffffu, t, pl);
+        T pg = 0, ps = 0;
+        if (MODE == MODE_BWD) { pg = __shfl_sync(0xffffffffu, g, pl); ps = __shfl_sync(0xffffffffu, sft, pl); }
+        if (!valid) continue;
+        const int k = q - pstart;
+        const int cell = (ubase + pl) * KS + k;
+        const int f = s_ids[(int)s_celli[cell]];
+        const int lx = pt & 15, ly = pt >> 4;
+        const T x0 = (T)s_px[lx], y0 = (T)s_py[ly];
+        T p[6];
+        load_face_xy<T>(sp.img, vbase + f, sp.coord_mult, sp.premultiplied, p);
+        int edgeid;
+        const T d = soft_distance<T>(p, x0, y0, sp.pix_mult, edgeid);
+        const T prob = soft_prob<T>(d, sp.sigmainv, sp.pix_mult);
+        if (MODE == MODE_FWD) {
+          s_cell[cell] = prob;
+          if (sp.prob) {
+            const int64_t o = (((int64_t)b * geo.H + ry0 + ly) * geo.W + rx0 + lx) * K + k;
+            sp.prob[o] = prob; sp.close_idx[o] = (int64_t)f; sp.dist_type[o] = (uint8_t)(edgeid + 1);
           }
+        } else {
+          soft_backward_pair<T>(p, x0, y0, prob, edgeid, pg, ps, sp.sigmainv, sp.pix_mult,
+                                sp.grad_img + (vbase + f) * 6);
+        }
       }
     }
-    __syncwarp();
+    __syncthreads();
+    // -- D
+    if (MODE == MODE_FWD && (int)threadIdx.x < nsb) {
+      const int t = s_upix[sb0 + threadIdx.x];
+      const int64_t tpix = ((int64_t)b * geo.H + ry0 + (t >> 4)) * geo.W + rx0 + (t & 15);
+      const int kid = s_kid[threadIdx.x];
+      const T* row = s_cell + threadIdx.x * KS;
+      T allprob = (T)1.0;
+      for (int k = 0; k < kid; ++k) allprob = (T)((double)allprob * (1.0 - (double)row[k]));
+      sp.soft[tpix] = (T)(1.0 - (double)allprob);
+      if (sp.prob)
+        for (int k = kid; k < K; ++k) {
+          sp.prob[tpix * K + k] = (T)0; sp.close_idx[tpix * K + k] = -1; sp.dist_type[tpix * K + k] = 0;
+        }
+    }
+    if (sb0 + NPB < U) __syncthreads();                  // the cells are reused by the next super-batch
   }
 }
 

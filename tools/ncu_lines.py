@@ -29,6 +29,21 @@ def parse_dis(path):
     return funcs
 
 
+_SRC = {}
+
+
+def src_text(ln):
+    """Source text of (file, line) for files under kaolin_b200/csrc."""
+    if not ln:
+        return ""
+    import os
+    f, n = ln
+    if f not in _SRC:
+        path = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "kaolin_b200", "csrc", f)
+        _SRC[f] = open(path).read().split("\n") if os.path.exists(path) else []
+    return _SRC[f][n - 1].strip()[:90] if 0 < n <= len(_SRC[f]) else ""
+
+
 def main():
     sass, dis = sys.argv[1], sys.argv[2]
     filt = sys.argv[3] if len(sys.argv) > 3 else ""
@@ -62,8 +77,9 @@ def main():
                 ln = lines[n] if n < len(lines) else None
                 v = int(r[ci] or 0); agg[ln][0] += v; agg[ln][1] += int(r[cs] or 0); tot += v
             print(f"== {name[:80]}  instr={tot} sass_rows={len(body)} dis_rows={len(lines)}")
-            for ln, (v, s) in sorted(agg.items(), key=lambda kv: -kv[1][0])[:28]:
-                print(f"   {str(ln):40s} {v:12d} {100.0 * v / max(tot, 1):5.1f}%  samples {s}")
+            top = int(sys.argv[4]) if len(sys.argv) > 4 else 28
+            for ln, (v, s) in sorted(agg.items(), key=lambda kv: -kv[1][0])[:top]:
+                print(f"   {str(ln):34s} {v:11d} {100.0 * v / max(tot, 1):5.1f}%  smp {s:5d}  {src_text(ln)}")
         else:
             i += 1
 
