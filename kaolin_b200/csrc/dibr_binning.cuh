@@ -9,9 +9,11 @@
 // K1b     scan        : per-view exclusive scan of the tile counters, segment base by one atomic.
 // K1c     fill        : scatter face ids into the per-tile lists.
 //
-// Faces touching more than PAIRS_PER_FACE (16) tiles go to a per-view "large" list that every tile
-// of the view filters (ballot + prefix-scan compaction in the consumer), so the per-tile storage is
-// bounded by PAIRS_PER_FACE * faces and cannot overflow.  Lists are UNORDERED; consumers that need
+// Two levels.  A face touching at most PAIRS_PER_FACE (16) tiles is listed in each of them; otherwise it is
+// listed in the coarse cells (4 x 4 tiles) it touches if those are at most 16; otherwise it goes to a per-view
+// "large" list.  A tile's consumer reads its own list as is and FILTERS the enclosing coarse cell's list and
+// the large list against the tile rectangle (ballot + prefix-scan compaction).  Every face occupies at most
+// 16 slots at exactly one level, so the storage is bounded by PAIRS_PER_FACE * faces and cannot overflow.  Lists are UNORDERED; consumers that need
 // face order (depth ties, soft-mask "first knum faces") use order-independent rules or sort in smem.
 #pragma once
 #include "dibr_common.cuh"
@@ -20,9 +22,9 @@ namespace dibr {
 
 struct BinLists {
   uint2* ranges;      // [Ntot]  packed inclusive pixel range per face (empty_range() = contributes nothing)
-  int* tile_count;    // [B*T]
-  int* tile_offset;   // [B*T]
-  int* tile_cursor;   // [B*T]   fill cursor (absolute position)
+  int* tile_count;    // [B*S]   S = slots_per_view: per view, the fine tiles then the coarse cells
+  int* tile_offset;   // [B*S]
+  int* tile_cursor;   // [B*S]   fill cursor (absolute position)
   int* pairs;         // [PAIRS_PER_FACE * Ntot] face ids local to their view
   int* large_list;    // [Ntot]  view b's entries start at view_base(b)
   int* large_count;   // [B]
@@ -116,14 +118,21 @@ __global__ void __launch_bounds__(256) setup_count_kernel(SetupParams<T> sp, Fac
       rec = pack_range(ix0, ix1, jy0, jy1);
       b = fl.view_of(g);
       const int tx0 = ix0 / TILE, tx1 = ix1 / TILE, ty0 = jy0 / TILE, ty1 = jy1 / TILE;
+      int* cnt = L.tile_count + (int64_t)b * geo.slots_per_view;
       if ((tx1 - tx0 + 1) * (ty1 - ty0 + 1) <= PAIRS_PER_FACE) {
-        int* cnt = L.tile_count + (int64_t)b * geo.tiles_per_view;
         for (int ty = ty0; ty <= ty1; ++ty)
           for (int tx = tx0; tx <= tx1; ++tx) atomicAdd(cnt + ty * geo.tiles_x + tx, 1);
       } else {
-        const int64_t vb = fl.base(b);
-        const int pos = atomicAdd(L.large_count + b, 1);
-        L.large_list[vb + pos] = (int)(g - vb);
+        const int cx0 = tx0 / COARSE, cx1 = tx1 / COARSE, cy0 = ty0 / COARSE, cy1 = ty1 / COARSE;
+        if ((cx1 - cx0 + 1) * (cy1 - cy0 + 1) <= PAIRS_PER_FACE) {
+          cnt += geo.tiles_per_view;
+          for (int cy = cy0; cy <= cy1; ++cy)
+            for (int cx = cx0; cx <= cx1; ++cx) atomicAdd(cnt + cy * geo.coarse_x + cx, 1);
+        } else {
+          const int64_t vb = fl.base(b);
+          const int pos = atomicAdd(L.large_count + b, 1);
+          L.large_list[vb + pos] = (int)(g - vb);
+        }
       }
     }
   }
@@ -135,7 +144,7 @@ __global__ void __launch_bounds__(1024) scan_kernel(Geometry geo, BinLists L) {
   __shared__ int warp_sums[32];
   __shared__ int s_base;
   const int b = blockIdx.x;
-  const int T = geo.tiles_per_view;
+  const int T = geo.slots_per_view;
   const int* cnt = L.tile_count + (int64_t)b * T;
   int* off = L.tile_offset + (int64_t)b * T;
   int* cur = L.tile_cursor + (int64_t)b * T;
@@ -196,15 +205,46 @@ __global__ void __launch_bounds__(256) fill_kernel(FaceLayout fl, Geometry geo, 
   if (range_empty(r)) return;
   const int tx0 = (int)(r.x & 0xffffu) / TILE, tx1 = (int)(r.x >> 16) / TILE;
   const int ty0 = (int)(r.y & 0xffffu) / TILE, ty1 = (int)(r.y >> 16) / TILE;
-  if ((tx1 - tx0 + 1) * (ty1 - ty0 + 1) > PAIRS_PER_FACE) return;   // in the large list
   const int b = fl.view_of(g);
   const int local = (int)(g - fl.base(b));
-  int* cur = L.tile_cursor + (int64_t)b * geo.tiles_per_view;
-  for (int ty = ty0; ty <= ty1; ++ty)
-    for (int tx = tx0; tx <= tx1; ++tx) {
-      const int pos = atomicAdd(cur + ty * geo.tiles_x + tx, 1);
+  int* cur = L.tile_cursor + (int64_t)b * geo.slots_per_view;
+  if ((tx1 - tx0 + 1) * (ty1 - ty0 + 1) <= PAIRS_PER_FACE) {
+    for (int ty = ty0; ty <= ty1; ++ty)
+      for (int tx = tx0; tx <= tx1; ++tx) {
+        const int pos = atomicAdd(cur + ty * geo.tiles_x + tx, 1);
+        L.pairs[pos] = local;
+      }
+    return;
+  }
+  const int cx0 = tx0 / COARSE, cx1 = tx1 / COARSE, cy0 = ty0 / COARSE, cy1 = ty1 / COARSE;
+  if ((cx1 - cx0 + 1) * (cy1 - cy0 + 1) > PAIRS_PER_FACE) return;   // in the large list
+  cur += geo.tiles_per_view;
+  for (int cy = cy0; cy <= cy1; ++cy)
+    for (int cx = cx0; cx <= cx1; ++cx) {
+      const int pos = atomicAdd(cur + cy * geo.coarse_x + cx, 1);
       L.pairs[pos] = local;
     }
+}
+
+// The candidate sources of one 16x16 tile: the faces binned to the tile itself (all touch it), those binned to
+// the enclosing coarse cell and the view's "large" list (both must be filtered with range_hits_rect).
+struct TileLists {
+  const int* fine; int n_fine;
+  const int* coarse; int n_coarse;
+  const int* large; int n_large;
+  __device__ __forceinline__ int n_filtered() const { return n_coarse + n_large; }
+  __device__ __forceinline__ int filtered_at(int k) const { return k < n_coarse ? coarse[k] : large[k - n_coarse]; }
+};
+__device__ __forceinline__ TileLists tile_lists(const BinLists& L, const Geometry& geo, const FaceLayout& fl,
+                                                const int b, const int tx, const int ty) {
+  TileLists t;
+  const int64_t s0 = (int64_t)b * geo.slots_per_view;
+  const int64_t sf = s0 + ty * geo.tiles_x + tx;
+  const int64_t sc = s0 + geo.tiles_per_view + (ty / COARSE) * geo.coarse_x + (tx / COARSE);
+  t.fine = L.pairs + L.tile_offset[sf];     t.n_fine = L.tile_count[sf];
+  t.coarse = L.pairs + L.tile_offset[sc];   t.n_coarse = L.tile_count[sc];
+  t.large = L.large_list + fl.base(b);      t.n_large = L.large_count[b];
+  return t;
 }
 
 // ---------------------------------------------------------------- block-level ordered compaction

@@ -62,7 +62,7 @@ struct WsLayout {
 };
 WsLayout ws_layout(int B, int64_t Ntot, const Geometry& geo) {
   WsLayout w;
-  const size_t bt = (size_t)B * geo.tiles_per_view;
+  const size_t bt = (size_t)B * geo.slots_per_view;
   size_t o = 0;
   w.zero_begin = o;
   w.tile_count = o;  o = align_up(o + bt * sizeof(int));
@@ -96,7 +96,7 @@ int check_dims(int B, int64_t Ntot, int H, int W) {
   if (H > 32768 || W > 32768) return DIBR_ERR_TOO_LARGE;
   if (Ntot >= (int64_t)1 << 31 || (int64_t)B * H * W >= (int64_t)1 << 40) return DIBR_ERR_TOO_LARGE;
   const Geometry geo = make_geometry(B, H, W);
-  if ((int64_t)B * geo.tiles_per_view >= (int64_t)1 << 31) return DIBR_ERR_TOO_LARGE;
+  if ((int64_t)B * geo.slots_per_view >= (int64_t)1 << 31) return DIBR_ERR_TOO_LARGE;
   return DIBR_OK;
 }
 

@@ -58,23 +58,21 @@ __device__ __forceinline__ void gather_tile(const RasterFwdParams<T>& rp, const 
   bool has_nan = false;
   int last_inside = -1;
 
-  const int n_tile = L.tile_count[blockIdx.x];
-  const int* tile_list = L.pairs + L.tile_offset[blockIdx.x];
-  const int n_large = L.large_count[b];
-  const int* large_list = L.large_list + vbase;
+  const TileLists tl = tile_lists(L, geo, fl, b, tx, ty);
+  const int n_tile = tl.n_fine;
   const int rx0 = tx * TILE, ry0 = ty * TILE, rx1 = rx0 + TILE - 1, ry1 = ry0 + TILE - 1;
 
-  const int n_total = n_tile + n_large;
+  const int n_total = n_tile + tl.n_filtered();
   for (int base = 0; base < n_total; base += 256) {
-    // ---- stage up to 256 candidates (tile entries pass unconditionally, large entries are filtered)
+    // ---- stage up to 256 candidates (tile entries pass unconditionally, coarse / large entries are filtered)
     const int k = base + threadIdx.x;
     int f = -1;
     uint2 r = empty_range();
     if (k < n_tile) {
-      f = tile_list[k];
+      f = tl.fine[k];
       r = L.ranges[vbase + f];
     } else if (k < n_total) {
-      f = large_list[k - n_tile];
+      f = tl.filtered_at(k - n_tile);
       r = L.ranges[vbase + f];
       if (!range_hits_rect(r, rx0, ry0, rx1, ry1)) f = -1;
     }
@@ -300,8 +298,9 @@ __global__ void __launch_bounds__(256) raster_fwd_scatter_kernel(RasterFwdParams
   if (threadIdx.x == 0) sh.nan_seen = 0;
   __syncthreads();
 
-  const int n_tile = L.tile_count[blockIdx.x];
-  const int* tile_list = L.pairs + L.tile_offset[blockIdx.x];
+  const TileLists tl = tile_lists(L, geo, fl, b, tx, ty);
+  const int n_tile = tl.n_fine;
+  const int* tile_list = tl.fine;
   // the tile's faces are dealt to the 8 warps in equal contiguous slices (a short list still keeps every
   // warp busy: the parallelism is in the pairs, not in the faces)
   const int per_warp = (n_tile + 7) >> 3;
@@ -310,13 +309,13 @@ __global__ void __launch_bounds__(256) raster_fwd_scatter_kernel(RasterFwdParams
     const int k = base + lane;
     scatter_faces(rp, L, sh, vbase, (k < slice_end) ? tile_list[k] : -1, rx0, ry0);
   }
-  const int n_large = L.large_count[b];
-  const int* large_list = L.large_list + vbase;
-  for (int base = warp * 32; base < n_large; base += 256) {
+  // faces binned at the coarse level / in the view's large list: filter against the tile, compact, scatter
+  const int n_filt = tl.n_filtered();
+  for (int base = warp * 32; base < n_filt; base += 256) {
     const int k = base + lane;
     int f = -1;
-    if (k < n_large) {
-      f = large_list[k];
+    if (k < n_filt) {
+      f = tl.filtered_at(k);
       if (!range_hits_rect(L.ranges[vbase + f], rx0, ry0, rx0 + TILE - 1, ry0 + TILE - 1)) f = -1;
     }
     const unsigned m = __ballot_sync(0xffffffffu, f >= 0);

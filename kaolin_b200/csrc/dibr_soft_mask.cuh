@@ -123,8 +123,37 @@ struct SoftSmem {
   static constexpr size_t cell = mask + (SOFT_CAP + 8) * sizeof(unsigned);
   static constexpr size_t upix = cell + 8 * CELLS * sizeof(T);
   static constexpr size_t wtab = upix + 256 * sizeof(int);
-  static constexpr size_t total = wtab + (256 + 8 * 32) * sizeof(int);
+  static constexpr size_t ktot = wtab + 8 * 32 * sizeof(int);
+  static constexpr size_t knew = ktot + 256 * sizeof(int);
+  static constexpr size_t acc = knew + 256 * sizeof(int);
+  static constexpr size_t total = acc + 256 * sizeof(T);
 };
+
+// Number of the tile's candidates (tile list + "large" faces touching the tile) with lo < id <= hi.
+// CTA-wide; `scratch` = 9 ints.  Used only by the multi-pass selection of very dense tiles.
+__device__ __forceinline__ int count_candidates(const TileLists& tl, const uint2* ranges, const int lo,
+                                                const int hi, const int rx0, const int ry0, const int rx1,
+                                                const int ry1, int* scratch) {
+  int c = 0;
+  for (int k = threadIdx.x; k < tl.n_fine; k += 256) {
+    const int f = tl.fine[k];
+    c += (f > lo && f <= hi) ? 1 : 0;
+  }
+  const int n_filt = tl.n_filtered();
+  for (int k = threadIdx.x; k < n_filt; k += 256) {
+    const int f = tl.filtered_at(k);
+    if (f > lo && f <= hi && range_hits_rect(ranges[f], rx0, ry0, rx1, ry1)) ++c;
+  }
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) c += __shfl_xor_sync(0xffffffffu, c, o);
+  __syncthreads();
+  if ((threadIdx.x & 31) == 0) scratch[threadIdx.x >> 5] = c;
+  __syncthreads();
+  int tot = 0;
+#pragma unroll
+  for (int w = 0; w < 8; ++w) tot += scratch[w];
+  return tot;
+}
 
 // Each thread ranks Q of the ids (k = tid + q*256); see the call site.
 template <int Q>
@@ -159,7 +188,7 @@ __device__ __forceinline__ void rank_sort(int* s_ids, const int count) {
 __device__ __forceinline__ unsigned bit_span16(int lo, int hi) { return ((2u << hi) - 1u) & ~((1u << lo) - 1u); }
 
 template <typename T, int MODE>
-__global__ void __launch_bounds__(256) soft_mask_kernel(SoftParams<T> sp, FaceLayout fl, Geometry geo,
+__global__ void __launch_bounds__(256, (sizeof(T) == 4 ? 4 : 2)) soft_mask_kernel(SoftParams<T> sp, FaceLayout fl, Geometry geo,
                                                         BinLists L) {
   typedef typename CellInt<T>::type cell_int;
   extern __shared__ __align__(16) unsigned char smem_raw[];
@@ -167,7 +196,10 @@ __global__ void __launch_bounds__(256) soft_mask_kernel(SoftParams<T> sp, FaceLa
   unsigned* s_mask = reinterpret_cast<unsigned*>(smem_raw + SoftSmem<T>::mask); // [SOFT_CAP] col bits | row bits << 16
   T* s_cell = reinterpret_cast<T*>(smem_raw + SoftSmem<T>::cell);              // [8][CELLS]
   int* s_upix = reinterpret_cast<int*>(smem_raw + SoftSmem<T>::upix);          // [256] thread index of uncovered px
-  int* s_wtab = reinterpret_cast<int*>(smem_raw + SoftSmem<T>::wtab);          // [256] list lengths + [8][32] per-warp tables
+  int* s_wtab = reinterpret_cast<int*>(smem_raw + SoftSmem<T>::wtab);          // [8][32] per-warp owner tables
+  int* s_ktot = reinterpret_cast<int*>(smem_raw + SoftSmem<T>::ktot);          // [256] hits so far per uncovered px
+  int* s_knew = reinterpret_cast<int*>(smem_raw + SoftSmem<T>::knew);          // [256] new hits (this pass, super-batch)
+  T* s_acc = reinterpret_cast<T*>(smem_raw + SoftSmem<T>::acc);                // [256] running product of (1 - prob)
   __shared__ int scratch[9];
   __shared__ float s_px[TILE], s_py[TILE];
 
@@ -205,206 +237,239 @@ __global__ void __launch_bounds__(256) soft_mask_kernel(SoftParams<T> sp, FaceLa
   const int uslot = block_compact_256(uncovered, scratch, U);
   if (U == 0) return;
   if (uncovered) s_upix[uslot] = threadIdx.x;
+  s_ktot[threadIdx.x] = 0;                               // hits so far of uncovered pixel u (< K)
+  s_acc[threadIdx.x] = (T)1.0;                           // forward: running product of (1 - prob), face order
 
-  // ---- gather the candidates: tile list + filtered large faces
-  const int n_tile = L.tile_count[blockIdx.x];
-  const int* tile_list = L.pairs + L.tile_offset[blockIdx.x];
-  const int n_large = L.large_count[b];
-  const int* large_list = L.large_list + vbase;
-  bool overflow = n_tile > SOFT_CAP || K > CELLS;
-  int count = 0;
-  if (!overflow) {
-    for (int k = threadIdx.x; k < n_tile; k += 256) s_ids[k] = tile_list[k];
-    count = n_tile;
-    for (int base = 0; base < n_large; base += 256) {                  // n_large is CTA-uniform
-      const int k = base + threadIdx.x;
-      int f = -1;
-      if (k < n_large) {
-        f = large_list[k];
-        if (!range_hits_rect(L.ranges[vbase + f], rx0, ry0, rx1, ry1)) f = -1;
+  const TileLists tl = tile_lists(L, geo, fl, b, tx, ty);
+  const int n_tile = tl.n_fine;
+  const int* tile_list = tl.fine;
+  const int n_filt = tl.n_filtered();
+  const int nf = (int)(fl.base(b + 1) - vbase);
+  const int KS = K | 1;                                  // odd row stride: conflict-free cell rows
+  const int NPB = max(1, min(256, (8 * CELLS) / KS));    // pixels per super-batch (K > 8 * CELLS: 1, clipped rows)
+  const int KROW = min(K, 8 * CELLS);                    // new hits a pixel can take per pass
+  cell_int* s_celli = reinterpret_cast<cell_int*>(s_cell);
+  int* w_tab = s_wtab + warp * 32;
+  const unsigned lt_mask = (1u << lane) - 1u, le_mask = 0xffffffffu >> (31 - lane);
+
+  // The candidates are consumed in PASSES of increasing face-index ranges (lo, hi], each holding at most
+  // SOFT_CAP candidates.  Nearly every tile needs a single pass (hi = last face); only very dense tiles
+  // (config 5) take the selection path below.
+  int lo = -1;
+  bool first = true;
+  while (true) {
+    // ---- gather the candidates with lo < id <= hi: tile list + filtered large faces
+    int hi = nf - 1;
+    int count = 0;
+    bool fits = first && n_tile <= SOFT_CAP;
+    if (fits) {
+      for (int k = threadIdx.x; k < n_tile; k += 256) s_ids[k] = tile_list[k];
+      count = n_tile;
+      for (int base = 0; base < n_filt; base += 256) {                 // n_filt is CTA-uniform
+        const int k = base + threadIdx.x;
+        int f = -1;
+        if (k < n_filt) {
+          f = tl.filtered_at(k);
+          if (!range_hits_rect(L.ranges[vbase + f], rx0, ry0, rx1, ry1)) f = -1;
+        }
+        int add;
+        const int slot = block_compact_256(f >= 0, scratch, add);
+        if (count + add > SOFT_CAP) { fits = false; break; }            // uniform
+        if (f >= 0) s_ids[count + slot] = f;
+        count += add;
       }
-      int add;
-      const int slot = block_compact_256(f >= 0, scratch, add);
-      if (count + add > SOFT_CAP) { overflow = true; break; }          // uniform
-      if (f >= 0) s_ids[count + slot] = f;
-      count += add;
     }
-  }
-
-  if (overflow) {
-    // ---- rare: more candidates than shared memory holds -> the reference's in-order scan over every face
-    if (uncovered) {
-      SoftPixel<T, MODE> st;
-      st.pix = pix; st.kid = 0; st.allprob = (T)1.0;
-      st.x0 = (T)pix_coord(pix_scale(sp.pix_mult, geo.W), geo.W, px);
-      st.y0 = (T)pix_coord(pix_scale(sp.pix_mult, geo.H), geo.H, geo.H - 1 - py);
-      if (MODE == MODE_BWD) { st.dLdp = sp.grad_soft[pix]; st.soft = sp.soft_in[pix]; }
-      const int nf = (int)(fl.base(b + 1) - vbase);
-      for (int f = 0; f < nf && st.kid < K; ++f) {
-        if (!range_hits_pixel(L.ranges[vbase + f], px, py)) continue;
-        soft_visit<T, MODE>(sp, st, vbase, f);
+    if (!fits) {
+      // -- selection: largest hi with #{candidates in (lo, hi]} <= SOFT_CAP, by bisection on the face index
+      //    (ids are unique, so a range of one id always fits)
+      __syncthreads();
+      if (count_candidates(tl, L.ranges + vbase, lo, hi, rx0, ry0, rx1, ry1, scratch) > SOFT_CAP) {
+        int good = lo, bad = hi;
+        while (bad - good > 1) {
+          const int mid = good + ((bad - good) >> 1);
+          if (count_candidates(tl, L.ranges + vbase, lo, mid, rx0, ry0, rx1, ry1, scratch) <= SOFT_CAP) good = mid; else bad = mid;
+        }
+        hi = good;
       }
-      if (MODE == MODE_FWD) {
-        sp.soft[pix] = (T)(1.0 - (double)st.allprob);
-        if (sp.prob)
-          for (int k = st.kid; k < K; ++k) {
-            sp.prob[pix * K + k] = (T)0; sp.close_idx[pix * K + k] = -1; sp.dist_type[pix * K + k] = 0;
+      if (threadIdx.x == 0) scratch[8] = 0;
+      __syncthreads();
+      for (int k = threadIdx.x; k < n_tile; k += 256) {
+        const int f = tile_list[k];
+        if (f > lo && f <= hi) s_ids[atomicAdd(&scratch[8], 1)] = f;
+      }
+      for (int k = threadIdx.x; k < n_filt; k += 256) {
+        const int f = tl.filtered_at(k);
+        if (f > lo && f <= hi && range_hits_rect(L.ranges[vbase + f], rx0, ry0, rx1, ry1))
+          s_ids[atomicAdd(&scratch[8], 1)] = f;
+      }
+      __syncthreads();
+      count = scratch[8];
+    }
+    first = false;
+    if (count > 0) {
+      // ---- sort by face index; order is semantic (first knum faces in face order)
+      __syncthreads();
+      if (count <= 1024) {
+        // rank sort: face ids are unique, so rank = number of smaller ids; one pass, one barrier.  The list
+        // is padded to a multiple of 4 with INT_MAX (never smaller than anything), read as int4 broadcasts.
+        if (threadIdx.x < 4) s_ids[count + threadIdx.x] = 0x7fffffff;   // SOFT_CAP + 8 slots are reserved
+        __syncthreads();
+        if (count <= 256) rank_sort<1>(s_ids, count);
+        else if (count <= 512) rank_sort<2>(s_ids, count);
+        else rank_sort<4>(s_ids, count);
+      } else {
+        int n2 = 1;
+        while (n2 < count) n2 <<= 1;
+        for (int k = count + threadIdx.x; k < n2; k += 256) s_ids[k] = 0x7fffffff;
+        __syncthreads();
+        for (int size = 2; size <= n2; size <<= 1) {
+          for (int stride = size >> 1; stride > 0; stride >>= 1) {
+            for (int t = threadIdx.x; t < (n2 >> 1); t += 256) {
+              const int lo_i = ((t / stride) * stride * 2) + (t % stride);
+              const int hi_i = lo_i + stride;
+              const bool up = ((lo_i & size) == 0);
+              const int a = s_ids[lo_i], c = s_ids[hi_i];
+              if ((a > c) == up) { s_ids[lo_i] = c; s_ids[hi_i] = a; }
+            }
+            __syncthreads();
           }
+        }
       }
-    }
-    return;
-  }
+      // ---- tile-local coverage mask of every candidate: bit x (columns) and bit 16 + y (rows) of the pixels
+      //      inside its enlarged bbox — the exact pixel range of the reference's float test (:89-97)
+      for (int k = threadIdx.x; k < count; k += 256) {
+        const uint2 r = L.ranges[vbase + s_ids[k]];
+        const int lx0 = max((int)(r.x & 0xffffu), rx0) - rx0, lx1 = min((int)(r.x >> 16), rx1) - rx0;
+        const int ly0 = max((int)(r.y & 0xffffu), ry0) - ry0, ly1 = min((int)(r.y >> 16), ry1) - ry0;
+        s_mask[k] = (lx0 <= lx1 && ly0 <= ly1) ? (bit_span16(lx0, lx1) | (bit_span16(ly0, ly1) << 16)) : 0u;
+      }
+      if (threadIdx.x < 4) s_mask[count + threadIdx.x] = 0u;
+      __syncthreads();
 
-  // ---- sort by face index; order is semantic (first knum faces in face order)
-  __syncthreads();
-  if (count <= 1024) {
-    // rank sort: face ids are unique, so rank = number of smaller ids; one pass, one barrier.  The list is
-    // padded to a multiple of 4 with INT_MAX (never smaller than anything) and read as int4 broadcasts.
-    if (threadIdx.x < 4) s_ids[count + threadIdx.x] = 0x7fffffff;       // SOFT_CAP + 8 slots are reserved
-    __syncthreads();
-    if (count <= 256) rank_sort<1>(s_ids, count);
-    else if (count <= 512) rank_sort<2>(s_ids, count);
-    else rank_sort<4>(s_ids, count);
-  } else {
-    int n2 = 1;
-    while (n2 < count) n2 <<= 1;
-    for (int k = count + threadIdx.x; k < n2; k += 256) s_ids[k] = 0x7fffffff;
-    __syncthreads();
-    for (int size = 2; size <= n2; size <<= 1) {
-      for (int stride = size >> 1; stride > 0; stride >>= 1) {
-        for (int t = threadIdx.x; t < (n2 >> 1); t += 256) {
-          const int lo = ((t / stride) * stride * 2) + (t % stride);
-          const int hi = lo + stride;
-          const bool up = ((lo & size) == 0);
-          const int a = s_ids[lo], c = s_ids[hi];
-          if ((a > c) == up) { s_ids[lo] = c; s_ids[hi] = a; }
+      // ---- phases B-D over super-batches of NPB uncovered pixels (usually the whole tile at once):
+      //      B  lane = pixel, 32 pixels per warp pass: one sweep over the candidate masks (uint4 broadcast
+      //         reads) appends the slots of the pixel's next hits, in face order, to its cell row, until it
+      //         has K in total
+      //      C  each warp takes an equal slice of the super-batch's pixels; their new (pixel, k) pairs are
+      //         flattened (prefix sum of the list lengths; owner by REDUX/ballot/popc) and evaluated one per
+      //         lane with full lanes: distance, probability (forward: stored back into the cell; backward:
+      //         gradients)
+      //      D  forward, thread = pixel: multiplies the new probabilities, in face order, into the pixel's
+      //         running product (:174-182)
+      const int n4 = (count + 3) >> 2;
+      for (int sb0 = 0; sb0 < U; sb0 += NPB) {
+        const int nsb = min(NPB, U - sb0);
+        // -- B
+        for (int u0 = warp * 32; u0 < nsb; u0 += 256) {
+          const int u = u0 + lane;
+          const bool act = u < nsb;
+          const int t = act ? s_upix[sb0 + u] : 0;
+          const int room = act ? min(K - s_ktot[sb0 + u], KROW) : 0;
+          const unsigned mybit = (1u << (t & 15)) | (0x10000u << (t >> 4));
+          cell_int* row = s_celli + u * KS;
+          int kid = 0;
+          for (int j = 0; j < n4; ++j) {
+            const uint4 m = reinterpret_cast<const uint4*>(s_mask)[j];
+            if ((m.x & mybit) == mybit && kid < room) { row[kid] = (cell_int)(4 * j); ++kid; }
+            if ((m.y & mybit) == mybit && kid < room) { row[kid] = (cell_int)(4 * j + 1); ++kid; }
+            if ((m.z & mybit) == mybit && kid < room) { row[kid] = (cell_int)(4 * j + 2); ++kid; }
+            if ((m.w & mybit) == mybit && kid < room) { row[kid] = (cell_int)(4 * j + 3); ++kid; }
+            if ((j & 7) == 7 && __all_sync(0xffffffffu, kid >= room)) break;
+          }
+          if (act) s_knew[u] = kid;
         }
         __syncthreads();
-      }
-    }
-  }
-  // ---- tile-local coverage mask of every candidate: bit x (columns) and bit 16 + y (rows) of the pixels
-  //      inside its enlarged bbox — the exact pixel range of the reference's float test (:89-97)
-  for (int k = threadIdx.x; k < count; k += 256) {
-    const uint2 r = L.ranges[vbase + s_ids[k]];
-    const int lx0 = max((int)(r.x & 0xffffu), rx0) - rx0, lx1 = min((int)(r.x >> 16), rx1) - rx0;
-    const int ly0 = max((int)(r.y & 0xffffu), ry0) - ry0, ly1 = min((int)(r.y >> 16), ry1) - ry0;
-    s_mask[k] = (lx0 <= lx1 && ly0 <= ly1) ? (bit_span16(lx0, lx1) | (bit_span16(ly0, ly1) << 16)) : 0u;
-  }
-  if (threadIdx.x < 4) s_mask[count + threadIdx.x] = 0u;
-  __syncthreads();
-
-  // ---- phases B-D over super-batches of NPB uncovered pixels (usually the whole tile at once):
-  //      B  lane = pixel, 32 pixels per warp pass: one sweep over the candidate masks (uint4 broadcast reads)
-  //         appends the slots of the first K hits, in face order, to the pixel's cell row
-  //      C  each warp takes an equal slice of the super-batch's pixels; their (pixel, k) pairs are flattened
-  //         (prefix sum of the list lengths; owner by REDUX/ballot/popc) and evaluated one per lane with full
-  //         lanes: distance, probability (forward: stored back into the cell; backward: gradients)
-  //      D  forward, thread = pixel: multiplies its probabilities in face order (:174-182)
-  const int KS = K | 1;                                  // odd row stride: conflict-free cell rows
-  const int NPB = min(256, (8 * CELLS) / KS);
-  cell_int* s_celli = reinterpret_cast<cell_int*>(s_cell);
-  int* s_kid = s_wtab;                                   // [256] list length of each pixel of the super-batch
-  int* w_tab = s_wtab + 256 + warp * 32;
-  const unsigned lt_mask = (1u << lane) - 1u, le_mask = 0xffffffffu >> (31 - lane);
-  const int n4 = (count + 3) >> 2;
-  for (int sb0 = 0; sb0 < U; sb0 += NPB) {
-    const int nsb = min(NPB, U - sb0);
-    // -- B
-    for (int u0 = warp * 32; u0 < nsb; u0 += 256) {
-      const int u = u0 + lane;
-      const bool act = u < nsb;
-      const int t = act ? s_upix[sb0 + u] : 0;
-      const unsigned mybit = (1u << (t & 15)) | (0x10000u << (t >> 4));
-      cell_int* row = s_celli + u * KS;
-      int kid = 0;
-      for (int j = 0; j < n4; ++j) {
-        const uint4 m = reinterpret_cast<const uint4*>(s_mask)[j];
-        if (act && (m.x & mybit) == mybit && kid < K) { row[kid] = (cell_int)(4 * j); ++kid; }
-        if (act && (m.y & mybit) == mybit && kid < K) { row[kid] = (cell_int)(4 * j + 1); ++kid; }
-        if (act && (m.z & mybit) == mybit && kid < K) { row[kid] = (cell_int)(4 * j + 2); ++kid; }
-        if (act && (m.w & mybit) == mybit && kid < K) { row[kid] = (cell_int)(4 * j + 3); ++kid; }
-        if ((j & 7) == 7 && __all_sync(0xffffffffu, !act || kid >= K)) break;
-      }
-      if (act) s_kid[u] = kid;
-    }
-    __syncthreads();
-    // -- C
-    const int PW = (nsb + 7) >> 3;                       // pixels per warp (<= 32)
-    const int ubase = warp * PW;
-    if (ubase < nsb) {
-      const int npix = min(PW, nsb - ubase);
-      const bool act = lane < npix;
-      const int t = act ? s_upix[sb0 + ubase + lane] : 0;
-      const int kid = act ? s_kid[ubase + lane] : 0;
-      int incl = kid;
+        // -- C
+        const int PW = (nsb + 7) >> 3;                   // pixels per warp (<= 32)
+        const int ubase = warp * PW;
+        if (ubase < nsb) {
+          const int npix = min(PW, nsb - ubase);
+          const bool act = lane < npix;
+          const int t = act ? s_upix[sb0 + ubase + lane] : 0;
+          const int kid = act ? s_knew[ubase + lane] : 0;
+          const int kprev = act ? s_ktot[sb0 + ubase + lane] : 0;
+          int incl = kid;
 #pragma unroll
-      for (int o = 1; o < 32; o <<= 1) {
-        const int v = __shfl_up_sync(0xffffffffu, incl, o);
-        if (lane >= o) incl += v;
-      }
-      const int start = incl - kid;
-      const int nq = __shfl_sync(0xffffffffu, incl, 31);
-      const unsigned ne = __ballot_sync(0xffffffffu, kid > 0);
-      if (kid > 0) w_tab[__popc(ne & lt_mask)] = lane;
-      T g = 0, sft = 0;
-      if (MODE == MODE_BWD && act) {
-        const int64_t tpix = ((int64_t)b * geo.H + ry0 + (t >> 4)) * geo.W + rx0 + (t & 15);
-        g = sp.grad_soft[tpix]; sft = sp.soft_in[tpix];
-      }
-      __syncwarp();
-      for (int q0 = 0; q0 < nq; q0 += 32) {
-        const unsigned rel = (unsigned)(start - q0);
-        const unsigned bit = (kid > 0 && rel < 32u) ? (1u << rel) : 0u;
-        const unsigned starts = __reduce_or_sync(0xffffffffu, bit);
-        const int before = __popc(__ballot_sync(0xffffffffu, kid > 0 && start < q0));
-        const int rank = before + __popc(starts & le_mask) - 1;        // rank among the pixels with hits
-        const int q = q0 + lane;
-        const bool valid = q < nq;
-        const int pl = valid ? w_tab[rank] : 0;
-        const int pstart = __shfl_sync(0xffffffffu, start, pl);
-        const int pt = __shfl_sync(0xffffffffu, t, pl);
-        T pg = 0, ps = 0;
-        if (MODE == MODE_BWD) { pg = __shfl_sync(0xffffffffu, g, pl); ps = __shfl_sync(0xffffffffu, sft, pl); }
-        if (!valid) continue;
-        const int k = q - pstart;
-        const int cell = (ubase + pl) * KS + k;
-        const int f = s_ids[(int)s_celli[cell]];
-        const int lx = pt & 15, ly = pt >> 4;
-        const T x0 = (T)s_px[lx], y0 = (T)s_py[ly];
-        T p[6];
-        load_face_xy<T>(sp.img, vbase + f, sp.coord_mult, sp.premultiplied, p);
-        int edgeid;
-        const T d = soft_distance<T>(p, x0, y0, sp.pix_mult, edgeid);
-        const T prob = soft_prob<T>(d, sp.sigmainv, sp.pix_mult);
-        if (MODE == MODE_FWD) {
-          s_cell[cell] = prob;
-          if (sp.prob) {
-            const int64_t o = (((int64_t)b * geo.H + ry0 + ly) * geo.W + rx0 + lx) * K + k;
-            sp.prob[o] = prob; sp.close_idx[o] = (int64_t)f; sp.dist_type[o] = (uint8_t)(edgeid + 1);
+          for (int o = 1; o < 32; o <<= 1) {
+            const int v = __shfl_up_sync(0xffffffffu, incl, o);
+            if (lane >= o) incl += v;
           }
-        } else {
-          soft_backward_pair<T>(p, x0, y0, prob, edgeid, pg, ps, sp.sigmainv, sp.pix_mult,
-                                sp.grad_img + (vbase + f) * 6);
+          const int start = incl - kid;
+          const int nq = __shfl_sync(0xffffffffu, incl, 31);
+          const unsigned ne = __ballot_sync(0xffffffffu, kid > 0);
+          if (kid > 0) w_tab[__popc(ne & lt_mask)] = lane;
+          T g = 0, sft = 0;
+          if (MODE == MODE_BWD && act) {
+            const int64_t tpix = ((int64_t)b * geo.H + ry0 + (t >> 4)) * geo.W + rx0 + (t & 15);
+            g = sp.grad_soft[tpix]; sft = sp.soft_in[tpix];
+          }
+          __syncwarp();
+          for (int q0 = 0; q0 < nq; q0 += 32) {
+            const unsigned rel = (unsigned)(start - q0);
+            const unsigned bit = (kid > 0 && rel < 32u) ? (1u << rel) : 0u;
+            const unsigned starts = __reduce_or_sync(0xffffffffu, bit);
+            const int before = __popc(__ballot_sync(0xffffffffu, kid > 0 && start < q0));
+            const int rank = before + __popc(starts & le_mask) - 1;    // rank among the pixels with hits
+            const int q = q0 + lane;
+            const bool valid = q < nq;
+            const int pl = valid ? w_tab[rank] : 0;
+            const int pstart = __shfl_sync(0xffffffffu, start, pl);
+            const int pt = __shfl_sync(0xffffffffu, t, pl);
+            const int pk0 = __shfl_sync(0xffffffffu, kprev, pl);
+            T pg = 0, ps = 0;
+            if (MODE == MODE_BWD) { pg = __shfl_sync(0xffffffffu, g, pl); ps = __shfl_sync(0xffffffffu, sft, pl); }
+            if (!valid) continue;
+            const int k = q - pstart;
+            const int cell = (ubase + pl) * KS + k;
+            const int f = s_ids[(int)s_celli[cell]];
+            const int lx = pt & 15, ly = pt >> 4;
+            const T x0 = (T)s_px[lx], y0 = (T)s_py[ly];
+            T p[6];
+            load_face_xy<T>(sp.img, vbase + f, sp.coord_mult, sp.premultiplied, p);
+            int edgeid;
+            const T d = soft_distance<T>(p, x0, y0, sp.pix_mult, edgeid);
+            const T prob = soft_prob<T>(d, sp.sigmainv, sp.pix_mult);
+            if (MODE == MODE_FWD) {
+              s_cell[cell] = prob;
+              if (sp.prob) {
+                const int64_t o = (((int64_t)b * geo.H + ry0 + ly) * geo.W + rx0 + lx) * K + pk0 + k;
+                sp.prob[o] = prob; sp.close_idx[o] = (int64_t)f; sp.dist_type[o] = (uint8_t)(edgeid + 1);
+              }
+            } else {
+              soft_backward_pair<T>(p, x0, y0, prob, edgeid, pg, ps, sp.sigmainv, sp.pix_mult,
+                                    sp.grad_img + (vbase + f) * 6);
+            }
+          }
         }
+        __syncthreads();
+        // -- D
+        if ((int)threadIdx.x < nsb) {
+          const int kid = s_knew[threadIdx.x];
+          if (MODE == MODE_FWD) {
+            const T* row = s_cell + threadIdx.x * KS;
+            T allprob = s_acc[sb0 + threadIdx.x];
+            for (int k = 0; k < kid; ++k) allprob = (T)((double)allprob * (1.0 - (double)row[k]));
+            s_acc[sb0 + threadIdx.x] = allprob;
+          }
+          s_ktot[sb0 + threadIdx.x] += kid;
+        }
+        __syncthreads();                                 // cells / s_knew are reused by the next super-batch
       }
     }
-    __syncthreads();
-    // -- D
-    if (MODE == MODE_FWD && (int)threadIdx.x < nsb) {
-      const int t = s_upix[sb0 + threadIdx.x];
-      const int64_t tpix = ((int64_t)b * geo.H + ry0 + (t >> 4)) * geo.W + rx0 + (t & 15);
-      const int kid = s_kid[threadIdx.x];
-      const T* row = s_cell + threadIdx.x * KS;
-      T allprob = (T)1.0;
-      for (int k = 0; k < kid; ++k) allprob = (T)((double)allprob * (1.0 - (double)row[k]));
-      sp.soft[tpix] = (T)(1.0 - (double)allprob);
-      if (sp.prob)
-        for (int k = kid; k < K; ++k) {
-          sp.prob[tpix * K + k] = (T)0; sp.close_idx[tpix * K + k] = -1; sp.dist_type[tpix * K + k] = 0;
-        }
-    }
-    if (sb0 + NPB < U) __syncthreads();                  // the cells are reused by the next super-batch
+    // ---- next pass?
+    if (hi >= nf - 1) break;
+    lo = hi;
+    if (__syncthreads_and((int)threadIdx.x >= U || s_ktot[threadIdx.x] >= K)) break;   // every list is full
+  }
+  __syncthreads();
+  if (MODE == MODE_FWD && (int)threadIdx.x < U) {
+    const int t = s_upix[threadIdx.x];
+    const int64_t tpix = ((int64_t)b * geo.H + ry0 + (t >> 4)) * geo.W + rx0 + (t & 15);
+    sp.soft[tpix] = (T)(1.0 - (double)s_acc[threadIdx.x]);
+    if (sp.prob)
+      for (int k = s_ktot[threadIdx.x]; k < K; ++k) {
+        sp.prob[tpix * K + k] = (T)0; sp.close_idx[tpix * K + k] = -1; sp.dist_type[tpix * K + k] = 0;
+      }
   }
 }
 
