@@ -35,6 +35,7 @@ def parse():
     ap.add_argument("--batch", type=int, default=None, help="override the per-rank batch of the workload")
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--e2e-chunks", type=int, default=1, help="view chunks of the pipelined end-to-end leg")
     return ap.parse_args()
 
 
@@ -140,10 +141,156 @@ KERNEL_ALGO = {  # algorithmic bytes of each kernel = the BASELINE.md §3 term i
     "raster_fwd": "raster_fwd", "raster_bwd": "raster_bwd", "soft_fwd": "soft_fwd", "soft_bwd": "soft_bwd"}
 
 
+class RenderWorkload:
+    """c1/c2/c3/c5: forward rasterize + dibr_soft_mask through the public API and backward of both outputs with
+    resident upstream gradients.  Every rank renders its own batch of views (weak scaling)."""
+
+    def __init__(self, args, rank, dev):
+        import torch
+        from kaolin_b200 import synth
+        self.torch = torch
+        d = synth.make_inputs(args.workload, batch=args.batch, seed_offset=rank * 100)
+        self.d, self.dev = d, dev
+        self.H, self.W = d["H"], d["W"]
+        # pinned host copies (the e2e leg copies these every step) and resident device copies (`value` leg)
+        self.h_z = d["face_vertices_z"].pin_memory()
+        self.h_img = d["face_vertices_image"].pin_memory()
+        self.h_feat = [f.contiguous().pin_memory() for f in d["face_features"]]
+        self.h_nz = None if d["face_normals_z"] is None else d["face_normals_z"].pin_memory()
+        self.B, self.F = self.h_z.shape[0], self.h_z.shape[1]
+        self.C = sum(f.shape[-1] for f in self.h_feat)
+        self.culling = self.h_nz is not None
+        g = torch.Generator().manual_seed(4242 + rank)
+        self.g_feats = [torch.rand(self.B, self.H, self.W, f.shape[-1], generator=g).to(dev) for f in self.h_feat]
+        self.g_soft = torch.rand(self.B, self.H, self.W, generator=g).to(dev)
+        self.d_z, self.d_img = self.h_z.to(dev), self.h_img.to(dev)
+        self.d_feat = [f.to(dev) for f in self.h_feat]
+        self.d_nz = None if self.h_nz is None else self.h_nz.to(dev)
+        self.h_loss = torch.zeros(1).pin_memory()
+        self.h2d = (self.h_z.numel() + self.h_img.numel() + sum(f.numel() for f in self.h_feat) +
+                    (0 if self.h_nz is None else self.h_nz.numel())) * 4
+        self.d2h = 4
+        # e2e pipeline: the batch is cut in view chunks; chunk i+1's host->device copies (copy stream) overlap
+        # chunk i's kernels (compute stream).  Views are independent, so this is the same public-API call made
+        # per chunk.
+        self.chunks = max(1, min(args.e2e_chunks, self.B))
+        self.copy_stream = torch.cuda.Stream(dev)
+        self.desc = {"per_gpu_batch": self.B, "faces": self.F, "height": self.H, "width": self.W,
+                     "channels": self.C, "knum": d["knum"], "sigmainv": d["sigmainv"],
+                     "sharding": "views across ranks, no data-path collective",
+                     "e2e_pipeline": "none (copies and kernels in order on one stream)" if self.chunks == 1 else
+                     f"{self.chunks} view chunks, H2D of chunk i+1 overlaps kernels of chunk i"}
+
+    def _step(self, z, img, feat, nz, g_feats, g_soft, loss=False):
+        import kaolin_b200 as kal
+        torch, d = self.torch, self.d
+        img = img.detach().requires_grad_(True)
+        feats = [f.detach().requires_grad_(True) for f in feat]
+        feats = feats if len(feats) > 1 else feats[0]
+        valid = None if nz is None else (nz >= 0.)
+        out, face_idx = kal.render.mesh.rasterize(self.H, self.W, z, img, feats, valid, d["multiplier"], d["eps"])
+        soft = kal.render.mesh.dibr_soft_mask(img, face_idx, d["sigmainv"], d["boxlen"], d["knum"], d["multiplier"])
+        outs = list(out) if isinstance(out, tuple) else [out]
+        torch.autograd.backward(outs + [soft], g_feats + [g_soft])
+        if loss:
+            fl = feats if isinstance(feats, list) else [feats]
+            return (img.grad.sum() + sum(f.grad.sum() for f in fl) + soft.sum()).reshape(1)
+        return None
+
+    def resident_step(self):
+        self._step(self.d_z, self.d_img, self.d_feat, self.d_nz, self.g_feats, self.g_soft)
+
+    def e2e_step(self):
+        torch, dev = self.torch, self.dev
+        if self.chunks == 1:                 # default: copies and kernels in order on the current stream
+            z, img = self.h_z.to(dev, non_blocking=True), self.h_img.to(dev, non_blocking=True)
+            feat = [f.to(dev, non_blocking=True) for f in self.h_feat]
+            nz = None if self.h_nz is None else self.h_nz.to(dev, non_blocking=True)
+            self.h_loss.copy_(self._step(z, img, feat, nz, self.g_feats, self.g_soft, loss=True), non_blocking=True)
+            return
+        cur = torch.cuda.current_stream(dev)
+        n = self.chunks
+        bounds = [(i * self.B // n, (i + 1) * self.B // n) for i in range(n)]
+        staged = []
+        self.copy_stream.wait_stream(cur)
+        with torch.cuda.stream(self.copy_stream):
+            for lo, hi in bounds:
+                t = (self.h_z[lo:hi].to(dev, non_blocking=True), self.h_img[lo:hi].to(dev, non_blocking=True),
+                     [f[lo:hi].to(dev, non_blocking=True) for f in self.h_feat],
+                     None if self.h_nz is None else self.h_nz[lo:hi].to(dev, non_blocking=True))
+                ev = torch.cuda.Event()
+                ev.record(self.copy_stream)
+                staged.append((t, ev))
+        total = None
+        for (lo, hi), ((z, img, feat, nz), ev) in zip(bounds, staged):
+            cur.wait_event(ev)
+            for t in [z, img] + feat + ([] if nz is None else [nz]):
+                t.record_stream(cur)
+            part = self._step(z, img, feat, nz, [g[lo:hi] for g in self.g_feats], self.g_soft[lo:hi], loss=True)
+            total = part if total is None else total + part
+        self.h_loss.copy_(total, non_blocking=True)
+
+    def pixels(self):
+        return self.B * self.H * self.W
+
+    def algorithmic_bytes(self):
+        from kaolin_b200 import synth
+        return synth.algorithmic_bytes(self.B, self.F, self.H, self.W, self.C, self.culling)
+
+
+class MultiViewWorkload:
+    """c4: multi-view DIB-R shape optimisation.  The mesh is replicated, the 128 cameras are sharded over the
+    ranks (weak scaling: `--batch` cameras per rank, default 128 // max(world, 1) ... per-rank views), one step =
+    prepare_vertices -> dibr_rasterization -> losses -> backward -> ONE all-reduce of vertices.grad -> Adam."""
+
+    def __init__(self, args, rank, world, dev):
+        import torch
+        from kaolin_b200 import multiview as mv
+        from kaolin_b200 import synth
+        self.torch = torch
+        cfg = synth.CONFIGS["c4"]
+        per_rank = args.batch or cfg["B"]
+        views = [(rank * per_rank + i) % cfg["B"] for i in range(per_rank)]
+        d = synth.make_inputs("c4", views=views)
+        self.d, self.dev = d, dev
+        self.H, self.W = d["H"], d["W"]
+        self.B, self.F, self.C, self.culling = per_rank, d["faces"].shape[0], 3, True
+        g = torch.Generator().manual_seed(77 + rank)
+        vcol = torch.rand(d["vertices"].shape[0], 3, generator=g)
+        self.h_rot, self.h_eye = d["rot"].contiguous().pin_memory(), d["eye"].contiguous().pin_memory()
+        tm = (torch.rand(per_rank, self.H, self.W, generator=g) > 0.5).float().to(dev)
+        tf = torch.rand(per_rank, self.H, self.W, 3, generator=g).to(dev)
+        self.opt = mv.MultiViewOptimizer(d["vertices"].to(dev), d["faces"].to(dev), vcol.to(dev), d["rot"].to(dev),
+                                         d["eye"].to(dev), tm, tf, self.H, self.W, per_rank * world,
+                                         sigmainv=d["sigmainv"], boxlen=d["boxlen"], knum=d["knum"])
+        self.h_loss = torch.zeros(1).pin_memory()
+        self.h2d = (self.h_rot.numel() + self.h_eye.numel()) * 4
+        self.d2h = 4
+        self.desc = {"per_gpu_batch": per_rank, "faces": self.F, "vertices": int(d["vertices"].shape[0]),
+                     "height": self.H, "width": self.W, "channels": 3, "knum": d["knum"], "sigmainv": d["sigmainv"],
+                     "sharding": "cameras across ranks; one NCCL sum all-reduce of vertices.grad per step",
+                     "step": "prepare_vertices + dibr_rasterization + mask-IoU/L1 losses + backward + all-reduce + Adam"}
+
+    def resident_step(self):
+        self.opt.step()
+
+    def e2e_step(self):
+        dev = self.dev
+        self.opt.rot = self.h_rot.to(dev, non_blocking=True)
+        self.opt.trans = self.h_eye.to(dev, non_blocking=True)
+        self.h_loss.copy_(self.opt.step().reshape(1), non_blocking=True)
+
+    def pixels(self):
+        return self.B * self.H * self.W
+
+    def algorithmic_bytes(self):
+        from kaolin_b200 import synth
+        return synth.algorithmic_bytes(self.B, self.F, self.H, self.W, self.C, self.culling)
+
+
 def gpu_run(args):
     import torch
     import torch.distributed as dist
-    import kaolin_b200 as kal
     from kaolin_b200 import _lib, synth
 
     world = int(os.environ.get("WORLD_SIZE", "1"))
@@ -155,40 +302,10 @@ def gpu_run(args):
         dist.init_process_group("nccl", device_id=dev)
     _lib.load()
 
-    d = synth.make_inputs(args.workload, batch=args.batch, seed_offset=rank * 100)
-    cfg = d["cfg"]
-    H, W = d["H"], d["W"]
-    # pinned host copies (the e2e leg copies these every step) and resident device copies (the `value` leg)
-    h_z = d["face_vertices_z"].pin_memory()
-    h_img = d["face_vertices_image"].pin_memory()
-    h_feat = [f.contiguous().pin_memory() for f in d["face_features"]]
-    h_nz = None if d["face_normals_z"] is None else d["face_normals_z"].pin_memory()
-    B, F, C = h_z.shape[0], h_z.shape[1], sum(f.shape[-1] for f in h_feat)
-    P = B * H * W
-    splits = [f.shape[-1] for f in d["face_features"]]
-    g = torch.Generator().manual_seed(4242 + rank)
-    g_feats = [torch.rand(B, H, W, c, generator=g).to(dev) for c in splits]
-    g_soft = torch.rand(B, H, W, generator=g).to(dev)
-    d_z, d_img, d_feat = h_z.to(dev), h_img.to(dev), [f.to(dev) for f in h_feat]
-    d_nz = None if h_nz is None else h_nz.to(dev)
+    cfg = synth.CONFIGS[args.workload]
+    wl = MultiViewWorkload(args, rank, world, dev) if args.workload == "c4" else RenderWorkload(args, rank, dev)
+    P = wl.pixels()
     flush = torch.empty(512 * 1024 * 1024, dtype=torch.uint8, device=dev)     # > 126 MB L2
-
-    def step(z, img, feat, nz, loss=False):
-        img = img.detach().requires_grad_(True)
-        if isinstance(feat, list):
-            feats = [f.detach().requires_grad_(True) for f in feat]
-            feats = feats if len(feats) > 1 else feats[0]
-        else:
-            feats = feat.detach().requires_grad_(True)
-        valid = None if nz is None else (nz >= 0.)
-        out, face_idx = kal.render.mesh.rasterize(H, W, z, img, feats, valid, d["multiplier"], d["eps"])
-        soft = kal.render.mesh.dibr_soft_mask(img, face_idx, d["sigmainv"], d["boxlen"], d["knum"], d["multiplier"])
-        outs = list(out) if isinstance(out, tuple) else [out]
-        torch.autograd.backward(outs + [soft], g_feats + [g_soft])
-        if loss:
-            fl = feats if isinstance(feats, list) else [feats]
-            return (img.grad.sum() + sum(f.grad.sum() for f in fl) + soft.sum()).reshape(1)
-        return None
 
     def barrier():
         if world > 1:
@@ -197,7 +314,7 @@ def gpu_run(args):
 
     def timed(fn, steps, per_kernel=None):
         """K steps, each bracketed by its own event pair; L2 is flushed (512 MB memset) between steps, outside
-        the pairs.  Returns total ms (max over ranks) and the per-step list."""
+        the pairs.  Returns total ms (max over ranks), the per-step list and the per-kernel list."""
         ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(steps)]
         kev = None
         if per_kernel is not None:
@@ -221,24 +338,14 @@ def gpu_run(args):
         kper = [a.elapsed_time(b) for a, b in kev] if kev is not None else None
         return float(tot.item()), per, kper
 
-    resident = lambda: step(d_z, d_img, d_feat, d_nz)                                       # noqa: E731
-    h_loss = torch.zeros(1).pin_memory()
-
-    def e2e_step():
-        z, img = h_z.to(dev, non_blocking=True), h_img.to(dev, non_blocking=True)
-        feat = [f.to(dev, non_blocking=True) for f in h_feat]
-        nz = None if h_nz is None else h_nz.to(dev, non_blocking=True)
-        h_loss.copy_(step(z, img, feat, nz, loss=True), non_blocking=True)
-    h2d = h_z.numel() * 4 + h_img.numel() * 4 + sum(f.numel() for f in h_feat) * 4 + \
-        (0 if h_nz is None else h_nz.numel() * 4)
-
     # ---- warm-up (also: which kernel dominates?)
-    for _ in range(max(args.warmup, 3)):
-        resident()
+    warm = max(args.warmup, 3)
+    for _ in range(warm):
+        wl.resident_step()
     torch.cuda.synchronize()
     kshare = {}
     for name in ("setup_count", "scan", "fill", "raster_fwd", "raster_bwd", "soft_fwd", "soft_bwd"):
-        _, _, kper = timed(resident, 3, per_kernel=_lib.KERNEL_IDS[name])
+        _, _, kper = timed(wl.resident_step, 3, per_kernel=_lib.KERNEL_IDS[name])
         kshare[name] = statistics.median(kper)
     dominant = max(KERNEL_ALGO, key=lambda k: kshare[k])
 
@@ -247,11 +354,11 @@ def gpu_run(args):
     if rank == 0:
         sampler.start()
     n0 = _lib.kernel_launch_count()
-    total_ms, per, kper = timed(resident, args.steps, per_kernel=_lib.KERNEL_IDS[dominant])
+    total_ms, per, kper = timed(wl.resident_step, args.steps, per_kernel=_lib.KERNEL_IDS[dominant])
     launches = _lib.kernel_launch_count() - n0
     for _ in range(2):
-        e2e_step()
-    e2e_ms, _, _ = timed(e2e_step, args.steps)
+        wl.e2e_step()
+    e2e_ms, _, _ = timed(wl.e2e_step, args.steps)
     clocks = sampler.stop() if rank == 0 else None
 
     if rank == 0:
@@ -264,24 +371,25 @@ def gpu_run(args):
         except Exception:
             pass
         peak = float(peaks.get("hbm_gbs", 6650.0))
-        algo = synth.algorithmic_bytes(B, F, H, W, C, h_nz is not None)
+        algo = wl.algorithmic_bytes()
         kms = statistics.mean(kper)
         achieved = algo[KERNEL_ALGO[dominant]] / (kms * 1e-3) / 1e9
         traffic = None
-        try:
+        try:       # ncu `--set full` DRAM bytes of that kernel, one launch of the nominal per-GPU batch
             traffic = json.load(open(os.path.join(ROOT, "profiles", "traffic.json"))).get(args.workload, {}).get(dominant)
+            if traffic is not None and args.batch and args.batch != cfg["B"]:
+                traffic = traffic * args.batch / cfg["B"]
         except Exception:
             pass
+        config = {"workload": f"{args.workload}: {cfg['desc']}",
+                  "l2": "512 MB memset between timed steps (outside the per-step event pairs)"}
+        config.update(wl.desc)
         line = {
             "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
-            "warmup": max(args.warmup, 3), "ms_per_step": ms, "higher_is_better": True, "scaling": "weak",
-            "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-            "config": {"workload": f"{args.workload}: {cfg['desc']}", "per_gpu_batch": B, "faces": F, "height": H,
-                       "width": W, "channels": C, "knum": d["knum"], "sigmainv": d["sigmainv"],
-                       "l2": "512 MB memset between timed steps (outside the per-step event pairs)",
-                       "sharding": "views across ranks, no data-path collective"},
-            "images_per_s": world * B / (ms * 1e-3),
-            "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": 4,
+            "warmup": warm, "ms_per_step": ms, "higher_is_better": True, "scaling": "weak",
+            "vs_baseline": None, "dtype": "f32", "data": "synthetic", "config": config,
+            "images_per_s": world * wl.B / (ms * 1e-3),
+            "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": wl.h2d, "d2h_bytes_per_step": wl.d2h,
                     "ms_per_step": e2e_ms / args.steps},
             "gpu_launches": int(launches),
             "roofline": {"bound": "hbm", "kernel": dominant, "achieved": achieved, "peak": peak, "unit": "GB/s",
@@ -291,7 +399,8 @@ def gpu_run(args):
                          "whole_step": {"algorithmic_bytes": algo["total"],
                                         "achieved": algo["total"] / (ms * 1e-3) / 1e9,
                                         "frac": algo["total"] / (ms * 1e-3) / 1e9 / peak},
-                         "kernel_ms_all": kshare},
+                         "kernel_ms_all": kshare,
+                         "note": "the kernels are instruction-issue bound, not HBM bound (DESIGN.md §5)"},
             "clocks": clocks,
         }
         if world == 1 and not args.no_cpu_baseline:

@@ -48,11 +48,14 @@ class DibrSoftMaskCuda(Function):
         ctx.boxlen = boxlen
         ctx.knum = knum
         ctx.save_for_backward(soft_mask, face_vertices_image, selected_face_idx)
+        ctx.set_materialize_grads(False)
         return soft_mask
 
     @staticmethod
     def backward(ctx, grad_soft_mask):
         fn = "dibr_soft_mask_backward_cuda"
+        if grad_soft_mask is None:
+            return None, None, None, None, None, None
         soft_mask, face_vertices_image, selected_face_idx = ctx.saved_tensors
         dev = face_vertices_image.device
         b, f = face_vertices_image.shape[0], face_vertices_image.shape[1]

@@ -181,12 +181,15 @@ class RasterizeCuda(Function):
         _lib.check(code, fn)
         ctx.save_for_backward(face_idx, face_vertices_image, face_features)
         ctx.mark_non_differentiable(face_idx)
+        ctx.set_materialize_grads(False)      # an unused output costs nothing (no zero-filled (B,H,W,C) gradient)
         ctx.eps = eps
         ctx.multiplier = multiplier
         return interpolated_features, face_idx
 
     @staticmethod
     def backward(ctx, grad_interpolated_features, grad_face_idx):
+        if grad_interpolated_features is None:
+            return None, None, None, None, None, None, None, None, None
         face_idx, face_vertices_image, face_features = ctx.saved_tensors
         gi, gf = _rasterize_backward(grad_interpolated_features.contiguous(), face_idx, None,
                                      face_vertices_image, face_features, ctx.multiplier, ctx.eps)
@@ -238,6 +241,7 @@ class RasterizeCudaList(Function):
         _lib.check(code, fn)
         ctx.save_for_backward(face_idx, face_vertices_image, *feats)
         ctx.mark_non_differentiable(face_idx)
+        ctx.set_materialize_grads(False)      # gradients of unused outputs arrive as None
         ctx.eps = eps
         ctx.multiplier = multiplier
         ctx.out_shapes = [tuple(o.shape) for o in outs]
@@ -246,6 +250,8 @@ class RasterizeCudaList(Function):
     @staticmethod
     def backward(ctx, *grads):
         fn = "rasterize_backward_cuda"
+        if all(g is None for g in grads[:-1]):
+            return (None,) * (7 + len(grads) - 1)
         face_idx, face_vertices_image = ctx.saved_tensors[:2]
         feats = list(ctx.saved_tensors[2:])
         dev = face_vertices_image.device

@@ -245,3 +245,54 @@ def test_knum_truncation_dense(kal, O, ref_C):
     d["face_vertices_image"] = (d["face_vertices_image"] * 0.5).contiguous()     # crowd the centre, empty border
     for knum in (1, 7, 30):
         full_pipeline_check(kal, O, ref_C, d, knum=knum, boxlen=0.05)
+
+
+# ----------------------------------------------------------------------------- binning levels / dense tiles
+@pytest.mark.parametrize("Hh,Ww,scale", [(200, 328, 0.25), (320, 200, 0.9), (600, 600, 2.5)])
+def test_binning_levels_vs_ref_C(kal, O, ref_C, Hh, Ww, scale):
+    """Faces of 40..700 pixels on images of several hundred pixels: fine tile lists, coarse (4x4-tile) cell lists
+    and the per-view large list are all populated; enlarged soft-mask boxes push more faces up one level."""
+    d = random_soup(2, 160, scale, seed=Hh + Ww)
+    d.update(H=Hh, W=Ww)
+    full_pipeline_check(kal, O, ref_C, d, knum=12, boxlen=0.04)
+
+
+def test_dense_tile_multi_pass_vs_ref_C(kal, O, ref_C):
+    """More than 2048 candidate faces in one 16x16 tile (config-5 regime): the soft-mask kernel consumes them in
+    several face-index ranges; k-lists (knum larger than the hits of some pixels, smaller than others), side
+    buffers and gradients must match the reference's single in-order scan."""
+    g = torch.Generator().manual_seed(99)
+    F = 6000
+    ctr = torch.rand(1, F, 1, 2, generator=g) * 0.9 - 0.45
+    img = ctr + (torch.rand(1, F, 3, 2, generator=g) - 0.5) * 0.12
+    img[:, :, :, 0] += 0.35                                     # leave the left part of the image uncovered
+    z = -1.0 - 2 * torch.rand(1, F, 3, generator=g)
+    feat = torch.rand(1, F, 3, 2, generator=g)
+    d = dict(face_vertices_z=z.cuda(), face_vertices_image=img.cuda(), face_features=[feat.cuda()],
+             face_normals_z=None, H=40, W=40)
+    for knum in (30, 3000):
+        full_pipeline_check(kal, O, ref_C, d, knum=knum, boxlen=0.3)
+
+
+def test_unused_outputs_cost_no_gradient(kal):
+    """Only one of the outputs feeds the loss: the other's gradient is None (no zero-filled tensors), results equal
+    the both-outputs run with a zero upstream gradient."""
+    d = random_soup(2, 200, 0.5, seed=3)
+    z, img0, feat0, nz = d["face_vertices_z"], d["face_vertices_image"], d["face_features"][0], d["face_normals_z"]
+    img = img0.clone().requires_grad_(True)
+    feat = feat0.clone().requires_grad_(True)
+    out, soft, idx = kal.render.mesh.dibr_rasterization(48, 56, z, img, feat, nz)
+    soft.sum().backward()
+    assert feat.grad is None and torch.isfinite(img.grad).all() and img.grad.abs().sum() > 0
+    g_soft_only = img.grad.clone()
+    img2 = img0.clone().requires_grad_(True)
+    feat2 = feat0.clone().requires_grad_(True)
+    out2, soft2, _ = kal.render.mesh.dibr_rasterization(48, 56, z, img2, feat2, nz)
+    (soft2.sum() + (out2 * 0).sum()).backward()
+    assert torch.allclose(img2.grad, g_soft_only, rtol=1e-5, atol=1e-6)
+    assert feat2.grad is not None and torch.all(feat2.grad == 0)
+    img3 = img0.clone().requires_grad_(True)
+    (o_a, o_b), _ = kal.render.mesh.rasterize(48, 56, z, img3, [feat0[..., :1].contiguous().requires_grad_(True),
+                                                              feat0[..., 1:].contiguous()], nz >= 0)
+    o_a.sum().backward()
+    assert torch.isfinite(img3.grad).all()
