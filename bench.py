@@ -35,7 +35,8 @@ def parse():
     ap.add_argument("--batch", type=int, default=None, help="override the per-rank batch of the workload")
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
-    ap.add_argument("--e2e-chunks", type=int, default=1, help="view chunks of the pipelined end-to-end leg")
+    ap.add_argument("--graphs", type=int, default=1,
+                    help="1: replay the step from a CUDA graph captured over the public API calls; 0: eager launches")
     return ap.parse_args()
 
 
@@ -170,16 +171,13 @@ class RenderWorkload:
         self.h2d = (self.h_z.numel() + self.h_img.numel() + sum(f.numel() for f in self.h_feat) +
                     (0 if self.h_nz is None else self.h_nz.numel())) * 4
         self.d2h = 4
-        # e2e pipeline: the batch is cut in view chunks; chunk i+1's host->device copies (copy stream) overlap
-        # chunk i's kernels (compute stream).  Views are independent, so this is the same public-API call made
-        # per chunk.
-        self.chunks = max(1, min(args.e2e_chunks, self.B))
-        self.copy_stream = torch.cuda.Stream(dev)
+        self.copy_stream = torch.cuda.Stream(dev)      # uploads of the end-to-end leg (see e2e_run)
         self.desc = {"per_gpu_batch": self.B, "faces": self.F, "height": self.H, "width": self.W,
                      "channels": self.C, "knum": d["knum"], "sigmainv": d["sigmainv"],
                      "sharding": "views across ranks, no data-path collective",
-                     "e2e_pipeline": "none (copies and kernels in order on one stream)" if self.chunks == 1 else
-                     f"{self.chunks} view chunks, H2D of chunk i+1 overlaps kernels of chunk i"}
+                     "e2e_pipeline": "double-buffered: the H2D copy of step i+1 (copy stream) overlaps the kernels of "
+                                     "step i; all copies and result reads are inside the timed region; no L2 flush "
+                                     "in this leg (per-step working set of outputs + gradients exceeds L2)"}
 
     def _step(self, z, img, feat, nz, g_feats, g_soft, loss=False):
         import kaolin_b200 as kal
@@ -200,35 +198,59 @@ class RenderWorkload:
     def resident_step(self):
         self._step(self.d_z, self.d_img, self.d_feat, self.d_nz, self.g_feats, self.g_soft)
 
-    def e2e_step(self):
+    # ---- end-to-end leg: a double-buffered input pipeline.  Every step's inputs are copied from pinned host
+    #      memory into one of two persistent device buffer sets on a copy stream while the compute stream renders
+    #      the previous step from the other set; every step's scalar result is read back to pinned host memory.
+    def e2e_prepare(self, use_graphs):
         torch, dev = self.torch, self.dev
-        if self.chunks == 1:                 # default: copies and kernels in order on the current stream
-            z, img = self.h_z.to(dev, non_blocking=True), self.h_img.to(dev, non_blocking=True)
-            feat = [f.to(dev, non_blocking=True) for f in self.h_feat]
-            nz = None if self.h_nz is None else self.h_nz.to(dev, non_blocking=True)
-            self.h_loss.copy_(self._step(z, img, feat, nz, self.g_feats, self.g_soft, loss=True), non_blocking=True)
-            return
+        self.stage = [(torch.empty_like(self.d_z), torch.empty_like(self.d_img),
+                       [torch.empty_like(f) for f in self.d_feat],
+                       None if self.d_nz is None else torch.empty_like(self.d_nz)) for _ in range(2)]
+        self.copied = [torch.cuda.Event() for _ in range(2)]
+        self.computed = [torch.cuda.Event() for _ in range(2)]
+        self.e2e_fns = []
+        for z, img, feat, nz in self.stage:
+            z.copy_(self.d_z); img.copy_(self.d_img)
+            for a, b in zip(feat, self.d_feat):
+                a.copy_(b)
+            if nz is not None:
+                nz.copy_(self.d_nz)
+            fn = (lambda z=z, img=img, feat=feat, nz=nz:
+                  self._step(z, img, feat, nz, self.g_feats, self.g_soft, loss=True))
+            if use_graphs:
+                from kaolin_b200.graphs import GraphedStep
+                fn = GraphedStep(fn)
+            self.e2e_fns.append(fn)
+
+    def _upload(self, s):
+        z, img, feat, nz = self.stage[s]
+        z.copy_(self.h_z, non_blocking=True)
+        img.copy_(self.h_img, non_blocking=True)
+        for fd, fh in zip(feat, self.h_feat):
+            fd.copy_(fh, non_blocking=True)
+        if nz is not None:
+            nz.copy_(self.h_nz, non_blocking=True)
+
+    def e2e_run(self, steps):
+        """Enqueue `steps` pipelined end-to-end steps (the caller brackets them with events)."""
+        torch, dev = self.torch, self.dev
         cur = torch.cuda.current_stream(dev)
-        n = self.chunks
-        bounds = [(i * self.B // n, (i + 1) * self.B // n) for i in range(n)]
-        staged = []
-        self.copy_stream.wait_stream(cur)
-        with torch.cuda.stream(self.copy_stream):
-            for lo, hi in bounds:
-                t = (self.h_z[lo:hi].to(dev, non_blocking=True), self.h_img[lo:hi].to(dev, non_blocking=True),
-                     [f[lo:hi].to(dev, non_blocking=True) for f in self.h_feat],
-                     None if self.h_nz is None else self.h_nz[lo:hi].to(dev, non_blocking=True))
-                ev = torch.cuda.Event()
-                ev.record(self.copy_stream)
-                staged.append((t, ev))
-        total = None
-        for (lo, hi), ((z, img, feat, nz), ev) in zip(bounds, staged):
-            cur.wait_event(ev)
-            for t in [z, img] + feat + ([] if nz is None else [nz]):
-                t.record_stream(cur)
-            part = self._step(z, img, feat, nz, [g[lo:hi] for g in self.g_feats], self.g_soft[lo:hi], loss=True)
-            total = part if total is None else total + part
-        self.h_loss.copy_(total, non_blocking=True)
+        cs = self.copy_stream
+        cs.wait_stream(cur)
+        with torch.cuda.stream(cs):
+            self._upload(0)
+            self.copied[0].record(cs)
+        for i in range(steps):
+            s = i & 1
+            if i + 1 < steps:                       # upload of step i+1 overlaps the kernels of step i
+                with torch.cuda.stream(cs):
+                    if i >= 1:
+                        cs.wait_event(self.computed[1 - s])      # step i-1 is done with that buffer set
+                    self._upload(1 - s)
+                    self.copied[1 - s].record(cs)
+            cur.wait_event(self.copied[s])
+            self.h_loss.copy_(self.e2e_fns[s](), non_blocking=True)
+            self.computed[s].record(cur)
 
     def pixels(self):
         return self.B * self.H * self.W
@@ -274,11 +296,15 @@ class MultiViewWorkload:
     def resident_step(self):
         self.opt.step()
 
-    def e2e_step(self):
+    def e2e_prepare(self, use_graphs):
+        pass
+
+    def e2e_run(self, steps):
         dev = self.dev
-        self.opt.rot = self.h_rot.to(dev, non_blocking=True)
-        self.opt.trans = self.h_eye.to(dev, non_blocking=True)
-        self.h_loss.copy_(self.opt.step().reshape(1), non_blocking=True)
+        for _ in range(steps):      # inputs of a step = the shard's camera matrices; result = the loss
+            self.opt.rot = self.h_rot.to(dev, non_blocking=True)
+            self.opt.trans = self.h_eye.to(dev, non_blocking=True)
+            self.h_loss.copy_(self.opt.step().reshape(1), non_blocking=True)
 
     def pixels(self):
         return self.B * self.H * self.W
@@ -349,16 +375,55 @@ def gpu_run(args):
         kshare[name] = statistics.median(kper)
     dominant = max(KERNEL_ALGO, key=lambda k: kshare[k])
 
+    # ---- launch mode: the same public-API calls, replayed from a CUDA graph (one launch per step) or eager
+    n0 = _lib.kernel_launch_count()
+    wl.resident_step()
+    launches_per_step = _lib.kernel_launch_count() - n0
+    torch.cuda.synchronize()
+    resident_fn, graph_note, use_graphs = wl.resident_step, "eager launches", False
+    if args.graphs and args.workload != "c4":
+        try:
+            from kaolin_b200.graphs import GraphedStep
+            resident_fn = GraphedStep(wl.resident_step)
+            wl.e2e_prepare(True)
+            use_graphs = True
+            graph_note = "CUDA graph replay of the public-API step (captured once)"
+        except Exception as exc:        # launch mode only — the kernels are the same either way
+            torch.cuda.synchronize()
+            resident_fn = wl.resident_step
+            graph_note = f"eager launches (graph capture failed: {type(exc).__name__}: {str(exc)[:120]})"
+    elif args.workload == "c4":
+        graph_note = "eager launches (optimizer step + NCCL all-reduce are not captured)"
+    if not use_graphs:
+        wl.e2e_prepare(False)
+
+    def timed_region(run, steps):
+        """`steps` steps enqueued by run(steps), bracketed by ONE event pair and a barrier + synchronize on both
+        sides; max over ranks."""
+        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        barrier()
+        a.record()
+        run(steps)
+        b.record()
+        barrier()
+        tot = torch.tensor([a.elapsed_time(b)], dtype=torch.float64, device=dev)
+        if world > 1:
+            dist.all_reduce(tot, op=dist.ReduceOp.MAX)
+        return float(tot.item())
+
     # ---- the timed region
     sampler = ClockSampler(local_rank)
     if rank == 0:
         sampler.start()
-    n0 = _lib.kernel_launch_count()
-    total_ms, per, kper = timed(wl.resident_step, args.steps, per_kernel=_lib.KERNEL_IDS[dominant])
-    launches = _lib.kernel_launch_count() - n0
     for _ in range(2):
-        wl.e2e_step()
-    e2e_ms, _, _ = timed(wl.e2e_step, args.steps)
+        resident_fn()
+    total_ms, per, _ = timed(resident_fn, args.steps)
+    launches = launches_per_step * args.steps
+    wl.e2e_run(3)
+    e2e_ms = timed_region(wl.e2e_run, args.steps)
+    # the dominant kernel's own duration: CUDA events recorded around its launch inside the library (eager
+    # launches of the same step; the kernel does not depend on the launch mode)
+    _, _, kper = timed(wl.resident_step, args.steps, per_kernel=_lib.KERNEL_IDS[dominant])
     clocks = sampler.stop() if rank == 0 else None
 
     if rank == 0:
@@ -384,6 +449,7 @@ def gpu_run(args):
         config = {"workload": f"{args.workload}: {cfg['desc']}",
                   "l2": "512 MB memset between timed steps (outside the per-step event pairs)"}
         config.update(wl.desc)
+        config["launch_mode"] = graph_note
         line = {
             "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
             "warmup": warm, "ms_per_step": ms, "higher_is_better": True, "scaling": "weak",

@@ -235,8 +235,19 @@ int soft_mask_impl(const T* img, const T* bbox_in, const int64_t* face_idx, int 
   p.close_idx = close_idx; p.dist_type = dist_type; p.grad_soft = grad_soft; p.soft_in = soft_in;
   p.grad_img = grad_img;
   const size_t smem = SoftSmem<T>::total;
-  CUDA_TRY(cudaFuncSetAttribute(soft_mask_kernel<T, MODE>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                (int)smem));
+  {
+    // once per device and instantiation: not a stream operation, kept out of the per-call path so that the
+    // entry points can be captured into CUDA graphs
+    static std::atomic<unsigned long long> done{0};
+    int dev = 0;
+    CUDA_TRY(cudaGetDevice(&dev));
+    const unsigned long long bit = 1ull << (dev & 63);
+    if (!(done.load(std::memory_order_acquire) & bit)) {
+      CUDA_TRY(cudaFuncSetAttribute(soft_mask_kernel<T, MODE>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                    (int)smem));
+      done.fetch_or(bit, std::memory_order_release);
+    }
+  }
   {
     ProfScope ps(MODE == MODE_FWD ? DIBR_KERNEL_SOFT_FWD : DIBR_KERNEL_SOFT_BWD, s);
     soft_mask_kernel<T, MODE><<<(unsigned)(B * geo.tiles_per_view), 256, smem, s>>>(p, fl, geo, L);
