@@ -9,6 +9,7 @@
 #include <atomic>
 #include <cstdio>
 #include <cstring>
+#include <cstdlib>
 
 using namespace dibr;
 
@@ -203,6 +204,37 @@ int rasterize_bwd_impl(const T* const* grad_outs, const int64_t* face_idx, const
   return DIBR_OK;
 }
 
+inline int soft_threads_default() {
+  static const int nt = [] {
+    const char* e = getenv("DIBR_SOFT_NT");
+    const int v = e ? atoi(e) : 0;
+    return (v == 64 || v == 128 || v == 256) ? v : 128;
+  }();
+  return nt;
+}
+
+template <typename T, int MODE, int NT>
+int launch_soft(const SoftParams<T>& p, const FaceLayout& fl, const Geometry& geo, const BinLists& L, unsigned grid,
+                int kernel_id, cudaStream_t s) {
+  const size_t smem = SoftSmem<T, NT>::total;
+  {
+    // once per device and instantiation: not a stream operation, kept out of the per-call path so that the
+    // entry points can be captured into CUDA graphs
+    static std::atomic<unsigned long long> done{0};
+    int dev = 0;
+    CUDA_TRY(cudaGetDevice(&dev));
+    const unsigned long long bit = 1ull << (dev & 63);
+    if (!(done.load(std::memory_order_acquire) & bit)) {
+      CUDA_TRY(cudaFuncSetAttribute(soft_mask_kernel<T, MODE, NT>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                    (int)smem));
+      done.fetch_or(bit, std::memory_order_release);
+    }
+  }
+  ProfScope ps(kernel_id, s);
+  soft_mask_kernel<T, MODE, NT><<<grid, NT, smem, s>>>(p, fl, geo, L);
+  return DIBR_OK;
+}
+
 template <typename T, int MODE>
 int soft_mask_impl(const T* img, const T* bbox_in, const int64_t* face_idx, int B, int F, int H, int W,
                    float sigmainv, int knum, T coord_mult, int premultiplied, T margin, float pix_mult,
@@ -234,23 +266,17 @@ int soft_mask_impl(const T* img, const T* bbox_in, const int64_t* face_idx, int 
   p.sigmainv = sigmainv; p.F = F; p.knum = knum; p.face_idx = face_idx; p.soft = soft; p.prob = prob;
   p.close_idx = close_idx; p.dist_type = dist_type; p.grad_soft = grad_soft; p.soft_in = soft_in;
   p.grad_img = grad_img;
-  const size_t smem = SoftSmem<T>::total;
-  {
-    // once per device and instantiation: not a stream operation, kept out of the per-call path so that the
-    // entry points can be captured into CUDA graphs
-    static std::atomic<unsigned long long> done{0};
-    int dev = 0;
-    CUDA_TRY(cudaGetDevice(&dev));
-    const unsigned long long bit = 1ull << (dev & 63);
-    if (!(done.load(std::memory_order_acquire) & bit)) {
-      CUDA_TRY(cudaFuncSetAttribute(soft_mask_kernel<T, MODE>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                    (int)smem));
-      done.fetch_or(bit, std::memory_order_release);
-    }
-  }
-  {
-    ProfScope ps(MODE == MODE_FWD ? DIBR_KERNEL_SOFT_FWD : DIBR_KERNEL_SOFT_BWD, s);
-    soft_mask_kernel<T, MODE><<<(unsigned)(B * geo.tiles_per_view), 256, smem, s>>>(p, fl, geo, L);
+  const unsigned grid = (unsigned)(B * geo.tiles_per_view);
+  const int kid = MODE == MODE_FWD ? DIBR_KERNEL_SOFT_FWD : DIBR_KERNEL_SOFT_BWD;
+  // threads per CTA (one CTA per tile either way): fp32 uses small CTAs (more resident tiles per SM hide the
+  // barrier-separated phases); DIBR_SOFT_NT=64|128|256 overrides for experiments.  fp64: 256.
+  int nt = sizeof(T) == 4 ? soft_threads_default() : 256;
+  if (sizeof(T) == 4 && nt == 64) {
+    if (int e = launch_soft<T, MODE, 64>(p, fl, geo, L, grid, kid, s)) return e;
+  } else if (sizeof(T) == 4 && nt == 128) {
+    if (int e = launch_soft<T, MODE, 128>(p, fl, geo, L, grid, kid, s)) return e;
+  } else {
+    if (int e = launch_soft<T, MODE, 256>(p, fl, geo, L, grid, kid, s)) return e;
   }
   LAUNCH_CHECK("soft_mask_kernel");
   return DIBR_OK;

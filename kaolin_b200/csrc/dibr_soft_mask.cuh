@@ -112,18 +112,23 @@ __device__ __forceinline__ void soft_visit(const SoftParams<T>& sp, SoftPixel<T,
 // Shared-memory plan (dynamic): sorted candidate ids, their tile-local coverage masks, the compacted
 // uncovered pixels and, per warp, CELLS k-list cells (a cell first holds the candidate slot of a
 // (pixel, k) pair, then — forward — its probability) plus small per-batch tables.
-constexpr int CELLS = 1024;        // k-list cells per warp: a batch is min(32, CELLS / knum) pixels
 template <typename T> struct CellInt;
 template <> struct CellInt<float> { typedef unsigned type; };
 template <> struct CellInt<double> { typedef unsigned long long type; };
-template <typename T>
+// NT = threads per CTA (64 / 128 / 256; one CTA per tile whatever NT).  Small CTAs keep more independent tiles
+// resident per SM, which matters because the per-tile phases are separated by barriers and rarely have work
+// for 8 warps (ncu: barrier stalls dominated the 256-thread version).
+template <typename T, int NT>
 struct SoftSmem {
+  static constexpr int NW = NT / 32;
+  static constexpr int CAP = (NT >= 256) ? 2048 : 1024;   // candidate faces per pass
+  static constexpr int CELLS_TOT = NT * 32;               // k-list cells: a super-batch is min(NT, CELLS_TOT / knum) pixels
   static constexpr size_t ids = 0;
-  static constexpr size_t mask = ids + (SOFT_CAP + 8) * sizeof(int);   // + INT_MAX padding of the rank sort
-  static constexpr size_t cell = mask + (SOFT_CAP + 8) * sizeof(unsigned);
-  static constexpr size_t upix = cell + 8 * CELLS * sizeof(T);
+  static constexpr size_t mask = ids + (CAP + 8) * sizeof(int);      // + INT_MAX padding of the rank sort
+  static constexpr size_t cell = mask + (CAP + 8) * sizeof(unsigned);
+  static constexpr size_t upix = cell + CELLS_TOT * sizeof(T);
   static constexpr size_t wtab = upix + 256 * sizeof(int);
-  static constexpr size_t ktot = wtab + 8 * 32 * sizeof(int);
+  static constexpr size_t ktot = wtab + NW * 32 * sizeof(int);
   static constexpr size_t knew = ktot + 256 * sizeof(int);
   static constexpr size_t acc = knew + 256 * sizeof(int);
   static constexpr size_t total = acc + 256 * sizeof(T);
@@ -131,16 +136,17 @@ struct SoftSmem {
 
 // Number of the tile's candidates (tile list + "large" faces touching the tile) with lo < id <= hi.
 // CTA-wide; `scratch` = 9 ints.  Used only by the multi-pass selection of very dense tiles.
+template <int NT>
 __device__ __forceinline__ int count_candidates(const TileLists& tl, const uint2* ranges, const int lo,
                                                 const int hi, const int rx0, const int ry0, const int rx1,
                                                 const int ry1, int* scratch) {
   int c = 0;
-  for (int k = threadIdx.x; k < tl.n_fine; k += 256) {
+  for (int k = threadIdx.x; k < tl.n_fine; k += NT) {
     const int f = tl.fine[k];
     c += (f > lo && f <= hi) ? 1 : 0;
   }
   const int n_filt = tl.n_filtered();
-  for (int k = threadIdx.x; k < n_filt; k += 256) {
+  for (int k = threadIdx.x; k < n_filt; k += NT) {
     const int f = tl.filtered_at(k);
     if (f > lo && f <= hi && range_hits_rect(ranges[f], rx0, ry0, rx1, ry1)) ++c;
   }
@@ -151,18 +157,18 @@ __device__ __forceinline__ int count_candidates(const TileLists& tl, const uint2
   __syncthreads();
   int tot = 0;
 #pragma unroll
-  for (int w = 0; w < 8; ++w) tot += scratch[w];
+  for (int w = 0; w < NT / 32; ++w) tot += scratch[w];
   return tot;
 }
 
-// Each thread ranks Q of the ids (k = tid + q*256); see the call site.
-template <int Q>
+// Each thread ranks Q of the ids (k = tid + q*NT); see the call site.
+template <int Q, int NT>
 __device__ __forceinline__ void rank_sort(int* s_ids, const int count) {
   int mine[Q], rank[Q];
   bool any = false;
 #pragma unroll
   for (int q = 0; q < Q; ++q) {
-    const int k = threadIdx.x + q * 256;
+    const int k = threadIdx.x + q * NT;
     mine[q] = (k < count) ? s_ids[k] : 0x7fffffff;
     rank[q] = 0;
     any |= k < count;
@@ -180,65 +186,77 @@ __device__ __forceinline__ void rank_sort(int* s_ids, const int count) {
   __syncthreads();
 #pragma unroll
   for (int q = 0; q < Q; ++q)
-    if (threadIdx.x + q * 256 < count) s_ids[rank[q]] = mine[q];
+    if (threadIdx.x + q * NT < count) s_ids[rank[q]] = mine[q];
   __syncthreads();
 }
 
 // bits lo..hi (inclusive, 0 <= lo <= hi <= 15)
 __device__ __forceinline__ unsigned bit_span16(int lo, int hi) { return ((2u << hi) - 1u) & ~((1u << lo) - 1u); }
 
-template <typename T, int MODE>
-__global__ void __launch_bounds__(256, (sizeof(T) == 4 ? 4 : 2)) soft_mask_kernel(SoftParams<T> sp, FaceLayout fl, Geometry geo,
-                                                        BinLists L) {
+template <typename T, int MODE, int NT>
+__global__ void __launch_bounds__(NT, (sizeof(T) == 4 ? 1024 / NT : 512 / NT))
+soft_mask_kernel(SoftParams<T> sp, FaceLayout fl, Geometry geo, BinLists L) {
   typedef typename CellInt<T>::type cell_int;
+  typedef SoftSmem<T, NT> SM;
+  constexpr int NW = NT / 32, CAP = SM::CAP, CELLS_TOT = SM::CELLS_TOT;
   extern __shared__ __align__(16) unsigned char smem_raw[];
-  int* s_ids = reinterpret_cast<int*>(smem_raw + SoftSmem<T>::ids);            // [SOFT_CAP] sorted candidate faces
-  unsigned* s_mask = reinterpret_cast<unsigned*>(smem_raw + SoftSmem<T>::mask); // [SOFT_CAP] col bits | row bits << 16
-  T* s_cell = reinterpret_cast<T*>(smem_raw + SoftSmem<T>::cell);              // [8][CELLS]
-  int* s_upix = reinterpret_cast<int*>(smem_raw + SoftSmem<T>::upix);          // [256] thread index of uncovered px
-  int* s_wtab = reinterpret_cast<int*>(smem_raw + SoftSmem<T>::wtab);          // [8][32] per-warp owner tables
-  int* s_ktot = reinterpret_cast<int*>(smem_raw + SoftSmem<T>::ktot);          // [256] hits so far per uncovered px
-  int* s_knew = reinterpret_cast<int*>(smem_raw + SoftSmem<T>::knew);          // [256] new hits (this pass, super-batch)
-  T* s_acc = reinterpret_cast<T*>(smem_raw + SoftSmem<T>::acc);                // [256] running product of (1 - prob)
-  __shared__ int scratch[9];
+  int* s_ids = reinterpret_cast<int*>(smem_raw + SM::ids);              // [CAP] sorted candidate faces
+  unsigned* s_mask = reinterpret_cast<unsigned*>(smem_raw + SM::mask);  // [CAP] col bits | row bits << 16
+  T* s_cell = reinterpret_cast<T*>(smem_raw + SM::cell);                // [CELLS_TOT] k-list cells
+  int* s_upix = reinterpret_cast<int*>(smem_raw + SM::upix);            // [256] tile-local index of uncovered px
+  int* s_wtab = reinterpret_cast<int*>(smem_raw + SM::wtab);            // [NW][32] per-warp owner tables
+  int* s_ktot = reinterpret_cast<int*>(smem_raw + SM::ktot);            // [256] hits so far per uncovered px
+  int* s_knew = reinterpret_cast<int*>(smem_raw + SM::knew);            // [256] new hits (this pass, super-batch)
+  T* s_acc = reinterpret_cast<T*>(smem_raw + SM::acc);                  // [256] running product of (1 - prob)
+  __shared__ int scratch[10];                                           // [0..7] warp sums, [8] append cursor, [9] U
   __shared__ float s_px[TILE], s_py[TILE];
 
   const int tile = blockIdx.x % geo.tiles_per_view;
   const int b = blockIdx.x / geo.tiles_per_view;
   const int tx = tile % geo.tiles_x, ty = tile / geo.tiles_x;
   const int rx0 = tx * TILE, ry0 = ty * TILE, rx1 = rx0 + TILE - 1, ry1 = ry0 + TILE - 1;
-  const int px = rx0 + (threadIdx.x & (TILE - 1));
-  const int py = ry0 + (threadIdx.x / TILE);
-  const bool in_image = px < geo.W && py < geo.H;
   const int64_t vbase = fl.base(b);
-  const int64_t pix = ((int64_t)b * geo.H + py) * geo.W + px;
-  const bool uncovered = in_image && (sp.face_idx[pix] < 0);
   const int K = sp.knum;
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const unsigned lt_mask = (1u << lane) - 1u, le_mask = 0xffffffffu >> (31 - lane);
 
-  if (MODE == MODE_FWD && in_image && !uncovered) {
-    sp.soft[pix] = (T)1.0;                                              // :68-70
-    if (sp.prob) {                                                      // dibr_soft_mask.cpp:86-96 defaults
-      for (int k = 0; k < K; ++k) {
-        sp.prob[pix * K + k] = (T)0;
-        sp.close_idx[pix * K + k] = -1;
-        sp.dist_type[pix * K + k] = 0;
-      }
-    }
-  }
   if (threadIdx.x < TILE) {
     s_px[threadIdx.x] = pix_coord(pix_scale(sp.pix_mult, geo.W), geo.W, rx0 + threadIdx.x);
   } else if (threadIdx.x < 2 * TILE) {
     const int j = threadIdx.x - TILE;
     s_py[j] = pix_coord(pix_scale(sp.pix_mult, geo.H), geo.H, geo.H - 1 - (ry0 + j));
   }
-  // ---- phase A: compact the uncovered pixels of the tile
-  int U;
-  const int uslot = block_compact_256(uncovered, scratch, U);
+  if (threadIdx.x == 0) scratch[9] = 0;
+  __syncthreads();
+  // ---- phase A: covered pixels are final; the uncovered ones are compacted (warp-aggregated append)
+  for (int t = threadIdx.x; t < TILE_PIX; t += NT) {                   // uniform trip count
+    const int px = rx0 + (t & (TILE - 1)), py = ry0 + (t / TILE);
+    const bool in_image = px < geo.W && py < geo.H;
+    const int64_t pix = ((int64_t)b * geo.H + py) * geo.W + px;
+    const bool uncovered = in_image && (sp.face_idx[pix] < 0);
+    if (MODE == MODE_FWD && in_image && !uncovered) {
+      sp.soft[pix] = (T)1.0;                                            // :68-70
+      if (sp.prob) {                                                    // dibr_soft_mask.cpp:86-96 defaults
+        for (int k = 0; k < K; ++k) {
+          sp.prob[pix * K + k] = (T)0;
+          sp.close_idx[pix * K + k] = -1;
+          sp.dist_type[pix * K + k] = 0;
+        }
+      }
+    }
+    const unsigned m = __ballot_sync(0xffffffffu, uncovered);
+    if (m != 0u) {
+      int base = 0;
+      if (lane == 0) base = atomicAdd(&scratch[9], __popc(m));
+      base = __shfl_sync(0xffffffffu, base, 0);
+      if (uncovered) s_upix[base + __popc(m & lt_mask)] = t;
+    }
+    s_ktot[t] = 0;                                       // hits so far of uncovered pixel u (< K)
+    s_acc[t] = (T)1.0;                                   // forward: running product of (1 - prob), face order
+  }
+  __syncthreads();
+  const int U = scratch[9];
   if (U == 0) return;
-  if (uncovered) s_upix[uslot] = threadIdx.x;
-  s_ktot[threadIdx.x] = 0;                               // hits so far of uncovered pixel u (< K)
-  s_acc[threadIdx.x] = (T)1.0;                           // forward: running product of (1 - prob), face order
 
   const TileLists tl = tile_lists(L, geo, fl, b, tx, ty);
   const int n_tile = tl.n_fine;
@@ -246,11 +264,10 @@ __global__ void __launch_bounds__(256, (sizeof(T) == 4 ? 4 : 2)) soft_mask_kerne
   const int n_filt = tl.n_filtered();
   const int nf = (int)(fl.base(b + 1) - vbase);
   const int KS = K | 1;                                  // odd row stride: conflict-free cell rows
-  const int NPB = max(1, min(256, (8 * CELLS) / KS));    // pixels per super-batch (K > 8 * CELLS: 1, clipped rows)
-  const int KROW = min(K, 8 * CELLS);                    // new hits a pixel can take per pass
+  const int NPB = max(1, min(NT, CELLS_TOT / KS));       // pixels per super-batch (K > CELLS_TOT: 1, clipped rows)
+  const int KROW = min(K, CELLS_TOT);                    // new hits a pixel can take per pass
   cell_int* s_celli = reinterpret_cast<cell_int*>(s_cell);
   int* w_tab = s_wtab + warp * 32;
-  const unsigned lt_mask = (1u << lane) - 1u, le_mask = 0xffffffffu >> (31 - lane);
 
   // The candidates are consumed in PASSES of increasing face-index ranges (lo, hi], each holding at most
   // SOFT_CAP candidates.  Nearly every tile needs a single pass (hi = last face); only very dense tiles
@@ -261,43 +278,49 @@ __global__ void __launch_bounds__(256, (sizeof(T) == 4 ? 4 : 2)) soft_mask_kerne
     // ---- gather the candidates with lo < id <= hi: tile list + filtered large faces
     int hi = nf - 1;
     int count = 0;
-    bool fits = first && n_tile <= SOFT_CAP;
+    bool fits = first && n_tile <= CAP;
     if (fits) {
-      for (int k = threadIdx.x; k < n_tile; k += 256) s_ids[k] = tile_list[k];
-      count = n_tile;
-      for (int base = 0; base < n_filt; base += 256) {                 // n_filt is CTA-uniform
+      for (int k = threadIdx.x; k < n_tile; k += NT) s_ids[k] = tile_list[k];
+      if (threadIdx.x == 0) scratch[8] = n_tile;
+      __syncthreads();
+      for (int base = 0; base < n_filt; base += NT) {                  // n_filt is CTA-uniform
         const int k = base + threadIdx.x;
         int f = -1;
         if (k < n_filt) {
           f = tl.filtered_at(k);
           if (!range_hits_rect(L.ranges[vbase + f], rx0, ry0, rx1, ry1)) f = -1;
         }
-        int add;
-        const int slot = block_compact_256(f >= 0, scratch, add);
-        if (count + add > SOFT_CAP) { fits = false; break; }            // uniform
-        if (f >= 0) s_ids[count + slot] = f;
-        count += add;
+        const unsigned m = __ballot_sync(0xffffffffu, f >= 0);
+        if (m != 0u) {                                                  // warp-aggregated append (sorted later)
+          int pos = 0;
+          if (lane == 0) pos = atomicAdd(&scratch[8], __popc(m));
+          pos = __shfl_sync(0xffffffffu, pos, 0) + __popc(m & lt_mask);
+          if (f >= 0 && pos < CAP) s_ids[pos] = f;
+        }
       }
+      __syncthreads();
+      count = scratch[8];
+      if (count > CAP) fits = false;
     }
     if (!fits) {
       // -- selection: largest hi with #{candidates in (lo, hi]} <= SOFT_CAP, by bisection on the face index
       //    (ids are unique, so a range of one id always fits)
       __syncthreads();
-      if (count_candidates(tl, L.ranges + vbase, lo, hi, rx0, ry0, rx1, ry1, scratch) > SOFT_CAP) {
+      if (count_candidates<NT>(tl, L.ranges + vbase, lo, hi, rx0, ry0, rx1, ry1, scratch) > CAP) {
         int good = lo, bad = hi;
         while (bad - good > 1) {
           const int mid = good + ((bad - good) >> 1);
-          if (count_candidates(tl, L.ranges + vbase, lo, mid, rx0, ry0, rx1, ry1, scratch) <= SOFT_CAP) good = mid; else bad = mid;
+          if (count_candidates<NT>(tl, L.ranges + vbase, lo, mid, rx0, ry0, rx1, ry1, scratch) <= CAP) good = mid; else bad = mid;
         }
         hi = good;
       }
       if (threadIdx.x == 0) scratch[8] = 0;
       __syncthreads();
-      for (int k = threadIdx.x; k < n_tile; k += 256) {
+      for (int k = threadIdx.x; k < n_tile; k += NT) {
         const int f = tile_list[k];
         if (f > lo && f <= hi) s_ids[atomicAdd(&scratch[8], 1)] = f;
       }
-      for (int k = threadIdx.x; k < n_filt; k += 256) {
+      for (int k = threadIdx.x; k < n_filt; k += NT) {
         const int f = tl.filtered_at(k);
         if (f > lo && f <= hi && range_hits_rect(L.ranges[vbase + f], rx0, ry0, rx1, ry1))
           s_ids[atomicAdd(&scratch[8], 1)] = f;
@@ -309,22 +332,22 @@ __global__ void __launch_bounds__(256, (sizeof(T) == 4 ? 4 : 2)) soft_mask_kerne
     if (count > 0) {
       // ---- sort by face index; order is semantic (first knum faces in face order)
       __syncthreads();
-      if (count <= 1024) {
+      if (count <= 4 * NT) {
         // rank sort: face ids are unique, so rank = number of smaller ids; one pass, one barrier.  The list
         // is padded to a multiple of 4 with INT_MAX (never smaller than anything), read as int4 broadcasts.
-        if (threadIdx.x < 4) s_ids[count + threadIdx.x] = 0x7fffffff;   // SOFT_CAP + 8 slots are reserved
+        if (threadIdx.x < 4) s_ids[count + threadIdx.x] = 0x7fffffff;   // CAP + 8 slots are reserved
         __syncthreads();
-        if (count <= 256) rank_sort<1>(s_ids, count);
-        else if (count <= 512) rank_sort<2>(s_ids, count);
-        else rank_sort<4>(s_ids, count);
+        if (count <= NT) rank_sort<1, NT>(s_ids, count);
+        else if (count <= 2 * NT) rank_sort<2, NT>(s_ids, count);
+        else rank_sort<4, NT>(s_ids, count);
       } else {
         int n2 = 1;
         while (n2 < count) n2 <<= 1;
-        for (int k = count + threadIdx.x; k < n2; k += 256) s_ids[k] = 0x7fffffff;
+        for (int k = count + threadIdx.x; k < n2; k += NT) s_ids[k] = 0x7fffffff;
         __syncthreads();
         for (int size = 2; size <= n2; size <<= 1) {
           for (int stride = size >> 1; stride > 0; stride >>= 1) {
-            for (int t = threadIdx.x; t < (n2 >> 1); t += 256) {
+            for (int t = threadIdx.x; t < (n2 >> 1); t += NT) {
               const int lo_i = ((t / stride) * stride * 2) + (t % stride);
               const int hi_i = lo_i + stride;
               const bool up = ((lo_i & size) == 0);
@@ -337,7 +360,7 @@ __global__ void __launch_bounds__(256, (sizeof(T) == 4 ? 4 : 2)) soft_mask_kerne
       }
       // ---- tile-local coverage mask of every candidate: bit x (columns) and bit 16 + y (rows) of the pixels
       //      inside its enlarged bbox — the exact pixel range of the reference's float test (:89-97)
-      for (int k = threadIdx.x; k < count; k += 256) {
+      for (int k = threadIdx.x; k < count; k += NT) {
         const uint2 r = L.ranges[vbase + s_ids[k]];
         const int lx0 = max((int)(r.x & 0xffffu), rx0) - rx0, lx1 = min((int)(r.x >> 16), rx1) - rx0;
         const int ly0 = max((int)(r.y & 0xffffu), ry0) - ry0, ly1 = min((int)(r.y >> 16), ry1) - ry0;
@@ -360,7 +383,7 @@ __global__ void __launch_bounds__(256, (sizeof(T) == 4 ? 4 : 2)) soft_mask_kerne
       for (int sb0 = 0; sb0 < U; sb0 += NPB) {
         const int nsb = min(NPB, U - sb0);
         // -- B
-        for (int u0 = warp * 32; u0 < nsb; u0 += 256) {
+        for (int u0 = warp * 32; u0 < nsb; u0 += NT) {
           const int u = u0 + lane;
           const bool act = u < nsb;
           const int t = act ? s_upix[sb0 + u] : 0;
@@ -380,7 +403,7 @@ __global__ void __launch_bounds__(256, (sizeof(T) == 4 ? 4 : 2)) soft_mask_kerne
         }
         __syncthreads();
         // -- C
-        const int PW = (nsb + 7) >> 3;                   // pixels per warp (<= 32)
+        const int PW = (nsb + NW - 1) / NW;              // pixels per warp (<= 32)
         const int ubase = warp * PW;
         if (ubase < nsb) {
           const int npix = min(PW, nsb - ubase);
@@ -459,17 +482,21 @@ __global__ void __launch_bounds__(256, (sizeof(T) == 4 ? 4 : 2)) soft_mask_kerne
     // ---- next pass?
     if (hi >= nf - 1) break;
     lo = hi;
-    if (__syncthreads_and((int)threadIdx.x >= U || s_ktot[threadIdx.x] >= K)) break;   // every list is full
+    bool full = true;
+    for (int u = threadIdx.x; u < U; u += NT) full = full && s_ktot[u] >= K;
+    if (__syncthreads_and(full)) break;                                                // every list is full
   }
   __syncthreads();
-  if (MODE == MODE_FWD && (int)threadIdx.x < U) {
-    const int t = s_upix[threadIdx.x];
-    const int64_t tpix = ((int64_t)b * geo.H + ry0 + (t >> 4)) * geo.W + rx0 + (t & 15);
-    sp.soft[tpix] = (T)(1.0 - (double)s_acc[threadIdx.x]);
-    if (sp.prob)
-      for (int k = s_ktot[threadIdx.x]; k < K; ++k) {
-        sp.prob[tpix * K + k] = (T)0; sp.close_idx[tpix * K + k] = -1; sp.dist_type[tpix * K + k] = 0;
-      }
+  if (MODE == MODE_FWD) {
+    for (int u = threadIdx.x; u < U; u += NT) {
+      const int t = s_upix[u];
+      const int64_t tpix = ((int64_t)b * geo.H + ry0 + (t >> 4)) * geo.W + rx0 + (t & 15);
+      sp.soft[tpix] = (T)(1.0 - (double)s_acc[u]);
+      if (sp.prob)
+        for (int k = s_ktot[u]; k < K; ++k) {
+          sp.prob[tpix * K + k] = (T)0; sp.close_idx[tpix * K + k] = -1; sp.dist_type[tpix * K + k] = 0;
+        }
+    }
   }
 }
 
