@@ -19,6 +19,7 @@
 //     LAST inside face in index order wins — tracked as (has_nan, max inside index) by the gather path.
 #pragma once
 #include "dibr_binning.cuh"
+#include <cstdlib>
 
 namespace dibr {
 
@@ -275,20 +276,51 @@ __device__ __forceinline__ void scatter_faces(const RasterFwdParams<float>& rp, 
   }
 }
 
-__global__ void __launch_bounds__(256) raster_fwd_scatter_kernel(RasterFwdParams<float> rp, FaceLayout fl,
-                                                                 Geometry geo, BinLists L) {
+// Rare fallback of the scatter kernel for tiles that met a NaN depth: the reference's in-order scan restated per
+// pixel over the tile's (unordered) candidate lists with the order-independent rule of the file header.
+__device__ __forceinline__ void scan_pixel_in_order_rule(const RasterFwdParams<float>& rp, const BinLists& L,
+                                                         const TileLists& tl, const int64_t vbase, const int px,
+                                                         const int py, const float x0, const float y0, int& best_f,
+                                                         float& bw0, float& bw1, float& bw2) {
+  float best_z = -RN<float>::inf();
+  bool has_nan = false;
+  int last_inside = -1;
+  best_f = -1; bw0 = 0; bw1 = 0; bw2 = 0;
+  const int n_total = tl.n_fine + tl.n_filtered();
+  for (int k = 0; k < n_total; ++k) {
+    const int f = k < tl.n_fine ? tl.fine[k] : tl.filtered_at(k - tl.n_fine);
+    if (!range_hits_pixel(L.ranges[vbase + f], px, py)) continue;
+    float p[6], w0, w1, w2;
+    load_face_xy<float>(rp.img, vbase + f, rp.coord_mult, rp.premultiplied, p);
+    if (!bary_weights<float>(p[0], p[1], p[2], p[3], p[4], p[5], x0, y0, rp.eps, w0, w1, w2)) continue;
+    const float* zz = rp.z + (vbase + f) * 3;
+    const float z0 = interp3<float>(zz[0], zz[1], zz[2], w0, w1, w2);
+    last_inside = max(last_inside, f);
+    if (z0 != z0) { has_nan = true; continue; }
+    if (z0 > best_z || (z0 == best_z && f < best_f)) { best_z = z0; best_f = f; bw0 = w0; bw1 = w1; bw2 = w2; }
+  }
+  if (has_nan) {
+    best_f = last_inside;
+    float p[6];
+    load_face_xy<float>(rp.img, vbase + best_f, rp.coord_mult, rp.premultiplied, p);
+    bary_weights<float>(p[0], p[1], p[2], p[3], p[4], p[5], x0, y0, rp.eps, bw0, bw1, bw2);
+  }
+}
+
+// NT threads per CTA (one CTA per 16x16 tile whatever NT).
+template <int NT>
+__global__ void __launch_bounds__(NT, 1024 / NT) raster_fwd_scatter_kernel(RasterFwdParams<float> rp, FaceLayout fl,
+                                                                           Geometry geo, BinLists L) {
+  constexpr int NW = NT / 32;
   __shared__ ScatterShared sh;
   const int tile = blockIdx.x % geo.tiles_per_view;
   const int b = blockIdx.x / geo.tiles_per_view;
   const int tx = tile % geo.tiles_x, ty = tile / geo.tiles_x;
   const int rx0 = tx * TILE, ry0 = ty * TILE;
-  const int px = rx0 + (threadIdx.x & (TILE - 1));
-  const int py = ry0 + (threadIdx.x / TILE);
-  const bool in_image = px < geo.W && py < geo.H;
   const int64_t vbase = fl.base(b);
   const int lane = lane_id(), warp = threadIdx.x >> 5;
 
-  sh.key[threadIdx.x] = KEY_NONE;
+  for (int t = threadIdx.x; t < TILE_PIX; t += NT) sh.key[t] = KEY_NONE;
   if (threadIdx.x < TILE) {
     sh.px[threadIdx.x] = pix_coord(pix_scale(rp.pix_mult, geo.W), geo.W, rx0 + threadIdx.x);
   } else if (threadIdx.x < 2 * TILE) {
@@ -301,9 +333,9 @@ __global__ void __launch_bounds__(256) raster_fwd_scatter_kernel(RasterFwdParams
   const TileLists tl = tile_lists(L, geo, fl, b, tx, ty);
   const int n_tile = tl.n_fine;
   const int* tile_list = tl.fine;
-  // the tile's faces are dealt to the 8 warps in equal contiguous slices (a short list still keeps every
-  // warp busy: the parallelism is in the pairs, not in the faces)
-  const int per_warp = (n_tile + 7) >> 3;
+  // the tile's faces are dealt to the warps in equal contiguous slices (a short list still keeps every warp
+  // busy: the parallelism is in the pairs, not in the faces)
+  const int per_warp = (n_tile + NW - 1) / NW;
   const int slice_end = min(n_tile, (warp + 1) * per_warp);
   for (int base = warp * per_warp; base < slice_end; base += 32) {   // warp-uniform trip count
     const int k = base + lane;
@@ -311,7 +343,7 @@ __global__ void __launch_bounds__(256) raster_fwd_scatter_kernel(RasterFwdParams
   }
   // faces binned at the coarse level / in the view's large list: filter against the tile, compact, scatter
   const int n_filt = tl.n_filtered();
-  for (int base = warp * 32; base < n_filt; base += 256) {
+  for (int base = warp * 32; base < n_filt; base += NT) {
     const int k = base + lane;
     int f = -1;
     if (k < n_filt) {
@@ -328,30 +360,44 @@ __global__ void __launch_bounds__(256) raster_fwd_scatter_kernel(RasterFwdParams
   }
   __syncthreads();
 
-  const float x0 = sh.px[threadIdx.x & (TILE - 1)], y0 = sh.py[threadIdx.x / TILE];
-  int best_f = -1;
-  float bw0 = 0, bw1 = 0, bw2 = 0;
-  if (sh.nan_seen) {                                                  // CTA-uniform, rare
-    __shared__ StagedFace<float> st;
-    __shared__ int scratch[9];
-    gather_tile<float>(rp, fl, geo, L, st, scratch, b, tx, ty, px, py, in_image, x0, y0, best_f, bw0, bw1, bw2);
-  } else {
-    const unsigned long long key = sh.key[threadIdx.x];
-    if ((unsigned)(key >> 32) != ORD_NEG_INF) {
-      best_f = (int)(0xffffffffu - (unsigned)key);
-      float p[6];
-      load_face_xy<float>(rp.img, vbase + best_f, rp.coord_mult, rp.premultiplied, p);
-      bary_weights<float>(p[0], p[1], p[2], p[3], p[4], p[5], x0, y0, rp.eps, bw0, bw1, bw2);
+  const bool nan_seen = sh.nan_seen != 0;                             // CTA-uniform, rare
+  for (int t = threadIdx.x; t < TILE_PIX; t += NT) {
+    const int px = rx0 + (t & (TILE - 1)), py = ry0 + (t / TILE);
+    if (px >= geo.W || py >= geo.H) continue;
+    const float x0 = sh.px[t & (TILE - 1)], y0 = sh.py[t / TILE];
+    int best_f = -1;
+    float bw0 = 0, bw1 = 0, bw2 = 0;
+    if (nan_seen) {
+      scan_pixel_in_order_rule(rp, L, tl, vbase, px, py, x0, y0, best_f, bw0, bw1, bw2);
+    } else {
+      const unsigned long long key = sh.key[t];
+      if ((unsigned)(key >> 32) != ORD_NEG_INF) {
+        best_f = (int)(0xffffffffu - (unsigned)key);
+        float p[6];
+        load_face_xy<float>(rp.img, vbase + best_f, rp.coord_mult, rp.premultiplied, p);
+        bary_weights<float>(p[0], p[1], p[2], p[3], p[4], p[5], x0, y0, rp.eps, bw0, bw1, bw2);
+      }
     }
+    raster_epilogue<float>(rp, vbase, ((int64_t)b * geo.H + py) * geo.W + px, best_f, bw0, bw1, bw2);
   }
-  if (!in_image) return;
-  raster_epilogue<float>(rp, vbase, ((int64_t)b * geo.H + py) * geo.W + px, best_f, bw0, bw1, bw2);
+}
+
+inline int raster_threads_default() {
+  static const int nt = [] {
+    const char* e = getenv("DIBR_RASTER_NT");
+    const int v = e ? atoi(e) : 0;
+    return (v == 64 || v == 128 || v == 256) ? v : 128;
+  }();
+  return nt;
 }
 
 // dispatch: fp32 -> scatter, fp64 -> gather
 inline void launch_raster_fwd(const RasterFwdParams<float>& rp, const FaceLayout& fl, const Geometry& geo,
                               const BinLists& L, unsigned grid, cudaStream_t s) {
-  raster_fwd_scatter_kernel<<<grid, 256, 0, s>>>(rp, fl, geo, L);
+  const int nt = raster_threads_default();          // DIBR_RASTER_NT=64|128|256 overrides for experiments
+  if (nt == 64) raster_fwd_scatter_kernel<64><<<grid, 64, 0, s>>>(rp, fl, geo, L);
+  else if (nt == 128) raster_fwd_scatter_kernel<128><<<grid, 128, 0, s>>>(rp, fl, geo, L);
+  else raster_fwd_scatter_kernel<256><<<grid, 256, 0, s>>>(rp, fl, geo, L);
 }
 inline void launch_raster_fwd(const RasterFwdParams<double>& rp, const FaceLayout& fl, const Geometry& geo,
                               const BinLists& L, unsigned grid, cudaStream_t s) {
