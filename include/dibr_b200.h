@@ -41,7 +41,7 @@
 extern "C" {
 #endif
 
-#define DIBR_ABI_VERSION 1
+#define DIBR_ABI_VERSION 2
 
 enum {
   DIBR_OK = 0,
@@ -171,6 +171,9 @@ int dibr_soft_mask_forward_f64(const double* img_mult, const double* large_bboxe
  *  probabilities and distance types with the forward arithmetic.  img NOT multiplied.
  *  grad_img (B,F,3,2) is zero-filled and accumulated by the library; it is the gradient w.r.t. the
  *  UN-multiplied coordinates in both variants (the /multiplier is in-kernel, :299-302).
+ *  bins_ready != 0 (fused variant): `ws` is the very workspace the matching dibr_soft_mask_fwd_fused call
+ *  (same img, sizes, boxlen, multiplier) left behind, untouched since; the setup / binning kernels are then
+ *  skipped (the kernels only read the workspace).  0 = rebuild the bins.
  */
 int dibr_soft_mask_backward_f32(const float* grad_soft, const float* soft, const int64_t* face_idx,
                                 const float* prob, const int64_t* close_idx, const uint8_t* dist_type,
@@ -183,11 +186,11 @@ int dibr_soft_mask_backward_f64(const double* grad_soft, const double* soft, con
 int dibr_soft_mask_bwd_fused_f32(const float* grad_soft, const float* soft, const int64_t* face_idx,
                                  const float* img, int B, int F, int H, int W, float sigmainv, double boxlen,
                                  int knum, double multiplier, float* grad_img,
-                                 void* ws, size_t ws_bytes, void* stream);
+                                 void* ws, size_t ws_bytes, int bins_ready, void* stream);
 int dibr_soft_mask_bwd_fused_f64(const double* grad_soft, const double* soft, const int64_t* face_idx,
                                  const double* img, int B, int F, int H, int W, float sigmainv, double boxlen,
                                  int knum, double multiplier, double* grad_img,
-                                 void* ws, size_t ws_bytes, void* stream);
+                                 void* ws, size_t ws_bytes, int bins_ready, void* stream);
 
 /* Counters for bench.py's `gpu_launches`: number of kernels this library has launched from the
  * calling process since load / since the last reset (relaxed atomic; diagnostics only). */

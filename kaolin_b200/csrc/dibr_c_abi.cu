@@ -239,7 +239,7 @@ template <typename T, int MODE>
 int soft_mask_impl(const T* img, const T* bbox_in, const int64_t* face_idx, int B, int F, int H, int W,
                    float sigmainv, int knum, T coord_mult, int premultiplied, T margin, float pix_mult,
                    T* soft, T* prob, int64_t* close_idx, uint8_t* dist_type, const T* grad_soft, const T* soft_in,
-                   T* grad_img, void* ws, size_t ws_bytes, void* stream) {
+                   T* grad_img, void* ws, size_t ws_bytes, void* stream, int bins_ready = 0) {
   if (int e = check_dims(B, (int64_t)B * F, H, W)) return e;
   if (F < 0 || knum < 0 || !(pix_mult > 0.0f)) return DIBR_ERR_INVALID_ARGUMENT;
   const bool side = prob || close_idx || dist_type;
@@ -260,7 +260,13 @@ int soft_mask_impl(const T* img, const T* bbox_in, const int64_t* face_idx, int 
   sp.img = img; sp.bbox_in = bbox_in; sp.valid = nullptr; sp.coord_mult = coord_mult;
   sp.premultiplied = premultiplied; sp.margin = margin; sp.pix_mult = pix_mult;
   BinLists L;
-  if (int e = run_binning<T>(sp, fl, geo, ws, ws_bytes, s, L)) return e;
+  if (bins_ready) {                      // the forward call's bins, still in `ws` (the consumers only read them)
+    const WsLayout w = ws_layout(geo.B, fl.Ntot, geo);
+    if (!ws || ws_bytes < w.total) return DIBR_ERR_WORKSPACE;
+    L = carve(ws, w);
+  } else if (int e = run_binning<T>(sp, fl, geo, ws, ws_bytes, s, L)) {
+    return e;
+  }
   SoftParams<T> p;
   p.img = img; p.coord_mult = coord_mult; p.premultiplied = premultiplied; p.pix_mult = pix_mult;
   p.sigmainv = sigmainv; p.F = F; p.knum = knum; p.face_idx = face_idx; p.soft = soft; p.prob = prob;
@@ -409,10 +415,11 @@ DIBR_API size_t dibr_workspace_bytes(int batch_size, int64_t total_faces, int he
   DIBR_API int dibr_soft_mask_bwd_fused_##SUF(const T* grad_soft, const T* soft, const int64_t* face_idx,    \
                                               const T* img, int B, int F, int H, int W, float sigmainv,     \
                                               double boxlen, int knum, double multiplier, T* grad_img,      \
-                                              void* ws, size_t ws_bytes, void* stream) {                     \
+                                              void* ws, size_t ws_bytes, int bins_ready, void* stream) {     \
     return soft_mask_impl<T, MODE_BWD>(img, nullptr, face_idx, B, F, H, W, sigmainv, knum, (T)multiplier, 0, \
                                        (T)(boxlen * multiplier), (float)multiplier, nullptr, nullptr,        \
-                                       nullptr, nullptr, grad_soft, soft, grad_img, ws, ws_bytes, stream);    \
+                                       nullptr, nullptr, grad_soft, soft, grad_img, ws, ws_bytes, stream,    \
+                                       bins_ready);                                                           \
   }
 
 DEFINE_ENTRY_POINTS(f32, float)

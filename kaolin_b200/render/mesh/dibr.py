@@ -48,6 +48,9 @@ class DibrSoftMaskCuda(Function):
         ctx.boxlen = boxlen
         ctx.knum = knum
         ctx.save_for_backward(soft_mask, face_vertices_image, selected_face_idx)
+        # the binning workspace (a few tens of bytes per face, vs the reference's 13*knum bytes per PIXEL of saved
+        # side buffers) is kept for backward, which then skips the setup / binning kernels
+        ctx.bins = ws if ctx.needs_input_grad[0] else None
         ctx.set_materialize_grads(False)
         return soft_mask
 
@@ -64,11 +67,15 @@ class DibrSoftMaskCuda(Function):
         grad_soft_mask = grad_soft_mask.contiguous()
         grad_face_vertices_image = torch.empty_like(face_vertices_image)
         with torch.cuda.device(dev):
-            ws, nbytes = _lib.workspace(b, b * f, h, w, dev)
+            ws, ready = ctx.bins, 1
+            if ws is None:
+                (ws, _), ready = _lib.workspace(b, b * f, h, w, dev), 0
+            ctx.bins = None
+            nbytes = _lib.load().dibr_workspace_bytes(b, b * f, h, w)
             code = getattr(_lib.load(), "dibr_soft_mask_bwd_fused_" + suf)(
                 _lib.ptr(grad_soft_mask), _lib.ptr(soft_mask), _lib.ptr(selected_face_idx),
                 _lib.ptr(face_vertices_image), b, f, h, w, float(ctx.sigmainv), float(ctx.boxlen), int(ctx.knum),
-                float(ctx.multiplier), _lib.ptr(grad_face_vertices_image), _lib.ptr(ws), nbytes,
+                float(ctx.multiplier), _lib.ptr(grad_face_vertices_image), _lib.ptr(ws), nbytes, ready,
                 _lib.current_stream(dev))
         _lib.check(code, fn)
         return grad_face_vertices_image, None, None, None, None, None

@@ -289,7 +289,7 @@ def test_unused_outputs_cost_no_gradient(kal):
     feat2 = feat0.clone().requires_grad_(True)
     out2, soft2, _ = kal.render.mesh.dibr_rasterization(48, 56, z, img2, feat2, nz)
     (soft2.sum() + (out2 * 0).sum()).backward()
-    assert torch.allclose(img2.grad, g_soft_only, rtol=1e-5, atol=1e-6)
+    rel_close(img2.grad, g_soft_only, 1e-4, "soft-only gradient")        # atomics: summation order differs run to run
     assert feat2.grad is not None and torch.all(feat2.grad == 0)
     img3 = img0.clone().requires_grad_(True)
     (o_a, o_b), _ = kal.render.mesh.rasterize(48, 56, z, img3, [feat0[..., :1].contiguous().requires_grad_(True),
