@@ -326,3 +326,64 @@ def test_cuda_graph_capture_matches_eager(kal):
         for a, b in zip(outs_g[3:], outs_e[3:]):
             scale = max(1.0, float(b.abs().max()))
             assert float((a - b).abs().max()) <= 1e-4 * scale
+
+
+# ----------------------------------------------------------------------------- full BASELINE sizes, by properties
+def _full_size_properties(kal, name, batch, shard):
+    """Size-independent properties at a BASELINE.json configuration's full size (the brute-force reference
+    cannot run there): run-to-run determinism of the forward, composition identity (dibr_rasterization ==
+    rasterize + dibr_soft_mask, test_dibr.py:527-529), view-shard invariance (rendering a contiguous shard of the
+    views alone gives exactly the shard of the full-batch result — the multi-GPU partition of SURVEY.md §8e),
+    value ranges, and finite gradients that vanish on culled faces."""
+    from kaolin_b200 import synth
+    d = to_dev(synth.make_inputs(name, batch=batch))
+    Hh, Ww = d["H"], d["W"]
+    z, img, feat, nz = d["face_vertices_z"], d["face_vertices_image"], d["face_features"][0], d["face_normals_z"]
+    img_l = img.clone().requires_grad_(True)
+    feat_l = feat.clone().requires_grad_(True)
+    out, soft, idx = kal.render.mesh.dibr_rasterization(Hh, Ww, z, img_l, feat_l, nz)
+    out2, idx2 = kal.render.mesh.rasterize(Hh, Ww, z, img, feat, nz >= 0)
+    soft2 = kal.render.mesh.dibr_soft_mask(img, idx2)
+    assert torch.equal(idx, idx2) and torch.equal(out, out2) and torch.equal(soft, soft2)
+    covered = idx >= 0
+    assert int(idx.max()) < z.shape[1] and int(idx.min()) >= -1
+    assert covered.float().mean() > 0.2, "the mesh should cover a good part of the image"
+    assert torch.all(soft[covered] == 1) and float(soft.min()) >= 0 and float(soft.max()) <= 1
+    assert torch.all(out[~covered] == 0)
+    # every rendered face is front-facing (valid_faces = normals_z >= 0, dibr.py:195)
+    b_idx = torch.arange(z.shape[0], device="cuda").view(-1, 1, 1).expand_as(idx)
+    assert torch.all(nz[b_idx[covered], idx[covered]] >= 0)
+    lo, hi = shard
+    o_s, s_s, i_s = kal.render.mesh.dibr_rasterization(Hh, Ww, z[lo:hi].contiguous(), img[lo:hi].contiguous(),
+                                                       feat[lo:hi].contiguous(), nz[lo:hi].contiguous())
+    assert torch.equal(i_s, idx[lo:hi]) and torch.equal(o_s, out[lo:hi]) and torch.equal(s_s, soft[lo:hi])
+    g = torch.Generator().manual_seed(5)
+    g_out = torch.rand(out.shape[1:], generator=g).cuda().expand_as(out)
+    g_soft = torch.rand(soft.shape[1:], generator=g).cuda().expand_as(soft)
+    torch.autograd.backward([out, soft], [g_out, g_soft])
+    assert torch.isfinite(img_l.grad).all() and torch.isfinite(feat_l.grad).all()
+    assert torch.all(feat_l.grad[nz < 0] == 0), "culled faces receive no feature gradient"
+    assert feat_l.grad.abs().sum() > 0 and img_l.grad.abs().sum() > 0
+    # sum over pixels of the interpolation weights = 1 per covered pixel: grad of a constant-1 upstream w.r.t. the
+    # features sums to the number of covered pixels per channel
+    feat_c = feat.clone().requires_grad_(True)
+    o3, _ = kal.render.mesh.rasterize(Hh, Ww, z, img, feat_c, nz >= 0)
+    o3.sum().backward()
+    total = feat_c.grad.double().sum().item()
+    expect = float(covered.sum().item()) * feat.shape[-1]
+    assert abs(total - expect) <= 1e-4 * expect, (total, expect)
+
+
+def test_c3_full_size_properties(kal):
+    """config 3: 100k faces, 64 views, 1024x1024."""
+    _full_size_properties(kal, "c3", None, (24, 32))
+
+
+def test_c5_full_size_properties(kal):
+    """config 5 (stress): 1M faces, 8 views, 2048x2048 — coarse-cell lists and multi-pass dense tiles."""
+    _full_size_properties(kal, "c5", None, (3, 4))
+
+
+def test_c4_shape_two_shards(kal):
+    """config 4 shape (40k faces, 512x512) on 16 of the 128 cameras."""
+    _full_size_properties(kal, "c4", 16, (8, 16))
