@@ -1,0 +1,172 @@
+// dibr_prepare.cuh — the step immediately BEFORE the rasterization path:
+// prepare_vertices of kaolin/render/mesh/utils.py:128-175, i.e.
+//   rotate_translate_points / camera_transform        kaolin/render/camera/legacy.py:22-37, utils.py:163-167
+//   perspective_camera                                 kaolin/render/camera/legacy.py:120-139
+//   index_vertices_by_faces (x2)                       kaolin/ops/mesh/mesh.py:24-45
+//   face_normals(unit=True)                            kaolin/ops/mesh/trianglemesh.py:313-336
+// fused into ONE pass: thread = (view, face) gathers its three vertices, transforms and projects them and writes
+// face_vertices_camera (B,F,3,3), face_vertices_image (B,F,3,2), face_normals (B,F,3).  The reference runs ~12
+// torch kernels and materialises vertices_camera / vertices_image / two expanded gathers on the way.
+// Backward: thread = (view, face) recomputes the camera-space triangle, folds the three upstream gradients
+// through normalisation, cross product, perspective divide and rotation, and scatters into grad_vertices with
+// red.global.add (vertices shared by all views when Bv == 1).
+// Floating point: tolerance parity (1e-5 relative, fp32), not bit-exactness — the reference's own matmul has no
+// specified summation order.
+#pragma once
+#include "dibr_common.cuh"
+
+namespace dibr {
+
+template <typename T>
+struct PrepareParams {
+  const T* vertices;        // (Bv,V,3), Bv = 1 (shared mesh) or B
+  const int64_t* faces;     // (F,3)
+  const T* proj;            // (3)
+  const T* rot;             // (B,3,3) or nullptr
+  const T* trans;           // (B,3)   or nullptr
+  const T* transform;       // (B,4,3) or nullptr (replaces rot/trans)
+  int B, Bv, V, F;
+  // forward outputs
+  T* face_cam;              // (B,F,3,3)
+  T* face_img;              // (B,F,3,2)
+  T* face_nrm;              // (B,F,3)
+  // backward inputs (each may be nullptr) / output
+  const T* g_cam;           // (B,F,3,3)
+  const T* g_img;           // (B,F,3,2)
+  const T* g_nrm;           // (B,F,3)
+  T* g_vertices;            // (Bv,V,3), zero-filled by the host wrapper
+};
+
+template <typename T>
+struct ViewCamera {         // cam_j = sum_k (p_k - t_k) * m[j][k]   (rot/trans)   or   sum_k p_k * m[j][k] + o[j]
+  T m[3][3];
+  T t[3];
+  T o[3];
+};
+
+template <typename T>
+__device__ __forceinline__ ViewCamera<T> load_camera(const PrepareParams<T>& pp, const int b) {
+  ViewCamera<T> c;
+  if (pp.transform) {                                  // padded_vertices @ camera_transform, utils.py:163-167
+    const T* M = pp.transform + (int64_t)b * 12;       // (4,3): M[k][j]
+#pragma unroll
+    for (int j = 0; j < 3; ++j) {
+#pragma unroll
+      for (int k = 0; k < 3; ++k) c.m[j][k] = M[k * 3 + j];
+      c.o[j] = M[9 + j];
+      c.t[j] = (T)0;
+    }
+  } else {                                             // (points - trans) @ rot^T, legacy.py:35-37
+    const T* R = pp.rot + (int64_t)b * 9;
+#pragma unroll
+    for (int j = 0; j < 3; ++j) {
+#pragma unroll
+      for (int k = 0; k < 3; ++k) c.m[j][k] = R[j * 3 + k];
+      c.o[j] = (T)0;
+      c.t[j] = pp.trans[(int64_t)b * 3 + j];
+    }
+  }
+  return c;
+}
+
+template <typename T>
+__device__ __forceinline__ void to_camera(const ViewCamera<T>& c, const T* p, T* q) {
+  const T x = p[0] - c.t[0], y = p[1] - c.t[1], z = p[2] - c.t[2];
+#pragma unroll
+  for (int j = 0; j < 3; ++j) q[j] = x * c.m[j][0] + y * c.m[j][1] + z * c.m[j][2] + c.o[j];
+}
+
+template <typename T> __device__ __forceinline__ T sqrt_t(T v);
+template <> __device__ __forceinline__ float sqrt_t<float>(float v) { return sqrtf(v); }
+template <> __device__ __forceinline__ double sqrt_t<double>(double v) { return sqrt(v); }
+
+template <typename T>
+__global__ void __launch_bounds__(256) prepare_vertices_fwd_kernel(PrepareParams<T> pp) {
+  const int64_t g = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (g >= (int64_t)pp.B * pp.F) return;
+  const int b = (int)(g / pp.F), f = (int)(g % pp.F);
+  const ViewCamera<T> cam = load_camera<T>(pp, b);
+  const T* vb = pp.vertices + (pp.Bv == 1 ? (int64_t)0 : (int64_t)b * pp.V * 3);
+  const T p0 = pp.proj[0], p1 = pp.proj[1], p2 = pp.proj[2];
+  T q[3][3];
+#pragma unroll
+  for (int k = 0; k < 3; ++k) {
+    const int64_t vi = pp.faces[(int64_t)f * 3 + k];
+    to_camera<T>(cam, vb + vi * 3, q[k]);
+  }
+  T* oc = pp.face_cam + g * 9;
+  T* oi = pp.face_img + g * 6;
+#pragma unroll
+  for (int k = 0; k < 3; ++k) {
+    oc[k * 3 + 0] = q[k][0]; oc[k * 3 + 1] = q[k][1]; oc[k * 3 + 2] = q[k][2];
+    const T pz = q[k][2] * p2;                                   // legacy.py:136-137
+    oi[k * 2 + 0] = (q[k][0] * p0) / pz;
+    oi[k * 2 + 1] = (q[k][1] * p1) / pz;
+  }
+  // trianglemesh.py:328-334
+  const T e0x = q[1][0] - q[0][0], e0y = q[1][1] - q[0][1], e0z = q[1][2] - q[0][2];
+  const T e1x = q[2][0] - q[0][0], e1y = q[2][1] - q[0][1], e1z = q[2][2] - q[0][2];
+  const T nx = e0y * e1z - e0z * e1y, ny = e0z * e1x - e0x * e1z, nz = e0x * e1y - e0y * e1x;
+  const T len = sqrt_t<T>(nx * nx + ny * ny + nz * nz) + (T)1e-10;
+  T* on = pp.face_nrm + g * 3;
+  on[0] = nx / len; on[1] = ny / len; on[2] = nz / len;
+}
+
+template <typename T>
+__global__ void __launch_bounds__(256) prepare_vertices_bwd_kernel(PrepareParams<T> pp) {
+  const int64_t g = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (g >= (int64_t)pp.B * pp.F) return;
+  const int b = (int)(g / pp.F), f = (int)(g % pp.F);
+  const ViewCamera<T> cam = load_camera<T>(pp, b);
+  const int64_t voff = pp.Bv == 1 ? (int64_t)0 : (int64_t)b * pp.V * 3;
+  const T* vb = pp.vertices + voff;
+  const T p0 = pp.proj[0], p1 = pp.proj[1], p2 = pp.proj[2];
+  int64_t vi[3];
+  T q[3][3], gq[3][3];
+#pragma unroll
+  for (int k = 0; k < 3; ++k) {
+    vi[k] = pp.faces[(int64_t)f * 3 + k];
+    to_camera<T>(cam, vb + vi[k] * 3, q[k]);
+#pragma unroll
+    for (int j = 0; j < 3; ++j) gq[k][j] = pp.g_cam ? pp.g_cam[g * 9 + k * 3 + j] : (T)0;
+  }
+  if (pp.g_img) {                     // img_x = (x p0) / (z p2),  img_y = (y p1) / (z p2)
+#pragma unroll
+    for (int k = 0; k < 3; ++k) {
+      const T gx = pp.g_img[g * 6 + k * 2], gy = pp.g_img[g * 6 + k * 2 + 1];
+      const T pz = q[k][2] * p2;
+      const T ix = (q[k][0] * p0) / pz, iy = (q[k][1] * p1) / pz;
+      gq[k][0] += gx * p0 / pz;
+      gq[k][1] += gy * p1 / pz;
+      gq[k][2] -= (gx * ix + gy * iy) / q[k][2];
+    }
+  }
+  if (pp.g_nrm) {                     // n = c / (|c| + 1e-10), c = e0 x e1
+    const T e0x = q[1][0] - q[0][0], e0y = q[1][1] - q[0][1], e0z = q[1][2] - q[0][2];
+    const T e1x = q[2][0] - q[0][0], e1y = q[2][1] - q[0][1], e1z = q[2][2] - q[0][2];
+    const T cx = e0y * e1z - e0z * e1y, cy = e0z * e1x - e0x * e1z, cz = e0x * e1y - e0y * e1x;
+    const T L = sqrt_t<T>(cx * cx + cy * cy + cz * cz);
+    const T Le = L + (T)1e-10;
+    const T gx = pp.g_nrm[g * 3], gy = pp.g_nrm[g * 3 + 1], gz = pp.g_nrm[g * 3 + 2];
+    const T dot = cx * gx + cy * gy + cz * gz;
+    const T s = L > (T)0 ? dot / (L * Le * Le) : (T)0;           // torch's norm backward is 0 at 0
+    const T hx = gx / Le - cx * s, hy = gy / Le - cy * s, hz = gz / Le - cz * s;     // dL/dc
+    // c = e0 x e1:  dL/de0 = e1 x h,  dL/de1 = h x e0
+    const T a0 = e1y * hz - e1z * hy, a1 = e1z * hx - e1x * hz, a2 = e1x * hy - e1y * hx;
+    const T b0 = hy * e0z - hz * e0y, b1 = hz * e0x - hx * e0z, b2 = hx * e0y - hy * e0x;
+    gq[1][0] += a0; gq[1][1] += a1; gq[1][2] += a2;
+    gq[2][0] += b0; gq[2][1] += b1; gq[2][2] += b2;
+    gq[0][0] -= a0 + b0; gq[0][1] -= a1 + b1; gq[0][2] -= a2 + b2;
+  }
+  T* gv = pp.g_vertices + voff;
+#pragma unroll
+  for (int k = 0; k < 3; ++k) {
+#pragma unroll
+    for (int c = 0; c < 3; ++c) {     // cam_j = sum_c (p_c - t_c) m[j][c]  =>  dL/dp_c = sum_j gq_j m[j][c]
+      const T v = gq[k][0] * cam.m[0][c] + gq[k][1] * cam.m[1][c] + gq[k][2] * cam.m[2][c];
+      atomicAdd(gv + vi[k] * 3 + c, v);
+    }
+  }
+}
+
+}  // namespace dibr
