@@ -41,7 +41,7 @@
 extern "C" {
 #endif
 
-#define DIBR_ABI_VERSION 2
+#define DIBR_ABI_VERSION 3
 
 enum {
   DIBR_OK = 0,
@@ -192,6 +192,41 @@ int dibr_soft_mask_bwd_fused_f64(const double* grad_soft, const double* soft, co
                                  int knum, double multiplier, double* grad_img,
                                  void* ws, size_t ws_bytes, int bins_ready, void* stream);
 
+/* ---------------------------------------------------------------------------------------------
+ * prepare_vertices — the producer of the path's inputs (first "next" row).
+ *  Replaces the torch composition of kaolin/render/mesh/utils.py:128-175:
+ *    camera transform      rotate_translate_points (kaolin/render/camera/legacy.py:22-37) when rot/trans are
+ *                          given, or [v,1] @ camera_transform (B,4,3) (utils.py:163-167) when transform is given
+ *    perspective_camera    kaolin/render/camera/legacy.py:120-139   (x*p0/(z*p2), y*p1/(z*p2))
+ *    index_vertices_by_faces (twice)   kaolin/ops/mesh/mesh.py:24-45
+ *    face_normals(unit=True)           kaolin/ops/mesh/trianglemesh.py:313-336  (n / (|n| + 1e-10))
+ *  by one kernel (thread = view x face).  vertices (Bv,V,3) with Bv == 1 (one mesh broadcast over the
+ *  B cameras, as torch broadcasting does in the reference) or Bv == B; faces (F,3) int64 in [0,V)
+ *  (an out-of-range index yields NaN outputs for that face, never an out-of-bounds read);
+ *  camera_proj (3); exactly one of {rot (B,3,3) + trans (B,3)} or {transform (B,4,3)} non-NULL.
+ *  Outputs: face_vertices_camera (B,F,3,3), face_vertices_image (B,F,3,2), face_normals (B,F,3).
+ *  _bwd: any of the three upstream gradients may be NULL (= zeros); grad_vertices (Bv,V,3) is zero-filled
+ *  and accumulated by the library (summed over views when Bv == 1).  Camera tensors get no gradient.
+ *  Floating point: agrees with the reference within 1e-5 relative (fp32) — its matmul has no fixed order.
+ */
+int dibr_prepare_vertices_fwd_f32(const float* vertices, const int64_t* faces, const float* camera_proj,
+                                  const float* rot, const float* trans, const float* transform,
+                                  int B, int Bv, int V, int F, float* face_vertices_camera,
+                                  float* face_vertices_image, float* face_normals, void* stream);
+int dibr_prepare_vertices_fwd_f64(const double* vertices, const int64_t* faces, const double* camera_proj,
+                                  const double* rot, const double* trans, const double* transform,
+                                  int B, int Bv, int V, int F, double* face_vertices_camera,
+                                  double* face_vertices_image, double* face_normals, void* stream);
+int dibr_prepare_vertices_bwd_f32(const float* grad_camera, const float* grad_image, const float* grad_normals,
+                                  const float* vertices, const int64_t* faces, const float* camera_proj,
+                                  const float* rot, const float* trans, const float* transform,
+                                  int B, int Bv, int V, int F, float* grad_vertices, void* stream);
+int dibr_prepare_vertices_bwd_f64(const double* grad_camera, const double* grad_image,
+                                  const double* grad_normals, const double* vertices, const int64_t* faces,
+                                  const double* camera_proj, const double* rot, const double* trans,
+                                  const double* transform, int B, int Bv, int V, int F,
+                                  double* grad_vertices, void* stream);
+
 /* Counters for bench.py's `gpu_launches`: number of kernels this library has launched from the
  * calling process since load / since the last reset (relaxed atomic; diagnostics only). */
 uint64_t dibr_kernel_launch_count(void);
@@ -208,7 +243,9 @@ enum {
   DIBR_KERNEL_RASTER_BWD = 4,
   DIBR_KERNEL_SOFT_FWD = 5,
   DIBR_KERNEL_SOFT_BWD = 6,
-  DIBR_KERNEL_COUNT = 7
+  DIBR_KERNEL_PREPARE_FWD = 7,
+  DIBR_KERNEL_PREPARE_BWD = 8,
+  DIBR_KERNEL_COUNT = 9
 };
 int dibr_profile_next_launch(int kernel_id, void* start_event, void* stop_event);
 

@@ -17,7 +17,7 @@ LIB_PATH = os.path.join(_PKG, "libdibr_b200.so")
 CSRC = os.path.join(_PKG, "csrc")
 SOURCES = ["dibr_c_abi.cu"]
 HEADERS = ["dibr_common.cuh", "dibr_binning.cuh", "dibr_raster_fwd.cuh", "dibr_raster_bwd.cuh",
-           "dibr_soft_mask.cuh"]
+           "dibr_soft_mask.cuh", "dibr_prepare.cuh"]
 NVCC_FLAGS = ["-O3", "-std=c++17", "-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo",
               "-cudart", "shared", "-Xcompiler", "-fPIC,-fvisibility=hidden"]
 
@@ -39,6 +39,8 @@ _TYPED = {
     "dibr_soft_mask_forward": [c_p, c_p, c_p, c_i, c_i, c_i, c_i, c_f, c_i, c_f, c_p, c_p, c_p, c_p, c_p, c_sz, c_p],
     "dibr_soft_mask_backward": [c_p, c_p, c_p, c_p, c_p, c_p, c_p, c_i, c_i, c_i, c_i, c_i, c_f, c_f, c_p, c_p],
     "dibr_soft_mask_bwd_fused": [c_p, c_p, c_p, c_p, c_i, c_i, c_i, c_i, c_f, c_d, c_i, c_d, c_p, c_p, c_sz, c_i, c_p],
+    "dibr_prepare_vertices_fwd": [c_p, c_p, c_p, c_p, c_p, c_p, c_i, c_i, c_i, c_i, c_p, c_p, c_p, c_p],
+    "dibr_prepare_vertices_bwd": [c_p, c_p, c_p, c_p, c_p, c_p, c_p, c_p, c_p, c_i, c_i, c_i, c_i, c_p, c_p],
 }
 EXPORTED_SYMBOLS = (["dibr_abi_version", "dibr_error_string", "dibr_last_cuda_error", "dibr_workspace_bytes",
                      "dibr_kernel_launch_count", "dibr_reset_kernel_launch_count", "dibr_profile_next_launch"] +
@@ -95,7 +97,7 @@ def load():
                 fn = getattr(lib, f"{name}_{suf}")
                 fn.restype = c_i
                 fn.argtypes = argtypes
-        if lib.dibr_abi_version() != 2:
+        if lib.dibr_abi_version() != 3:
             raise RuntimeError("kaolin_b200: libdibr_b200.so ABI version mismatch")
         _lib = lib
     return _lib
@@ -142,7 +144,8 @@ def current_stream(device):
     return torch.cuda.current_stream(device).cuda_stream
 
 
-KERNEL_IDS = dict(setup_count=0, scan=1, fill=2, raster_fwd=3, raster_bwd=4, soft_fwd=5, soft_bwd=6)
+KERNEL_IDS = dict(setup_count=0, scan=1, fill=2, raster_fwd=3, raster_bwd=4, soft_fwd=5, soft_bwd=6,
+                  prepare_fwd=7, prepare_bwd=8)
 
 
 def profile_next_launch(kernel_id, start_event, stop_event):

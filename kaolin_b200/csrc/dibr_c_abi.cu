@@ -5,6 +5,7 @@
 #include "dibr_raster_fwd.cuh"
 #include "dibr_raster_bwd.cuh"
 #include "dibr_soft_mask.cuh"
+#include "dibr_prepare.cuh"
 
 #include <atomic>
 #include <cstdio>
@@ -311,6 +312,45 @@ int soft_mask_bwd_sidebuf_impl(const T* grad_soft, const T* soft, const int64_t*
   return DIBR_OK;
 }
 
+// prepare_vertices (utils.py:128-175): one kernel each way; grad_vertices is zero-filled here.
+template <typename T>
+int prepare_impl(bool backward, const T* g_cam, const T* g_img, const T* g_nrm, const T* vertices,
+                 const int64_t* faces, const T* proj, const T* rot, const T* trans, const T* transform, int B,
+                 int Bv, int V, int F, T* face_cam, T* face_img, T* face_nrm, T* g_vertices, void* stream) {
+  if (B < 0 || V < 0 || F < 0 || (Bv != 1 && Bv != B)) return DIBR_ERR_INVALID_ARGUMENT;
+  if ((int64_t)B * F >= (int64_t)1 << 40 || (int64_t)Bv * V >= (int64_t)1 << 40) return DIBR_ERR_TOO_LARGE;
+  const bool by_matrix = transform != nullptr;
+  if (by_matrix == (rot != nullptr || trans != nullptr)) return DIBR_ERR_INVALID_ARGUMENT;   // exactly one camera form
+  if (!by_matrix && (!rot || !trans)) return DIBR_ERR_INVALID_ARGUMENT;
+  cudaStream_t s = static_cast<cudaStream_t>(stream);
+  const int64_t n = (int64_t)B * F;
+  if (backward) {
+    if ((int64_t)Bv * V > 0) {
+      if (!g_vertices) return DIBR_ERR_INVALID_ARGUMENT;
+      CUDA_TRY(cudaMemsetAsync(g_vertices, 0, (size_t)Bv * V * 3 * sizeof(T), s));
+    }
+  } else if (n > 0 && (!face_cam || !face_img || !face_nrm)) {
+    return DIBR_ERR_INVALID_ARGUMENT;
+  }
+  if (n == 0) return DIBR_OK;
+  if (!vertices || !faces || !proj) return DIBR_ERR_INVALID_ARGUMENT;
+  PrepareParams<T> pp;
+  pp.vertices = vertices; pp.faces = faces; pp.proj = proj; pp.rot = rot; pp.trans = trans;
+  pp.transform = transform; pp.B = B; pp.Bv = Bv; pp.V = V; pp.F = F;
+  pp.face_cam = face_cam; pp.face_img = face_img; pp.face_nrm = face_nrm;
+  pp.g_cam = g_cam; pp.g_img = g_img; pp.g_nrm = g_nrm; pp.g_vertices = g_vertices;
+  const unsigned nb = (unsigned)((n + 255) / 256);
+  if (backward) {
+    if (!g_cam && !g_img && !g_nrm) return DIBR_OK;                 // all-zero upstream: the memset is the answer
+    { ProfScope ps(DIBR_KERNEL_PREPARE_BWD, s); prepare_vertices_bwd_kernel<T><<<nb, 256, 0, s>>>(pp); }
+    LAUNCH_CHECK("prepare_vertices_bwd_kernel");
+  } else {
+    { ProfScope ps(DIBR_KERNEL_PREPARE_FWD, s); prepare_vertices_fwd_kernel<T><<<nb, 256, 0, s>>>(pp); }
+    LAUNCH_CHECK("prepare_vertices_fwd_kernel");
+  }
+  return DIBR_OK;
+}
+
 }  // namespace
 
 #define DIBR_API extern "C" __attribute__((visibility("default")))
@@ -420,6 +460,22 @@ DIBR_API size_t dibr_workspace_bytes(int batch_size, int64_t total_faces, int he
                                        (T)(boxlen * multiplier), (float)multiplier, nullptr, nullptr,        \
                                        nullptr, nullptr, grad_soft, soft, grad_img, ws, ws_bytes, stream,    \
                                        bins_ready);                                                           \
+  }                                                                                                           \
+  DIBR_API int dibr_prepare_vertices_fwd_##SUF(const T* vertices, const int64_t* faces, const T* camera_proj, \
+                                               const T* rot, const T* trans, const T* transform, int B,      \
+                                               int Bv, int V, int F, T* face_vertices_camera,                \
+                                               T* face_vertices_image, T* face_normals, void* stream) {      \
+    return prepare_impl<T>(false, nullptr, nullptr, nullptr, vertices, faces, camera_proj, rot, trans,       \
+                           transform, B, Bv, V, F, face_vertices_camera, face_vertices_image, face_normals,  \
+                           nullptr, stream);                                                                  \
+  }                                                                                                           \
+  DIBR_API int dibr_prepare_vertices_bwd_##SUF(const T* grad_camera, const T* grad_image,                    \
+                                               const T* grad_normals, const T* vertices,                     \
+                                               const int64_t* faces, const T* camera_proj, const T* rot,     \
+                                               const T* trans, const T* transform, int B, int Bv, int V,     \
+                                               int F, T* grad_vertices, void* stream) {                      \
+    return prepare_impl<T>(true, grad_camera, grad_image, grad_normals, vertices, faces, camera_proj, rot,   \
+                           trans, transform, B, Bv, V, F, nullptr, nullptr, nullptr, grad_vertices, stream); \
   }
 
 DEFINE_ENTRY_POINTS(f32, float)

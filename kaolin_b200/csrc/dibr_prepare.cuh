@@ -92,6 +92,10 @@ __global__ void __launch_bounds__(256) prepare_vertices_fwd_kernel(PrepareParams
 #pragma unroll
   for (int k = 0; k < 3; ++k) {
     const int64_t vi = pp.faces[(int64_t)f * 3 + k];
+    if ((uint64_t)vi >= (uint64_t)pp.V) {              // out-of-range index: never read outside the buffer
+      q[k][0] = q[k][1] = q[k][2] = (T)NAN;
+      continue;
+    }
     to_camera<T>(cam, vb + vi * 3, q[k]);
   }
   T* oc = pp.face_cam + g * 9;
@@ -126,6 +130,7 @@ __global__ void __launch_bounds__(256) prepare_vertices_bwd_kernel(PrepareParams
 #pragma unroll
   for (int k = 0; k < 3; ++k) {
     vi[k] = pp.faces[(int64_t)f * 3 + k];
+    if ((uint64_t)vi[k] >= (uint64_t)pp.V) return;     // forward wrote NaN for this face; nothing to scatter
     to_camera<T>(cam, vb + vi[k] * 3, q[k]);
 #pragma unroll
     for (int j = 0; j < 3; ++j) gq[k][j] = pp.g_cam ? pp.g_cam[g * 9 + k * 3 + j] : (T)0;

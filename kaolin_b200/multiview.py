@@ -66,26 +66,6 @@ def look_at(eye, at, up):
     return torch.stack([cx, cy, -cz], dim=1), eye
 
 
-def prepare_vertices(vertices, faces, rot, trans, fovy=math.pi / 4):
-    """Differentiable torch restatement of kaolin/render/mesh/utils.py:128-175 (input producer of the path):
-    vertices (V,3) or (1,V,3) shared by all views, rot (B,3,3), trans (B,3) ->
-    face_vertices_camera (B,F,3,3), face_vertices_image (B,F,3,2), face_normals (B,F,3)."""
-    if vertices.dim() == 2:
-        vertices = vertices.unsqueeze(0)
-    vcam = torch.matmul(vertices - trans.view(-1, 1, 3), rot.permute(0, 2, 1))
-    tanfov = math.tan(fovy / 2.0)
-    proj = torch.tensor([1.0 / tanfov, 1.0 / tanfov, -1.0], dtype=vertices.dtype, device=vertices.device)
-    p = vcam * proj.view(1, 1, 3)
-    vimg = p[:, :, :2] / p[:, :, 2:3]
-    fcam = vcam[:, faces]
-    fimg = vimg[:, faces]
-    e1 = fcam[:, :, 1] - fcam[:, :, 0]
-    e2 = fcam[:, :, 2] - fcam[:, :, 0]
-    nrm = torch.cross(e1, e2, dim=-1)
-    nrm = nrm / (nrm.norm(dim=-1, keepdim=True) + 1e-10)
-    return fcam, fimg, nrm
-
-
 def mask_iou(lhs_mask, rhs_mask):
     """kaolin/metrics/render.py:18-40."""
     b = lhs_mask.shape[0]
@@ -98,13 +78,13 @@ def mask_iou(lhs_mask, rhs_mask):
 
 class MultiViewOptimizer:
     """Multi-view DIB-R shape optimisation (BASELINE.json config 4).  Each rank owns a contiguous shard of the
-    cameras; the mesh (vertices leaf, faces, per-vertex features) is replicated.  One step = prepare_vertices
+    cameras; the mesh (vertices leaf, faces, per-vertex features) is replicated.  One step = prepare_vertices (fused CUDA kernel)
     -> dibr_rasterization -> mask IoU + L1 feature loss -> backward -> ONE all-reduce of ``vertices.grad`` ->
     Adam.  Losses are sums over the local views divided by the GLOBAL view count, so the all-reduced gradient
     equals the single-process gradient over all cameras."""
 
     def __init__(self, vertices, faces, vertex_features, rot, trans, target_mask, target_feat, height, width,
-                 n_views_total, lr=1e-3, sigmainv=7000., boxlen=0.02, knum=30, group=None):
+                 n_views_total, lr=1e-3, sigmainv=7000., boxlen=0.02, knum=30, group=None, fovy=math.pi / 4):
         self.vertices = vertices.detach().clone().requires_grad_(True)
         self.faces = faces
         self.vertex_features = vertex_features
@@ -114,15 +94,21 @@ class MultiViewOptimizer:
         self.n_views_total = n_views_total
         self.sigmainv, self.boxlen, self.knum = sigmainv, boxlen, knum
         self.group = group
+        # kaolin/render/camera/legacy.py:141-159 (generate_perspective_projection, ratio 1)
+        self.proj = torch.tensor([1.0 / math.tan(fovy / 2.0), 1.0 / math.tan(fovy / 2.0), -1.0],
+                                 dtype=vertices.dtype, device=vertices.device)
+        # the per-face features do not depend on the vertices being optimised: gathered once
+        self.face_features = vertex_features[faces].unsqueeze(0).expand(rot.shape[0], -1, -1, -1).contiguous()
         self.opt = torch.optim.Adam([self.vertices], lr=lr)
 
     def loss(self):
-        from .render.mesh import dibr_rasterization
-        fcam, fimg, nrm = prepare_vertices(self.vertices, self.faces, self.rot, self.trans)
+        from .render.mesh import dibr_rasterization, prepare_vertices
+        verts = self.vertices if self.vertices.dim() == 3 else self.vertices.unsqueeze(0)
+        fcam, fimg, nrm = prepare_vertices(verts, self.faces, self.proj, camera_rot=self.rot,
+                                           camera_trans=self.trans)
         b = fimg.shape[0]
-        feats = self.vertex_features[self.faces].unsqueeze(0).expand(b, -1, -1, -1).contiguous()
-        img, soft, face_idx = dibr_rasterization(self.height, self.width, fcam[..., 2].contiguous(),
-                                                 fimg.contiguous(), feats, nrm[..., 2].contiguous(),
+        img, soft, face_idx = dibr_rasterization(self.height, self.width, fcam[..., 2], fimg,
+                                                 self.face_features, nrm[..., 2],
                                                  sigmainv=self.sigmainv, boxlen=self.boxlen, knum=self.knum)
         # per-view IoU and L1 terms, normalised by the global number of views
         mul = soft * self.target_mask

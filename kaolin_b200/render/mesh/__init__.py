@@ -1,4 +1,5 @@
 # mirrors kaolin/render/mesh/__init__.py:1-4 for the hot-path modules
 from .rasterization import *  # noqa: F401,F403
 from .dibr import *  # noqa: F401,F403
-from . import rasterization, dibr  # noqa: F401
+from .utils import *  # noqa: F401,F403
+from . import rasterization, dibr, utils  # noqa: F401

@@ -1,0 +1,144 @@
+"""Mirror of ``kaolin.render.mesh.utils.prepare_vertices`` (kaolin/render/mesh/utils.py:128-175), the producer
+of the rasterization path's inputs, backed by libdibr_b200.so.
+
+The reference composes rotate_translate_points / ``padded @ camera_transform``, perspective_camera, two
+index_vertices_by_faces gathers and face_normals(unit=True) out of ~12 torch kernels and materialises the
+per-vertex camera / image coordinates and two expanded gathers on the way.  Here ONE kernel per direction:
+thread = (camera, face) gathers its three vertices, transforms, projects, and writes the three outputs;
+backward scatters into ``vertices.grad`` (summed over cameras when one mesh is broadcast over the batch).
+
+Only ``vertices`` is differentiable: a camera tensor that requires grad raises (the multi-view fitting loop
+of the reference, examples/tutorial/ian_dibr.py, optimises vertices / textures, not cameras).
+"""
+import torch
+from torch.autograd import Function
+
+from ... import _lib
+
+__all__ = ["prepare_vertices"]
+
+
+def _cam_ptrs(rot, trans, transform):
+    return _lib.ptr(rot), _lib.ptr(trans), _lib.ptr(transform)
+
+
+class PrepareVerticesCuda(Function):
+    """forward(ctx, vertices (Bv,V,3), faces (F,3), proj (3), rot|None, trans|None, transform|None, B)
+    -> face_vertices_camera (B,F,3,3), face_vertices_image (B,F,3,2), face_normals (B,F,3)."""
+    @staticmethod
+    def forward(ctx, vertices, faces, proj, rot, trans, transform, batch):
+        fn = "prepare_vertices"
+        dev = vertices.device
+        suf = _lib.suffix(vertices.dtype, fn)
+        bv, v = vertices.shape[0], vertices.shape[1]
+        f = faces.shape[0]
+        fcam = torch.empty((batch, f, 3, 3), dtype=vertices.dtype, device=dev)
+        fimg = torch.empty((batch, f, 3, 2), dtype=vertices.dtype, device=dev)
+        fnrm = torch.empty((batch, f, 3), dtype=vertices.dtype, device=dev)
+        with torch.cuda.device(dev):
+            code = getattr(_lib.load(), "dibr_prepare_vertices_fwd_" + suf)(
+                _lib.ptr(vertices), _lib.ptr(faces), _lib.ptr(proj), *_cam_ptrs(rot, trans, transform),
+                batch, bv, v, f, _lib.ptr(fcam), _lib.ptr(fimg), _lib.ptr(fnrm), _lib.current_stream(dev))
+        _lib.check(code, fn)
+        ctx.save_for_backward(vertices, faces, proj, rot, trans, transform)
+        ctx.batch = batch
+        ctx.set_materialize_grads(False)
+        return fcam, fimg, fnrm
+
+    @staticmethod
+    def backward(ctx, g_cam, g_img, g_nrm):
+        fn = "prepare_vertices_backward"
+        vertices, faces, proj, rot, trans, transform = ctx.saved_tensors
+        if not ctx.needs_input_grad[0]:
+            return (None,) * 7
+        dev = vertices.device
+        suf = _lib.suffix(vertices.dtype, fn)
+        g_cam = None if g_cam is None else g_cam.contiguous()
+        g_img = None if g_img is None else g_img.contiguous()
+        g_nrm = None if g_nrm is None else g_nrm.contiguous()
+        grad_vertices = torch.empty_like(vertices)
+        with torch.cuda.device(dev):
+            code = getattr(_lib.load(), "dibr_prepare_vertices_bwd_" + suf)(
+                _lib.ptr(g_cam), _lib.ptr(g_img), _lib.ptr(g_nrm), _lib.ptr(vertices), _lib.ptr(faces),
+                _lib.ptr(proj), *_cam_ptrs(rot, trans, transform), ctx.batch, vertices.shape[0],
+                vertices.shape[1], faces.shape[0], _lib.ptr(grad_vertices), _lib.current_stream(dev))
+        _lib.check(code, fn)
+        return grad_vertices, None, None, None, None, None, None
+
+
+def _camera_tensor(name, t, shape_tail, like):
+    if t.dim() != len(shape_tail) + 1 or tuple(t.shape[1:]) != shape_tail:
+        raise RuntimeError(f"prepare_vertices: {name} must be of shape (batch_size, "
+                           f"{', '.join(str(s) for s in shape_tail)}), got {tuple(t.shape)}")
+    if t.device != like.device:
+        raise RuntimeError(f"prepare_vertices: {name} must be on {like.device}, got {t.device}")
+    if t.dtype != like.dtype:
+        raise RuntimeError(f"prepare_vertices: {name} must be of dtype {like.dtype}, got {t.dtype}")
+    if t.requires_grad and torch.is_grad_enabled():
+        raise RuntimeError(f"prepare_vertices: gradients w.r.t. {name} are not implemented "
+                           "(only `vertices` is differentiable)")
+    return t.contiguous()
+
+
+def prepare_vertices(vertices, faces, camera_proj, camera_rot=None, camera_trans=None, camera_transform=None):
+    r"""Move and project vertices to cameras, then index them with faces (reference:
+    kaolin/render/mesh/utils.py:128-175 — same arguments, same three return values).
+
+    Args:
+        vertices (torch.Tensor): of shape :math:`(\text{batch_size}, \text{num_vertices}, 3)`; a batch of 1 is
+            broadcast over the cameras' batch, as torch broadcasting does in the reference.
+        faces (torch.LongTensor): of shape :math:`(\text{num_faces}, 3)`.
+        camera_proj (torch.Tensor): projection vector, of shape :math:`(3, 1)`.
+        camera_rot (torch.Tensor, optional): of shape :math:`(\text{batch_size}, 3, 3)`.
+        camera_trans (torch.Tensor, optional): of shape :math:`(\text{batch_size}, 3)`.
+        camera_transform (torch.Tensor, optional): of shape :math:`(\text{batch_size}, 4, 3)`; replaces
+            ``camera_rot`` and ``camera_trans``.
+
+    Returns:
+        (torch.Tensor, torch.Tensor, torch.Tensor): face_vertices_camera :math:`(B, F, 3, 3)`,
+        face_vertices_image :math:`(B, F, 3, 2)`, face_normals :math:`(B, F, 3)`.
+    """
+    if camera_transform is None:
+        assert camera_trans is not None and camera_rot is not None, \
+            "camera_transform or camera_trans and camera_rot must be defined"
+    else:
+        assert camera_trans is None and camera_rot is None, \
+            "camera_trans and camera_rot must be None when camera_transform is defined"
+    if not vertices.is_cuda:
+        raise RuntimeError("prepare_vertices: vertices must be a CUDA tensor (libdibr_b200.so has no CPU path)")
+    if vertices.dim() != 3 or vertices.shape[-1] != 3:
+        raise RuntimeError(f"prepare_vertices: vertices must be of shape (batch_size, num_vertices, 3), "
+                           f"got {tuple(vertices.shape)}")
+    if faces.dim() != 2 or faces.dtype != torch.long:
+        raise RuntimeError("prepare_vertices: faces must be a LongTensor of shape (num_faces, face_size)")
+    if faces.shape[1] != 3:
+        # kaolin/ops/mesh/trianglemesh.py:326-327
+        raise NotImplementedError("face_normals is only implemented for triangle meshes")
+    if faces.device != vertices.device:
+        raise RuntimeError(f"prepare_vertices: faces must be on {vertices.device}, got {faces.device}")
+    if camera_proj.numel() != 3:
+        raise RuntimeError(f"prepare_vertices: camera_proj must hold 3 values, got {tuple(camera_proj.shape)}")
+    proj = camera_proj.to(device=vertices.device, dtype=vertices.dtype).reshape(3).contiguous()
+    rot = trans = transform = None
+    if camera_transform is None:
+        rot = _camera_tensor("camera_rot", camera_rot, (3, 3), vertices)
+        # legacy.py:35 views camera_trans as (-1, 1, 3)
+        trans = _camera_tensor("camera_trans", camera_trans.reshape(-1, 3), (3,), vertices)
+        batch = rot.shape[0]
+        if trans.shape[0] != batch:
+            if trans.shape[0] != 1:
+                raise RuntimeError("prepare_vertices: camera_rot and camera_trans batch sizes differ")
+            trans = trans.expand(batch, 3).contiguous()
+    else:
+        transform = _camera_tensor("camera_transform", camera_transform, (4, 3), vertices)
+        batch = transform.shape[0]
+    bv = vertices.shape[0]
+    if batch == 1 and bv > 1:                         # one camera broadcast over a batch of meshes
+        batch = bv
+        if transform is None:
+            rot, trans = rot.expand(batch, 3, 3).contiguous(), trans.expand(batch, 3).contiguous()
+        else:
+            transform = transform.expand(batch, 4, 3).contiguous()
+    if bv != 1 and bv != batch:
+        raise RuntimeError(f"prepare_vertices: vertices batch ({bv}) and camera batch ({batch}) do not broadcast")
+    return PrepareVerticesCuda.apply(vertices.contiguous(), faces.contiguous(), proj, rot, trans, transform, batch)

@@ -269,3 +269,49 @@ def dibr_rasterization_forward(height, width, face_vertices_z, face_vertices_ima
     m = 1000. if multiplier is None else multiplier
     soft = dibr_soft_mask_forward(face_vertices_image, face_idx, sigmainv, boxlen, knum, m)[0]
     return feat, soft, face_idx
+
+
+# ---------------------------------------------------------------------------------------------
+# prepare_vertices — CPU restatement in torch ops, differentiable through autograd.
+# Parity status: pinned against tests/golden/prepare_vertices.npz (outputs and gradients produced by the
+# reference's own modules, tests/golden/make_golden_prepare.py).
+def rotate_translate_points(points, camera_rot, camera_trans):
+    """kaolin/render/camera/legacy.py:22-37: (points - trans) @ rot^T."""
+    translated = points - camera_trans.view(-1, 1, 3)
+    return torch.matmul(translated, camera_rot.permute(0, 2, 1))
+
+
+def perspective_camera(points, camera_proj):
+    """kaolin/render/camera/legacy.py:120-139: (x*p0, y*p1) / (z*p2)."""
+    projected = points * camera_proj.view(-1, 1, 3)
+    return projected[:, :, :2] / projected[:, :, 2:3]
+
+
+def index_vertices_by_faces(vertices_features, faces):
+    """kaolin/ops/mesh/mesh.py:24-45: gather (B,V,k) by (F,3) -> (B,F,3,k)."""
+    return vertices_features[:, faces]
+
+
+def face_normals(face_vertices, unit=False):
+    """kaolin/ops/mesh/trianglemesh.py:313-336."""
+    e0 = face_vertices[:, :, 1] - face_vertices[:, :, 0]
+    e1 = face_vertices[:, :, 2] - face_vertices[:, :, 0]
+    n = torch.cross(e0, e1, dim=2)
+    if unit:
+        n = n / (n.norm(dim=2, keepdim=True) + 1e-10)
+    return n
+
+
+def prepare_vertices(vertices, faces, camera_proj, camera_rot=None, camera_trans=None, camera_transform=None):
+    """kaolin/render/mesh/utils.py:128-175."""
+    if camera_transform is None:
+        assert camera_trans is not None and camera_rot is not None
+        vertices_camera = rotate_translate_points(vertices, camera_rot, camera_trans)
+    else:
+        assert camera_trans is None and camera_rot is None
+        padded = torch.nn.functional.pad(vertices, (0, 1), mode='constant', value=1.)
+        vertices_camera = padded @ camera_transform
+    vertices_image = perspective_camera(vertices_camera, camera_proj)
+    face_vertices_camera = index_vertices_by_faces(vertices_camera, faces)
+    face_vertices_image = index_vertices_by_faces(vertices_image, faces)
+    return face_vertices_camera, face_vertices_image, face_normals(face_vertices_camera, unit=True)

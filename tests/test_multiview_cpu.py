@@ -30,7 +30,7 @@ def test_shard_range_partitions():
 
 
 def _surrogate_loss(vertices, faces, rot, trans, n_total):
-    fcam, fimg, nrm = mv.prepare_vertices(vertices, faces, rot, trans)
+    fcam, fimg, nrm = synth.prepare_vertices(vertices, faces, rot, trans)
     return (fimg.square().sum() + (nrm[..., 2] * fcam[..., 2].mean(-1)).sum()) / n_total
 
 
