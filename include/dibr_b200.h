@@ -41,7 +41,7 @@
 extern "C" {
 #endif
 
-#define DIBR_ABI_VERSION 3
+#define DIBR_ABI_VERSION 4
 
 enum {
   DIBR_OK = 0,
@@ -227,6 +227,46 @@ int dibr_prepare_vertices_bwd_f64(const double* grad_camera, const double* grad_
                                   const double* transform, int B, int Bv, int V, int F,
                                   double* grad_vertices, void* stream);
 
+/* ---------------------------------------------------------------------------------------------
+ * texture_mapping — the consumer of the rasterizer's interpolated uv map.
+ *  Replaces kaolin/render/mesh/utils.py:23-76 (clamp to [0,1], *2-1, flip y,
+ *  torch.nn.functional.grid_sample(mode, align_corners=False, padding_mode='border'), permute to
+ *  channels-last) and, when `mask` is non-NULL, the tutorial epilogue torch.clamp(image * mask, 0., 1.)
+ *  (examples/tutorial/ian_dibr.py:254-258) by one kernel per direction.
+ *  uv (B,N,2) with N = h*w (dense) or num_points (sparse); texture_maps (Bt,C,Ht,Wt) with Bt == B, or
+ *  Bt == 1 for one texture shared by the batch; mask (B,N) or NULL; mode 0 = nearest, 1 = bilinear;
+ *  out (B,N,C).  _bwd: grad_uv (B,N,2), grad_texture_maps (Bt,C,Ht,Wt; zero-filled and accumulated by the
+ *  library), grad_mask (B,N) — each may be NULL when not needed (grad_mask requires mask).
+ */
+int dibr_texture_mapping_fwd_f32(const float* uv, const float* texture_maps, const float* mask, int B,
+                                 int64_t N, int Bt, int C, int Ht, int Wt, int mode, float* out, void* stream);
+int dibr_texture_mapping_fwd_f64(const double* uv, const double* texture_maps, const double* mask, int B,
+                                 int64_t N, int Bt, int C, int Ht, int Wt, int mode, double* out, void* stream);
+int dibr_texture_mapping_bwd_f32(const float* grad_out, const float* uv, const float* texture_maps,
+                                 const float* mask, int B, int64_t N, int Bt, int C, int Ht, int Wt, int mode,
+                                 float* grad_uv, float* grad_texture_maps, float* grad_mask, void* stream);
+int dibr_texture_mapping_bwd_f64(const double* grad_out, const double* uv, const double* texture_maps,
+                                 const double* mask, int B, int64_t N, int Bt, int C, int Ht, int Wt, int mode,
+                                 double* grad_uv, double* grad_texture_maps, double* grad_mask, void* stream);
+
+/* ---------------------------------------------------------------------------------------------
+ * mask_iou — the consumer of soft_mask.
+ *  Replaces kaolin/metrics/render.py:18-40: loss = 1 - mean_b( sum(l*r) / (sum(l + r - l*r) + 1e-10) ).
+ *  lhs, rhs (B,P) with P = height*width.  _fwd writes the scalar loss (device) and sums (B,2) = per-view
+ *  {sum(l*r), sum(l+r-l*r)}, which _bwd consumes; the reduction is two-stage and deterministic (no float
+ *  atomics).  ws: dibr_mask_iou_workspace_bytes(B, P, elem_size) bytes.  _bwd: grad_loss is a DEVICE scalar;
+ *  grad_lhs / grad_rhs (B,P) may each be NULL.
+ */
+size_t dibr_mask_iou_workspace_bytes(int B, int64_t P, int elem_size);
+int dibr_mask_iou_fwd_f32(const float* lhs, const float* rhs, int B, int64_t P, float* loss, float* sums,
+                          void* ws, size_t ws_bytes, void* stream);
+int dibr_mask_iou_fwd_f64(const double* lhs, const double* rhs, int B, int64_t P, double* loss, double* sums,
+                          void* ws, size_t ws_bytes, void* stream);
+int dibr_mask_iou_bwd_f32(const float* grad_loss, const float* lhs, const float* rhs, const float* sums,
+                          int B, int64_t P, float* grad_lhs, float* grad_rhs, void* stream);
+int dibr_mask_iou_bwd_f64(const double* grad_loss, const double* lhs, const double* rhs, const double* sums,
+                          int B, int64_t P, double* grad_lhs, double* grad_rhs, void* stream);
+
 /* Counters for bench.py's `gpu_launches`: number of kernels this library has launched from the
  * calling process since load / since the last reset (relaxed atomic; diagnostics only). */
 uint64_t dibr_kernel_launch_count(void);
@@ -245,7 +285,11 @@ enum {
   DIBR_KERNEL_SOFT_BWD = 6,
   DIBR_KERNEL_PREPARE_FWD = 7,
   DIBR_KERNEL_PREPARE_BWD = 8,
-  DIBR_KERNEL_COUNT = 9
+  DIBR_KERNEL_TEXTURE_FWD = 9,
+  DIBR_KERNEL_TEXTURE_BWD = 10,
+  DIBR_KERNEL_IOU_FWD = 11,
+  DIBR_KERNEL_IOU_BWD = 12,
+  DIBR_KERNEL_COUNT = 13
 };
 int dibr_profile_next_launch(int kernel_id, void* start_event, void* stop_event);
 

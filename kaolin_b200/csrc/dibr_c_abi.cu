@@ -6,6 +6,8 @@
 #include "dibr_raster_bwd.cuh"
 #include "dibr_soft_mask.cuh"
 #include "dibr_prepare.cuh"
+#include "dibr_texture.cuh"
+#include "dibr_losses.cuh"
 
 #include <atomic>
 #include <cstdio>
@@ -351,6 +353,76 @@ int prepare_impl(bool backward, const T* g_cam, const T* g_img, const T* g_nrm, 
   return DIBR_OK;
 }
 
+// texture_mapping (utils.py:23-76) [+ clamp(image * mask, 0, 1)]: one kernel each way.
+template <typename T>
+int texture_impl(bool backward, const T* g_out, const T* uv, const T* tex, const T* mask, int B, int64_t N, int Bt,
+                 int C, int Ht, int Wt, int mode, T* out, T* g_uv, T* g_tex, T* g_mask, void* stream) {
+  if (B < 0 || N < 0 || C < 0 || Ht < 0 || Wt < 0 || (Bt != 1 && Bt != B)) return DIBR_ERR_INVALID_ARGUMENT;
+  if (mode != TEX_NEAREST && mode != TEX_BILINEAR) return DIBR_ERR_INVALID_ARGUMENT;
+  if ((int64_t)B * N >= (int64_t)1 << 40 || Ht > 32768 || Wt > 32768) return DIBR_ERR_TOO_LARGE;
+  if (g_mask && !mask) return DIBR_ERR_INVALID_ARGUMENT;
+  cudaStream_t s = static_cast<cudaStream_t>(stream);
+  const int64_t n = (int64_t)B * N;
+  const size_t tex_elems = (size_t)Bt * C * Ht * Wt;
+  if (backward && g_tex && tex_elems > 0) CUDA_TRY(cudaMemsetAsync(g_tex, 0, tex_elems * sizeof(T), s));
+  if (n == 0 || C == 0) return DIBR_OK;
+  if (Ht == 0 || Wt == 0) return DIBR_ERR_INVALID_ARGUMENT;       // grid_sample rejects empty spatial sizes
+  if (!uv || !tex || (backward ? !g_out : !out)) return DIBR_ERR_INVALID_ARGUMENT;
+  TextureParams<T> tp;
+  tp.uv = uv; tp.tex = tex; tp.mask = mask; tp.B = B; tp.Bt = Bt; tp.C = C; tp.Ht = Ht; tp.Wt = Wt; tp.N = N;
+  tp.mode = mode; tp.out = out; tp.g_out = g_out; tp.g_uv = g_uv; tp.g_tex = g_tex; tp.g_mask = g_mask;
+  const unsigned nb = (unsigned)((n + 255) / 256);
+  if (backward) {
+    { ProfScope ps(DIBR_KERNEL_TEXTURE_BWD, s); texture_mapping_bwd_kernel<T><<<nb, 256, 0, s>>>(tp); }
+    LAUNCH_CHECK("texture_mapping_bwd_kernel");
+  } else {
+    { ProfScope ps(DIBR_KERNEL_TEXTURE_FWD, s); texture_mapping_fwd_kernel<T><<<nb, 256, 0, s>>>(tp); }
+    LAUNCH_CHECK("texture_mapping_fwd_kernel");
+  }
+  return DIBR_OK;
+}
+
+// mask_iou (kaolin/metrics/render.py:18-40)
+inline int iou_chunks(int64_t P) { return (int)((P + IOU_CHUNK - 1) / IOU_CHUNK); }
+size_t iou_ws_bytes(int B, int64_t P, int elem) {
+  if (B <= 0 || P <= 0) return 256;
+  return align_up((size_t)B * iou_chunks(P) * 2 * (size_t)elem);
+}
+template <typename T>
+int iou_fwd_impl(const T* lhs, const T* rhs, int B, int64_t P, T* loss, T* sums, void* ws, size_t ws_bytes,
+                 void* stream) {
+  if (B < 0 || P < 0 || !loss) return DIBR_ERR_INVALID_ARGUMENT;
+  if (B > 65535 || P >= (int64_t)1 << 40) return DIBR_ERR_TOO_LARGE;
+  cudaStream_t s = static_cast<cudaStream_t>(stream);
+  const int chunks = iou_chunks(P);
+  if (B > 0 && (!sums || (P > 0 && (!lhs || !rhs)))) return DIBR_ERR_INVALID_ARGUMENT;
+  if (B > 0 && P > 0) {
+    if (!ws || ws_bytes < iou_ws_bytes(B, P, (int)sizeof(T))) return DIBR_ERR_WORKSPACE;
+    { ProfScope ps(DIBR_KERNEL_IOU_FWD, s);
+      mask_iou_partial_kernel<T><<<dim3((unsigned)chunks, (unsigned)B), 256, 0, s>>>(lhs, rhs, P, chunks,
+                                                                                      static_cast<T*>(ws)); }
+    LAUNCH_CHECK("mask_iou_partial_kernel");
+  }
+  // B == 0: mean of an empty tensor is NaN in torch -> 1 - NaN; the finish kernel divides 0 by 0 likewise
+  mask_iou_finish_kernel<T><<<1, 256, 0, s>>>(static_cast<const T*>(ws), B, P > 0 ? chunks : 0, sums, loss);
+  LAUNCH_CHECK("mask_iou_finish_kernel");
+  return DIBR_OK;
+}
+template <typename T>
+int iou_bwd_impl(const T* g_loss, const T* lhs, const T* rhs, const T* sums, int B, int64_t P, T* g_lhs, T* g_rhs,
+                 void* stream) {
+  if (B < 0 || P < 0) return DIBR_ERR_INVALID_ARGUMENT;
+  if (B > 65535 || P >= (int64_t)1 << 40) return DIBR_ERR_TOO_LARGE;
+  if (B == 0 || P == 0 || (!g_lhs && !g_rhs)) return DIBR_OK;
+  if (!g_loss || !lhs || !rhs || !sums) return DIBR_ERR_INVALID_ARGUMENT;
+  cudaStream_t s = static_cast<cudaStream_t>(stream);
+  { ProfScope ps(DIBR_KERNEL_IOU_BWD, s);
+    mask_iou_bwd_kernel<T><<<dim3((unsigned)iou_chunks(P), (unsigned)B), 256, 0, s>>>(lhs, rhs, sums, g_loss, P,
+                                                                                       B, g_lhs, g_rhs); }
+  LAUNCH_CHECK("mask_iou_bwd_kernel");
+  return DIBR_OK;
+}
+
 }  // namespace
 
 #define DIBR_API extern "C" __attribute__((visibility("default")))
@@ -380,6 +452,10 @@ DIBR_API int dibr_profile_next_launch(int kernel_id, void* start_event, void* st
 DIBR_API size_t dibr_workspace_bytes(int batch_size, int64_t total_faces, int height, int width) {
   if (batch_size < 0 || total_faces < 0 || height < 0 || width < 0) return 0;
   return ws_layout(batch_size, total_faces, make_geometry(batch_size, height, width)).total;
+}
+
+DIBR_API size_t dibr_mask_iou_workspace_bytes(int B, int64_t P, int elem_size) {
+  return iou_ws_bytes(B, P, elem_size);
 }
 
 #define DEFINE_ENTRY_POINTS(SUF, T)                                                                           \
@@ -476,6 +552,27 @@ DIBR_API size_t dibr_workspace_bytes(int batch_size, int64_t total_faces, int he
                                                int F, T* grad_vertices, void* stream) {                      \
     return prepare_impl<T>(true, grad_camera, grad_image, grad_normals, vertices, faces, camera_proj, rot,   \
                            trans, transform, B, Bv, V, F, nullptr, nullptr, nullptr, grad_vertices, stream); \
+  }                                                                                                           \
+  DIBR_API int dibr_texture_mapping_fwd_##SUF(const T* uv, const T* texture_maps, const T* mask, int B,      \
+                                              int64_t N, int Bt, int C, int Ht, int Wt, int mode, T* out,    \
+                                              void* stream) {                                                \
+    return texture_impl<T>(false, nullptr, uv, texture_maps, mask, B, N, Bt, C, Ht, Wt, mode, out, nullptr,  \
+                           nullptr, nullptr, stream);                                                         \
+  }                                                                                                           \
+  DIBR_API int dibr_texture_mapping_bwd_##SUF(const T* grad_out, const T* uv, const T* texture_maps,         \
+                                              const T* mask, int B, int64_t N, int Bt, int C, int Ht,        \
+                                              int Wt, int mode, T* grad_uv, T* grad_texture_maps,            \
+                                              T* grad_mask, void* stream) {                                  \
+    return texture_impl<T>(true, grad_out, uv, texture_maps, mask, B, N, Bt, C, Ht, Wt, mode, nullptr,       \
+                           grad_uv, grad_texture_maps, grad_mask, stream);                                    \
+  }                                                                                                           \
+  DIBR_API int dibr_mask_iou_fwd_##SUF(const T* lhs, const T* rhs, int B, int64_t P, T* loss, T* sums,       \
+                                       void* ws, size_t ws_bytes, void* stream) {                            \
+    return iou_fwd_impl<T>(lhs, rhs, B, P, loss, sums, ws, ws_bytes, stream);                                 \
+  }                                                                                                           \
+  DIBR_API int dibr_mask_iou_bwd_##SUF(const T* grad_loss, const T* lhs, const T* rhs, const T* sums,        \
+                                       int B, int64_t P, T* grad_lhs, T* grad_rhs, void* stream) {           \
+    return iou_bwd_impl<T>(grad_loss, lhs, rhs, sums, B, P, grad_lhs, grad_rhs, stream);                      \
   }
 
 DEFINE_ENTRY_POINTS(f32, float)

@@ -103,6 +103,7 @@ class MultiViewOptimizer:
 
     def loss(self):
         from .render.mesh import dibr_rasterization, prepare_vertices
+        from .metrics.render import mask_iou as fused_mask_iou
         verts = self.vertices if self.vertices.dim() == 3 else self.vertices.unsqueeze(0)
         fcam, fimg, nrm = prepare_vertices(verts, self.faces, self.proj, camera_rot=self.rot,
                                            camera_trans=self.trans)
@@ -110,11 +111,9 @@ class MultiViewOptimizer:
         img, soft, face_idx = dibr_rasterization(self.height, self.width, fcam[..., 2], fimg,
                                                  self.face_features, nrm[..., 2],
                                                  sigmainv=self.sigmainv, boxlen=self.boxlen, knum=self.knum)
-        # per-view IoU and L1 terms, normalised by the global number of views
-        mul = soft * self.target_mask
-        add = soft + self.target_mask
-        iou = torch.sum(mul.reshape(b, -1), 1) / (torch.sum((add - mul).reshape(b, -1), 1) + 1e-10)
-        l_mask = torch.sum(1.0 - iou) / self.n_views_total
+        # per-view IoU and L1 terms, normalised by the global number of views:
+        # sum_local(1 - iou_b) / n_total = mask_iou(local) * b / n_total   (fused reduction + analytic backward)
+        l_mask = fused_mask_iou(soft, self.target_mask) * (b / self.n_views_total)
         l_feat = torch.sum(torch.abs(img - self.target_feat).mean(dim=(1, 2, 3))) / self.n_views_total
         return l_mask + l_feat, soft, face_idx
 

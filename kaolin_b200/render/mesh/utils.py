@@ -1,5 +1,6 @@
 """Mirror of ``kaolin.render.mesh.utils.prepare_vertices`` (kaolin/render/mesh/utils.py:128-175), the producer
-of the rasterization path's inputs, backed by libdibr_b200.so.
+of the rasterization path's inputs, and of ``texture_mapping`` (utils.py:23-76), the consumer of its
+interpolated uv map, backed by libdibr_b200.so.
 
 The reference composes rotate_translate_points / ``padded @ camera_transform``, perspective_camera, two
 index_vertices_by_faces gathers and face_normals(unit=True) out of ~12 torch kernels and materialises the
@@ -15,7 +16,7 @@ from torch.autograd import Function
 
 from ... import _lib
 
-__all__ = ["prepare_vertices"]
+__all__ = ["prepare_vertices", "texture_mapping"]
 
 
 def _cam_ptrs(rot, trans, transform):
@@ -142,3 +143,99 @@ def prepare_vertices(vertices, faces, camera_proj, camera_rot=None, camera_trans
     if bv != 1 and bv != batch:
         raise RuntimeError(f"prepare_vertices: vertices batch ({bv}) and camera batch ({batch}) do not broadcast")
     return PrepareVerticesCuda.apply(vertices.contiguous(), faces.contiguous(), proj, rot, trans, transform, batch)
+
+
+# ----------------------------------------------------------------------------------------------------------
+_TEX_MODES = {"nearest": 0, "bilinear": 1}
+
+
+class TextureMappingCuda(Function):
+    """forward(ctx, uv (B,N,2), texture_maps (Bt,C,Ht,Wt), mask (B,N)|None, mode) -> (B,N,C)."""
+    @staticmethod
+    def forward(ctx, uv, texture_maps, mask, mode):
+        fn = "texture_mapping"
+        dev = uv.device
+        suf = _lib.suffix(uv.dtype, fn)
+        b, n = uv.shape[0], uv.shape[1]
+        bt, c, ht, wt = texture_maps.shape
+        out = torch.empty((b, n, c), dtype=uv.dtype, device=dev)
+        with torch.cuda.device(dev):
+            code = getattr(_lib.load(), "dibr_texture_mapping_fwd_" + suf)(
+                _lib.ptr(uv), _lib.ptr(texture_maps), _lib.ptr(mask), b, n, bt, c, ht, wt, mode, _lib.ptr(out),
+                _lib.current_stream(dev))
+        _lib.check(code, fn)
+        ctx.save_for_backward(uv, texture_maps, mask)
+        ctx.mode = mode
+        return out
+
+    @staticmethod
+    def backward(ctx, grad_out):
+        fn = "texture_mapping_backward"
+        uv, texture_maps, mask = ctx.saved_tensors
+        dev = uv.device
+        suf = _lib.suffix(uv.dtype, fn)
+        need_uv, need_tex, need_mask = ctx.needs_input_grad[0], ctx.needs_input_grad[1], \
+            mask is not None and ctx.needs_input_grad[2]
+        g_uv = torch.empty_like(uv) if need_uv else None
+        g_tex = torch.empty_like(texture_maps) if need_tex else None
+        g_mask = torch.empty_like(mask) if need_mask else None
+        b, n = uv.shape[0], uv.shape[1]
+        bt, c, ht, wt = texture_maps.shape
+        with torch.cuda.device(dev):
+            code = getattr(_lib.load(), "dibr_texture_mapping_bwd_" + suf)(
+                _lib.ptr(grad_out.contiguous()), _lib.ptr(uv), _lib.ptr(texture_maps), _lib.ptr(mask), b, n, bt, c,
+                ht, wt, ctx.mode, _lib.ptr(g_uv), _lib.ptr(g_tex), _lib.ptr(g_mask), _lib.current_stream(dev))
+        _lib.check(code, fn)
+        return g_uv, g_tex, g_mask, None
+
+
+def texture_mapping(texture_coordinates, texture_maps, mode='nearest', mask=None):
+    r"""Interpolates texture_maps by dense or sparse texture_coordinates (reference:
+    kaolin/render/mesh/utils.py:23-76 — same arguments and return value).
+
+    Args:
+        texture_coordinates (torch.FloatTensor): dense :math:`(\text{batch_size}, h, w, 2)` or sparse
+            :math:`(\text{batch_size}, \text{num_points}, 2)`, OpenGL convention in [0, 1] (values outside
+            are clamped, y goes up).
+        texture_maps (torch.FloatTensor): :math:`(\text{batch_size}, \text{num_channels}, h', w')`.
+            Extension: a batch of 1 is shared by all ``batch_size`` coordinate maps (no ``repeat`` needed).
+        mode (str): ``'nearest'`` or ``'bilinear'`` (``torch.nn.functional.grid_sample`` with
+            ``align_corners=False, padding_mode='border'``).
+        mask (torch.FloatTensor, optional): extension — :math:`(\text{batch_size}, h, w[, 1])`; when given the
+            result is ``torch.clamp(texture * mask, 0., 1.)`` computed in the same kernel (the epilogue of
+            examples/tutorial/ian_dibr.py:254-258).
+
+    Returns:
+        (torch.FloatTensor): :math:`(\text{batch_size}, h, w, \text{num_channels})` or
+        :math:`(\text{batch_size}, \text{num_points}, \text{num_channels})`.
+    """
+    if mode not in _TEX_MODES:
+        # torch.nn.functional.grid_sample raises ValueError for an unknown mode
+        raise ValueError(f"nn.functional.grid_sample(): expected mode to be 'bilinear', 'nearest' or "
+                         f"'bicubic', but got: '{mode}'" if mode != 'bicubic' else
+                         "texture_mapping: mode 'bicubic' is not implemented by libdibr_b200.so")
+    if not texture_coordinates.is_cuda:
+        raise RuntimeError("texture_mapping: texture_coordinates must be a CUDA tensor "
+                           "(libdibr_b200.so has no CPU path)")
+    if texture_coordinates.dim() not in (3, 4) or texture_coordinates.shape[-1] != 2:
+        raise RuntimeError(f"texture_mapping: texture_coordinates must be of shape (batch_size, h, w, 2) or "
+                           f"(batch_size, num_points, 2), got {tuple(texture_coordinates.shape)}")
+    if texture_maps.dim() != 4:
+        raise RuntimeError(f"texture_mapping: texture_maps must be of shape (batch_size, num_channels, h', w'), "
+                           f"got {tuple(texture_maps.shape)}")
+    if texture_maps.device != texture_coordinates.device or texture_maps.dtype != texture_coordinates.dtype:
+        raise RuntimeError("texture_mapping: texture_maps and texture_coordinates must share device and dtype")
+    batch_size = texture_coordinates.shape[0]
+    if texture_maps.shape[0] not in (1, batch_size):
+        raise RuntimeError(f"texture_mapping: texture_maps batch ({texture_maps.shape[0]}) does not match "
+                           f"texture_coordinates batch ({batch_size})")
+    num_channels = texture_maps.shape[1]
+    uv = texture_coordinates.reshape(batch_size, -1, 2).contiguous()
+    m = None
+    if mask is not None:
+        if mask.numel() != uv.shape[0] * uv.shape[1]:
+            raise RuntimeError(f"texture_mapping: mask of shape {tuple(mask.shape)} does not match the "
+                               f"texture_coordinates {tuple(texture_coordinates.shape)}")
+        m = mask.to(uv.dtype).reshape(batch_size, -1).contiguous()
+    out = TextureMappingCuda.apply(uv, texture_maps.contiguous(), m, _TEX_MODES[mode])
+    return out.reshape(batch_size, *texture_coordinates.shape[1:-1], num_channels)

@@ -315,3 +315,32 @@ def prepare_vertices(vertices, faces, camera_proj, camera_rot=None, camera_trans
     face_vertices_camera = index_vertices_by_faces(vertices_camera, faces)
     face_vertices_image = index_vertices_by_faces(vertices_image, faces)
     return face_vertices_camera, face_vertices_image, face_normals(face_vertices_camera, unit=True)
+
+
+# ---------------------------------------------------------------------------------------------
+# texture_mapping and mask_iou (row 3) — CPU restatements in torch ops.
+# Parity status: pinned against the reference's known-answer tests
+# (tests/python/kaolin/render/mesh/test_utils.py:61-112, tests/python/kaolin/metrics/test_render.py:24-53),
+# restated in tests/test_texture_losses.py.
+def texture_mapping(texture_coordinates, texture_maps, mode='nearest'):
+    """kaolin/render/mesh/utils.py:23-76."""
+    batch_size = texture_coordinates.shape[0]
+    num_channels = texture_maps.shape[1]
+    coords = texture_coordinates.reshape(batch_size, -1, 1, 2)
+    coords = torch.clamp(coords, 0., 1.) * 2 - 1                       # utils.py:62-63
+    coords = torch.stack([coords[..., 0], -coords[..., 1]], dim=-1)    # utils.py:64 (reverse y), out of place
+    sampled = torch.nn.functional.grid_sample(texture_maps, coords, mode=mode, align_corners=False,
+                                              padding_mode='border')
+    sampled = sampled.permute(0, 2, 3, 1)
+    return sampled.reshape(batch_size, *texture_coordinates.shape[1:-1], num_channels)
+
+
+def mask_iou(lhs_mask, rhs_mask):
+    """kaolin/metrics/render.py:18-40."""
+    batch_size = lhs_mask.shape[0]
+    assert rhs_mask.shape == lhs_mask.shape
+    sil_mul = lhs_mask * rhs_mask
+    sil_add = lhs_mask + rhs_mask
+    iou_up = torch.sum(sil_mul.reshape(batch_size, -1), dim=1)
+    iou_down = torch.sum((sil_add - sil_mul).reshape(batch_size, -1), dim=1)
+    return 1.0 - torch.mean(iou_up / (iou_down + 1e-10))
