@@ -1,0 +1,74 @@
+"""The reference's own CUDA kernels (oracle/_ref/ref_C.so: kaolin/csrc/render/mesh/*.cu compiled unmodified for
+sm_100a) behind the reference's torch glue, timed on the same B200 next to this library, on BASELINE.json
+configs 1 and 2 (rasterize + dibr_soft_mask, forward + backward).  Device-timed with CUDA events.  The table is
+written to gpurun_out/vs_reference_cuda.json when that directory exists (DESIGN.md §7 quotes it)."""
+import json
+import os
+
+import pytest
+import torch
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+RESULTS = {}
+
+
+def _time(fn, iters, warm):
+    for _ in range(warm):
+        fn()
+    torch.cuda.synchronize()
+    a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    a.record()
+    for _ in range(iters):
+        fn()
+    b.record()
+    torch.cuda.synchronize()
+    return a.elapsed_time(b) / iters
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("name,iters", [("c1", 10), ("c2", 2)])
+def test_step_time_vs_reference_cuda_kernels(name, iters):
+    import kaolin_b200 as kal
+    from kaolin_b200 import synth
+    from oracle import oracle as O
+    ref_C = O.load_ref_C()
+    if ref_C is None:
+        pytest.skip("oracle/_ref/ref_C.so not built")
+    d = synth.make_inputs(name)
+    Hh, Ww = d["H"], d["W"]
+    z = d["face_vertices_z"].cuda()
+    img = d["face_vertices_image"].cuda()
+    feats = torch.cat([f.cuda() for f in d["face_features"]], -1).contiguous()
+    valid = None if d["face_normals_z"] is None else (d["face_normals_z"].cuda() >= 0.)
+    g = torch.Generator().manual_seed(1)
+    B, C = z.shape[0], feats.shape[-1]
+    g_feat = torch.rand(B, Hh, Ww, C, generator=g).cuda()
+    g_soft = torch.rand(B, Hh, Ww, generator=g).cuda()
+    sig, box, knum, mult, eps = d["sigmainv"], d["boxlen"], d["knum"], 1000., 1e-8
+
+    def ours():
+        il, fl = img.clone().requires_grad_(True), feats.clone().requires_grad_(True)
+        out, idx = kal.render.mesh.rasterize(Hh, Ww, z, il, fl, valid, mult, eps)
+        soft = kal.render.mesh.dibr_soft_mask(il, idx, sig, box, knum, mult)
+        torch.autograd.backward([out, soft], [g_feat, g_soft])
+        return il.grad
+
+    def reference():            # RasterizeCuda / DibrSoftMaskCuda forward+backward of the reference, on ref_C
+        r_feat, r_idx, r_w = O.rasterize_forward(Hh, Ww, z, img, feats, valid, mult, eps, backend=ref_C)
+        r_soft, r_img_m, r_prob, r_cidx, r_ctype = O.dibr_soft_mask_forward(img, r_idx, sig, box, knum, mult,
+                                                                             backend=ref_C)
+        gi, gf = O.rasterize_backward(g_feat, r_idx, r_w, img, feats, eps, backend=ref_C,
+                                      interpolated_features=r_feat)
+        gs = O.dibr_soft_mask_backward(g_soft, r_soft, r_img_m, r_idx, r_prob, r_cidx, r_ctype, sig, mult,
+                                       backend=ref_C)
+        return gi + gs
+
+    t_ours = _time(ours, iters * 5, 3)
+    t_ref = _time(reference, iters, 1)
+    RESULTS[name] = {"ours_ms": round(t_ours, 4), "reference_cuda_kernels_ms": round(t_ref, 3),
+                     "speedup": round(t_ref / t_ours, 1), "pixels": B * Hh * Ww, "faces": int(z.shape[1])}
+    out = os.path.join(ROOT, "gpurun_out")
+    if os.path.isdir(out):
+        with open(os.path.join(out, "vs_reference_cuda.json"), "w") as fh:
+            json.dump(RESULTS, fh, indent=1)
+    assert t_ours < t_ref
