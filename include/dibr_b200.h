@@ -41,7 +41,7 @@
 extern "C" {
 #endif
 
-#define DIBR_ABI_VERSION 4
+#define DIBR_ABI_VERSION 5
 
 enum {
   DIBR_OK = 0,
@@ -267,6 +267,49 @@ int dibr_mask_iou_bwd_f32(const float* grad_loss, const float* lhs, const float*
 int dibr_mask_iou_bwd_f64(const double* grad_loss, const double* lhs, const double* rhs, const double* sums,
                           int B, int64_t P, double* grad_lhs, double* grad_rhs, void* stream);
 
+/* ---------------------------------------------------------------------------------------------
+ * deftet_sparse_render — DefTet volumetric renderer on the path's bins.
+ *  For every query point: the first knum faces IN FACE ORDER that contain the point (half-open bbox test,
+ *  barycentric weights >= 0) with depth in [render_ranges[...,0], render_ranges[...,1]).
+ *  reference-shaped dibr_deftet_forward_* = deftet_sparse_render_forward_cuda (kaolin/csrc/render/mesh/deftet.h,
+ *    deftet.cpp:47-109; kernel deftet_cuda.cu:31-190): face_bboxes (B,F,4) given; outputs in face order with the
+ *    reference's fills: face_idx (B,P,knum) int64 (-1), pixel_depth (-inf), w0, w1 (0).
+ *  _fused = DeftetSparseRenderer.forward (kaolin/render/mesh/deftet.py:272-318): bboxes computed in-kernel,
+ *    entries sorted by depth (descending; equal depths keep face order), features of n_feat tensors
+ *    (B,F,3,channels[t]) interpolated into outs[t] (B,P,knum,channels[t]) (no torch.cat), weights (B,P,knum,3)
+ *    optional (backward needs them).
+ *  dibr_deftet_backward_* = deftet_sparse_render_backward_cuda (deftet.cpp:111-170, deftet_cuda.cu:240-410) for
+ *    a list of feature tensors; grad_img (B,F,3,2) and grad_feats[t] are zero-filled and accumulated by the
+ *    library; grad_img or any grad_feats[t] may be NULL.
+ *  knum <= 4064.  ws: dibr_deftet_workspace_bytes(B, total_faces).  eps: float, as in the reference.
+ */
+size_t dibr_deftet_workspace_bytes(int batch_size, int64_t total_faces);
+int dibr_deftet_forward_f32(const float* face_vertices_z, const float* face_vertices_image, const float* face_bboxes,
+                            const float* pixel_coords, const float* render_ranges, int B, int F, int P, int knum,
+                            float eps, int64_t* face_idx, float* pixel_depth, float* w0, float* w1,
+                            void* ws, size_t ws_bytes, void* stream);
+int dibr_deftet_forward_f64(const double* face_vertices_z, const double* face_vertices_image,
+                            const double* face_bboxes, const double* pixel_coords, const double* render_ranges,
+                            int B, int F, int P, int knum, float eps, int64_t* face_idx, double* pixel_depth,
+                            double* w0, double* w1, void* ws, size_t ws_bytes, void* stream);
+int dibr_deftet_render_fused_f32(const float* pixel_coords, const float* render_ranges, const float* face_vertices_z,
+                                 const float* face_vertices_image, const float* const* feats, const int* channels,
+                                 int n_feat, int B, int F, int P, int knum, float eps, float* const* outs,
+                                 int64_t* face_idx, float* weights, void* ws, size_t ws_bytes, void* stream);
+int dibr_deftet_render_fused_f64(const double* pixel_coords, const double* render_ranges,
+                                 const double* face_vertices_z, const double* face_vertices_image,
+                                 const double* const* feats, const int* channels, int n_feat, int B, int F, int P,
+                                 int knum, float eps, double* const* outs, int64_t* face_idx, double* weights,
+                                 void* ws, size_t ws_bytes, void* stream);
+int dibr_deftet_backward_f32(const float* const* grad_outs, const int64_t* face_idx, const float* weights,
+                             const float* face_vertices_image, const float* const* feats, const int* channels,
+                             int n_feat, int B, int F, int P, int knum, float eps, float* grad_img,
+                             float* const* grad_feats, void* stream);
+int dibr_deftet_backward_f64(const double* const* grad_outs, const int64_t* face_idx, const double* weights,
+                             const double* face_vertices_image, const double* const* feats, const int* channels,
+                             int n_feat, int B, int F, int P, int knum, float eps, double* grad_img,
+                             double* const* grad_feats, void* stream);
+
 /* Counters for bench.py's `gpu_launches`: number of kernels this library has launched from the
  * calling process since load / since the last reset (relaxed atomic; diagnostics only). */
 uint64_t dibr_kernel_launch_count(void);
@@ -289,7 +332,9 @@ enum {
   DIBR_KERNEL_TEXTURE_BWD = 10,
   DIBR_KERNEL_IOU_FWD = 11,
   DIBR_KERNEL_IOU_BWD = 12,
-  DIBR_KERNEL_COUNT = 13
+  DIBR_KERNEL_DEFTET_FWD = 13,
+  DIBR_KERNEL_DEFTET_BWD = 14,
+  DIBR_KERNEL_COUNT = 15
 };
 int dibr_profile_next_launch(int kernel_id, void* start_event, void* stop_event);
 

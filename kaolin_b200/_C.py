@@ -1,4 +1,4 @@
-"""``kaolin_b200._C.render.mesh`` — the reference's four native ops (kaolin/csrc/bindings.cpp:75-80),
+"""``kaolin_b200._C.render.mesh`` — the reference's native ops of the path (kaolin/csrc/bindings.cpp:75-82),
 same names, positional arguments, return conventions and error behaviour, backed by libdibr_b200.so.
 
 Validation mirrors the host wrappers kaolin/csrc/render/mesh/rasterization.cpp:60-85,127-154 and
@@ -180,7 +180,77 @@ def dibr_soft_mask_backward_cuda(grad_soft_mask, soft_mask, selected_face_idx, c
     return gi
 
 
+def deftet_sparse_render_forward_cuda(face_vertices_z, face_vertices_image, face_bboxes, pixel_coords,
+                                      pixel_depth_ranges, knum, eps):
+    """kaolin/csrc/render/mesh/deftet.h (deftet.cpp:47-109).  Returns [selected_face_idx, pixel_depths, w0, w1]
+    in face order, with the reference's fills (-1, -inf, 0, 0)."""
+    fn = "deftet_sparse_render_forward_cuda"
+    named = [("face_vertices_z", face_vertices_z), ("face_vertices_image", face_vertices_image),
+             ("face_bboxes", face_bboxes), ("pixel_coords", pixel_coords),
+             ("pixel_depth_ranges", pixel_depth_ranges)]
+    dev = _check_all_same_gpu(fn, named)
+    _check_all_contiguous(fn, named)
+    b, f = face_vertices_z.shape[0], face_vertices_z.shape[1]
+    p = pixel_coords.shape[1]
+    _check_size(fn, "face_vertices_z", face_vertices_z, (b, f, 3))
+    _check_size(fn, "face_vertices_image", face_vertices_image, (b, f, 3, 2))
+    _check_size(fn, "face_bboxes", face_bboxes, (b, f, 4))
+    _check_size(fn, "pixel_coords", pixel_coords, (b, p, 2))
+    _check_size(fn, "pixel_depth_ranges", pixel_depth_ranges, (b, p, 2))
+    suf = _lib.suffix(face_vertices_z.dtype, fn)
+    for nm, t in named[1:]:
+        _check_dtype(fn, nm, t, face_vertices_z.dtype)
+    knum = int(knum)
+    opt = dict(dtype=face_vertices_z.dtype, device=dev)
+    idx = torch.empty((b, p, knum), dtype=torch.long, device=dev)
+    depth, w0, w1 = (torch.empty((b, p, knum), **opt) for _ in range(3))
+    lib = _lib.load()
+    with torch.cuda.device(dev):
+        nbytes = lib.dibr_deftet_workspace_bytes(b, b * f)
+        ws = torch.empty(max(int(nbytes), 256), dtype=torch.uint8, device=dev)
+        code = getattr(lib, "dibr_deftet_forward_" + suf)(
+            _lib.ptr(face_vertices_z), _lib.ptr(face_vertices_image), _lib.ptr(face_bboxes), _lib.ptr(pixel_coords),
+            _lib.ptr(pixel_depth_ranges), b, f, p, knum, float(eps), _lib.ptr(idx), _lib.ptr(depth), _lib.ptr(w0),
+            _lib.ptr(w1), _lib.ptr(ws), nbytes, _lib.current_stream(dev))
+    _lib.check(code, fn)
+    return [idx, depth, w0, w1]
+
+
+def deftet_sparse_render_backward_cuda(grad_interpolated_features, face_idx, weights, face_vertices_image,
+                                       face_features, eps):
+    """kaolin/csrc/render/mesh/deftet.h (deftet.cpp:111-170).  Returns [grad_face_vertices_image,
+    grad_face_features]."""
+    fn = "deftet_sparse_render_backward_cuda"
+    named = [("grad_interpolated_features", grad_interpolated_features), ("face_idx", face_idx),
+             ("weights", weights), ("face_vertices_image", face_vertices_image), ("face_features", face_features)]
+    dev = _check_all_same_gpu(fn, named)
+    _check_all_contiguous(fn, named)
+    if grad_interpolated_features.dim() != 4:
+        raise RuntimeError(f"{fn}: grad_interpolated_features must be of shape (B,P,knum,C)")
+    b, p, knum, c = grad_interpolated_features.shape
+    f = face_vertices_image.shape[1]
+    _check_size(fn, "face_idx", face_idx, (b, p, knum))
+    _check_size(fn, "weights", weights, (b, p, knum, 3))
+    _check_size(fn, "face_vertices_image", face_vertices_image, (b, f, 3, 2))
+    _check_size(fn, "face_features", face_features, (b, f, 3, c))
+    suf = _lib.suffix(face_vertices_image.dtype, fn)
+    for nm, t in (named[0], named[2], named[4]):
+        _check_dtype(fn, nm, t, face_vertices_image.dtype)
+    _check_dtype(fn, "face_idx", face_idx, torch.long)
+    gi = torch.empty_like(face_vertices_image)
+    gf = torch.empty_like(face_features)
+    with torch.cuda.device(dev):
+        code = getattr(_lib.load(), "dibr_deftet_backward_" + suf)(
+            _lib.ptr_array([grad_interpolated_features]), _lib.ptr(face_idx), _lib.ptr(weights),
+            _lib.ptr(face_vertices_image), _lib.ptr_array([face_features]), _lib.int_array([c]), 1, b, f, p, knum,
+            float(eps), _lib.ptr(gi), _lib.ptr_array([gf]), _lib.current_stream(dev))
+    _lib.check(code, fn)
+    return [gi, gf]
+
+
 mesh = types.SimpleNamespace(
+    deftet_sparse_render_forward_cuda=deftet_sparse_render_forward_cuda,
+    deftet_sparse_render_backward_cuda=deftet_sparse_render_backward_cuda,
     packed_rasterize_forward_cuda=packed_rasterize_forward_cuda,
     rasterize_backward_cuda=rasterize_backward_cuda,
     dibr_soft_mask_forward_cuda=dibr_soft_mask_forward_cuda,

@@ -17,7 +17,7 @@ LIB_PATH = os.path.join(_PKG, "libdibr_b200.so")
 CSRC = os.path.join(_PKG, "csrc")
 SOURCES = ["dibr_c_abi.cu"]
 HEADERS = ["dibr_common.cuh", "dibr_binning.cuh", "dibr_raster_fwd.cuh", "dibr_raster_bwd.cuh",
-           "dibr_soft_mask.cuh", "dibr_prepare.cuh", "dibr_texture.cuh", "dibr_losses.cuh"]
+           "dibr_soft_mask.cuh", "dibr_prepare.cuh", "dibr_texture.cuh", "dibr_losses.cuh", "dibr_deftet.cuh"]
 NVCC_FLAGS = ["-O3", "-std=c++17", "-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo",
               "-cudart", "shared", "-Xcompiler", "-fPIC,-fvisibility=hidden"]
 
@@ -45,10 +45,14 @@ _TYPED = {
     "dibr_texture_mapping_bwd": [c_p, c_p, c_p, c_p, c_i, c_i64, c_i, c_i, c_i, c_i, c_i, c_p, c_p, c_p, c_p],
     "dibr_mask_iou_fwd": [c_p, c_p, c_i, c_i64, c_p, c_p, c_p, c_sz, c_p],
     "dibr_mask_iou_bwd": [c_p, c_p, c_p, c_p, c_i, c_i64, c_p, c_p, c_p],
+    "dibr_deftet_forward": [c_p, c_p, c_p, c_p, c_p, c_i, c_i, c_i, c_i, c_f, c_p, c_p, c_p, c_p, c_p, c_sz, c_p],
+    "dibr_deftet_render_fused": [c_p, c_p, c_p, c_p, c_p, c_p, c_i, c_i, c_i, c_i, c_i, c_f, c_p, c_p, c_p, c_p,
+                                 c_sz, c_p],
+    "dibr_deftet_backward": [c_p, c_p, c_p, c_p, c_p, c_p, c_i, c_i, c_i, c_i, c_i, c_f, c_p, c_p, c_p],
 }
 EXPORTED_SYMBOLS = (["dibr_abi_version", "dibr_error_string", "dibr_last_cuda_error", "dibr_workspace_bytes",
                      "dibr_kernel_launch_count", "dibr_reset_kernel_launch_count", "dibr_profile_next_launch",
-                     "dibr_mask_iou_workspace_bytes"] +
+                     "dibr_mask_iou_workspace_bytes", "dibr_deftet_workspace_bytes"] +
                     [f"{n}_{s}" for n in _TYPED for s in ("f32", "f64")])
 
 
@@ -97,6 +101,8 @@ def load():
         lib.dibr_reset_kernel_launch_count.restype = None
         lib.dibr_mask_iou_workspace_bytes.restype = c_sz
         lib.dibr_mask_iou_workspace_bytes.argtypes = [c_i, c_i64, c_i]
+        lib.dibr_deftet_workspace_bytes.restype = c_sz
+        lib.dibr_deftet_workspace_bytes.argtypes = [c_i, c_i64]
         lib.dibr_profile_next_launch.restype = c_i
         lib.dibr_profile_next_launch.argtypes = [c_i, c_p, c_p]
         for name, argtypes in _TYPED.items():
@@ -104,7 +110,7 @@ def load():
                 fn = getattr(lib, f"{name}_{suf}")
                 fn.restype = c_i
                 fn.argtypes = argtypes
-        if lib.dibr_abi_version() != 4:
+        if lib.dibr_abi_version() != 5:
             raise RuntimeError("kaolin_b200: libdibr_b200.so ABI version mismatch")
         _lib = lib
     return _lib
@@ -152,7 +158,8 @@ def current_stream(device):
 
 
 KERNEL_IDS = dict(setup_count=0, scan=1, fill=2, raster_fwd=3, raster_bwd=4, soft_fwd=5, soft_bwd=6,
-                  prepare_fwd=7, prepare_bwd=8, texture_fwd=9, texture_bwd=10, iou_fwd=11, iou_bwd=12)
+                  prepare_fwd=7, prepare_bwd=8, texture_fwd=9, texture_bwd=10, iou_fwd=11, iou_bwd=12,
+                  deftet_fwd=13, deftet_bwd=14)
 
 
 def profile_next_launch(kernel_id, start_event, stop_event):

@@ -8,8 +8,10 @@
 #include "dibr_prepare.cuh"
 #include "dibr_texture.cuh"
 #include "dibr_losses.cuh"
+#include "dibr_deftet.cuh"
 
 #include <atomic>
+#include <cmath>
 #include <cstdio>
 #include <cstring>
 #include <cstdlib>
@@ -423,6 +425,117 @@ int iou_bwd_impl(const T* g_loss, const T* lhs, const T* rhs, const T* sums, int
   return DIBR_OK;
 }
 
+// deftet_sparse_render (deftet.py:269-417).  Grid resolution: about 8 faces per cell, G in [1, 512].
+inline int deftet_grid(int F) {
+  int g = (int)std::ceil(std::sqrt((double)(F > 0 ? F : 1) / 8.0));
+  return g < 1 ? 1 : (g > 512 ? 512 : g);
+}
+inline int deftet_cap(int knum) {
+  int c = 64;
+  while (c < knum + 32) c <<= 1;
+  return c;
+}
+constexpr int DEFTET_MAX_KNUM = 4064;
+
+template <typename T>
+int deftet_fwd_impl(const T* z, const T* img, const T* bbox, const T* pix, const T* ranges, const T* const* feats,
+                    const int* channels, int n_feat, int B, int F, int P, int knum, float eps, T* const* outs,
+                    int64_t* face_idx, T* weights, int64_t* idx_unsorted, T* depth, T* w0, T* w1, void* ws,
+                    size_t ws_bytes, void* stream) {
+  if (B < 0 || F < 0 || P < 0 || knum < 0) return DIBR_ERR_INVALID_ARGUMENT;
+  if (knum > DEFTET_MAX_KNUM) return DIBR_ERR_TOO_LARGE;
+  const int64_t Ntot = (int64_t)B * F;
+  if (Ntot >= (int64_t)1 << 31 || (int64_t)B * P * (knum > 0 ? knum : 1) >= (int64_t)1 << 40) return DIBR_ERR_TOO_LARGE;
+  if ((int64_t)B * P == 0 || knum == 0) return DIBR_OK;
+  const bool native = idx_unsorted != nullptr;
+  if (native ? (!depth || !w0 || !w1) : !face_idx) return DIBR_ERR_INVALID_ARGUMENT;
+  if (!pix || !ranges || (Ntot > 0 && (!z || !img))) return DIBR_ERR_INVALID_ARGUMENT;
+  FeatSet<const T> fin; FeatSet<T> fout;
+  fin.n = fout.n = 0;
+  if (!native) { if (int e = make_featsets<T>(feats, outs, channels, n_feat, Ntot > 0, fin, fout)) return e; }
+  cudaStream_t s = static_cast<cudaStream_t>(stream);
+  const int G = deftet_grid(F);
+  const Geometry geo = make_geometry(B, G * TILE, G * TILE);
+  FaceLayout fl; fl.first_idx = nullptr; fl.F = F; fl.Ntot = Ntot; fl.B = B;
+  const WsLayout w = ws_layout(B, Ntot, geo);
+  if (!ws || ws_bytes < w.total) return DIBR_ERR_WORKSPACE;
+  BinLists L = carve(ws, w);
+  CUDA_TRY(cudaMemsetAsync(static_cast<unsigned char*>(ws) + w.zero_begin, 0, w.zero_end - w.zero_begin, s));
+  const unsigned nb = (unsigned)((Ntot + 255) / 256);
+  if (nb > 0) {
+    deftet_setup_count_kernel<T><<<nb, 256, 0, s>>>(img, bbox, fl, geo, L, G);
+    LAUNCH_CHECK("deftet_setup_count_kernel");
+  }
+  scan_kernel<<<B, 1024, 0, s>>>(geo, L);
+  LAUNCH_CHECK("scan_kernel");
+  if (nb > 0) {
+    fill_kernel<<<nb, 256, 0, s>>>(fl, geo, L);
+    LAUNCH_CHECK("fill_kernel");
+  }
+  DeftetParams<T> dp;
+  dp.z = z; dp.img = img; dp.bbox = bbox; dp.pix = pix; dp.ranges = ranges;
+  dp.B = B; dp.F = F; dp.P = P; dp.knum = knum; dp.grid = G; dp.eps = eps; dp.cap = deftet_cap(knum);
+  dp.face_idx_unsorted = idx_unsorted; dp.depth = depth; dp.w0 = w0; dp.w1 = w1;
+  dp.face_idx = face_idx; dp.weights = weights; dp.feat = fin; dp.out = fout;
+  using K = typename DepthKey<T>::type;
+  const size_t smem = (size_t)DEFTET_WARPS * dp.cap * (sizeof(K) + sizeof(unsigned));
+  if (smem > 48 * 1024) {
+    static std::atomic<int> done[64];                 // once per device (graph-capture safe after warm-up)
+    int dev = 0;
+    CUDA_TRY(cudaGetDevice(&dev));
+    if (dev < 0 || dev >= 64 || !done[dev].load(std::memory_order_acquire)) {
+      CUDA_TRY(cudaFuncSetAttribute(deftet_forward_kernel<T>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                    227 * 1024));
+      if (dev >= 0 && dev < 64) done[dev].store(1, std::memory_order_release);
+    }
+  }
+  const unsigned nblk = (unsigned)(((int64_t)B * P + DEFTET_WARPS - 1) / DEFTET_WARPS);
+  { ProfScope ps(DIBR_KERNEL_DEFTET_FWD, s);
+    deftet_forward_kernel<T><<<nblk, DEFTET_WARPS * 32, smem, s>>>(dp, fl, geo, L); }
+  LAUNCH_CHECK("deftet_forward_kernel");
+  return DIBR_OK;
+}
+
+template <typename T>
+int deftet_bwd_impl(const T* const* grad_outs, const int64_t* face_idx, const T* weights, const T* img,
+                    const T* const* feats, const int* channels, int n_feat, int B, int F, int P, int knum,
+                    float eps, T* grad_img, T* const* grad_feats, void* stream) {
+  if (B < 0 || F < 0 || P < 0 || knum < 0) return DIBR_ERR_INVALID_ARGUMENT;
+  if (n_feat < 0 || n_feat > MAX_FEATS || (n_feat > 0 && (!channels || !feats))) return DIBR_ERR_INVALID_ARGUMENT;
+  const size_t nf = (size_t)B * F;
+  const int64_t ne = (int64_t)B * P * knum;
+  if (nf >= (size_t)1 << 31 || ne >= (int64_t)1 << 40) return DIBR_ERR_TOO_LARGE;
+  cudaStream_t s = static_cast<cudaStream_t>(stream);
+  DeftetBwdParams<T> bp;
+  bp.face_idx = face_idx; bp.weights = weights; bp.img = img; bp.B = B; bp.F = F; bp.P = P; bp.knum = knum;
+  bp.eps = eps; bp.grad_img = grad_img;
+  bp.grad_out.n = bp.feat.n = bp.grad_feat.n = n_feat;
+  for (int t = 0; t < MAX_FEATS; ++t) {
+    bp.grad_out.ptr[t] = nullptr; bp.feat.ptr[t] = nullptr; bp.grad_feat.ptr[t] = nullptr;
+    bp.grad_out.ch[t] = bp.feat.ch[t] = bp.grad_feat.ch[t] = 0;
+  }
+  for (int t = 0; t < n_feat; ++t) {
+    if (channels[t] < 0) return DIBR_ERR_INVALID_ARGUMENT;
+    bp.grad_out.ch[t] = bp.feat.ch[t] = bp.grad_feat.ch[t] = channels[t];
+    if (channels[t] > 0 && nf > 0 && ne > 0 && (!grad_outs || !grad_outs[t] || !feats[t])) return DIBR_ERR_INVALID_ARGUMENT;
+    bp.grad_out.ptr[t] = grad_outs ? grad_outs[t] : nullptr;
+    bp.feat.ptr[t] = feats[t];
+    bp.grad_feat.ptr[t] = grad_feats ? grad_feats[t] : nullptr;
+  }
+  if (nf > 0) {
+    if (grad_img) CUDA_TRY(cudaMemsetAsync(grad_img, 0, nf * 6 * sizeof(T), s));
+    for (int t = 0; t < n_feat; ++t)
+      if (channels[t] > 0 && bp.grad_feat.ptr[t])
+        CUDA_TRY(cudaMemsetAsync(bp.grad_feat.ptr[t], 0, nf * 3 * channels[t] * sizeof(T), s));
+  }
+  if (nf == 0 || ne == 0) return DIBR_OK;
+  if (!face_idx || !weights || !img) return DIBR_ERR_INVALID_ARGUMENT;
+  { ProfScope ps(DIBR_KERNEL_DEFTET_BWD, s);
+    deftet_backward_kernel<T><<<(unsigned)((ne + 255) / 256), 256, 0, s>>>(bp); }
+  LAUNCH_CHECK("deftet_backward_kernel");
+  return DIBR_OK;
+}
+
 }  // namespace
 
 #define DIBR_API extern "C" __attribute__((visibility("default")))
@@ -452,6 +565,13 @@ DIBR_API int dibr_profile_next_launch(int kernel_id, void* start_event, void* st
 DIBR_API size_t dibr_workspace_bytes(int batch_size, int64_t total_faces, int height, int width) {
   if (batch_size < 0 || total_faces < 0 || height < 0 || width < 0) return 0;
   return ws_layout(batch_size, total_faces, make_geometry(batch_size, height, width)).total;
+}
+
+DIBR_API size_t dibr_deftet_workspace_bytes(int batch_size, int64_t total_faces) {
+  if (batch_size <= 0 || total_faces < 0) return 256;
+  const int F = (int)((total_faces + batch_size - 1) / batch_size);
+  const int G = deftet_grid(F);
+  return ws_layout(batch_size, total_faces, make_geometry(batch_size, G * TILE, G * TILE)).total;
 }
 
 DIBR_API size_t dibr_mask_iou_workspace_bytes(int B, int64_t P, int elem_size) {
@@ -573,6 +693,32 @@ DIBR_API size_t dibr_mask_iou_workspace_bytes(int B, int64_t P, int elem_size) {
   DIBR_API int dibr_mask_iou_bwd_##SUF(const T* grad_loss, const T* lhs, const T* rhs, const T* sums,        \
                                        int B, int64_t P, T* grad_lhs, T* grad_rhs, void* stream) {           \
     return iou_bwd_impl<T>(grad_loss, lhs, rhs, sums, B, P, grad_lhs, grad_rhs, stream);                      \
+  }                                                                                                           \
+  DIBR_API int dibr_deftet_forward_##SUF(const T* z, const T* img, const T* bboxes, const T* pixel_coords,   \
+                                         const T* render_ranges, int B, int F, int P, int knum, float eps,   \
+                                         int64_t* face_idx, T* pixel_depth, T* w0, T* w1, void* ws,          \
+                                         size_t ws_bytes, void* stream) {                                    \
+    if ((int64_t)B * F > 0 && !bboxes) return DIBR_ERR_INVALID_ARGUMENT;                                      \
+    if ((int64_t)B * P * knum > 0 && !face_idx) return DIBR_ERR_INVALID_ARGUMENT;                             \
+    return deftet_fwd_impl<T>(z, img, bboxes, pixel_coords, render_ranges, nullptr, nullptr, 0, B, F, P,     \
+                              knum, eps, nullptr, nullptr, nullptr, face_idx, pixel_depth, w0, w1, ws,       \
+                              ws_bytes, stream);                                                              \
+  }                                                                                                           \
+  DIBR_API int dibr_deftet_render_fused_##SUF(const T* pixel_coords, const T* render_ranges, const T* z,     \
+                                              const T* img, const T* const* feats, const int* channels,      \
+                                              int n_feat, int B, int F, int P, int knum, float eps,          \
+                                              T* const* outs, int64_t* face_idx, T* weights, void* ws,       \
+                                              size_t ws_bytes, void* stream) {                               \
+    return deftet_fwd_impl<T>(z, img, nullptr, pixel_coords, render_ranges, feats, channels, n_feat, B, F,   \
+                              P, knum, eps, outs, face_idx, weights, nullptr, nullptr, nullptr, nullptr, ws, \
+                              ws_bytes, stream);                                                              \
+  }                                                                                                           \
+  DIBR_API int dibr_deftet_backward_##SUF(const T* const* grad_outs, const int64_t* face_idx,                \
+                                          const T* weights, const T* img, const T* const* feats,             \
+                                          const int* channels, int n_feat, int B, int F, int P, int knum,    \
+                                          float eps, T* grad_img, T* const* grad_feats, void* stream) {      \
+    return deftet_bwd_impl<T>(grad_outs, face_idx, weights, img, feats, channels, n_feat, B, F, P, knum,     \
+                              eps, grad_img, grad_feats, stream);                                             \
   }
 
 DEFINE_ENTRY_POINTS(f32, float)

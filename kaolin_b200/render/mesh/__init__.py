@@ -2,4 +2,5 @@
 from .rasterization import *  # noqa: F401,F403
 from .dibr import *  # noqa: F401,F403
 from .utils import *  # noqa: F401,F403
-from . import rasterization, dibr, utils  # noqa: F401
+from .deftet import *  # noqa: F401,F403
+from . import rasterization, dibr, utils, deftet  # noqa: F401

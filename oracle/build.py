@@ -2,7 +2,7 @@
 
 * ``build_oracle()``  -> oracle/_ref/libdibr_oracle.so : the C++ CPU restatement (dibr_oracle.cpp).
 * ``build_ref_C()``   -> oracle/_ref/ref_C.so          : the reference's OWN CUDA implementation of the
-  hot path (kaolin/csrc/render/mesh/{rasterization,dibr_soft_mask}{.cpp,_cuda.cu}), compiled
+  hot path (kaolin/csrc/render/mesh/{rasterization,dibr_soft_mask,deftet}{.cpp,_cuda.cu}), compiled
   unmodified for sm_100a from the sources where they lie under /root/reference, with the
   reference's nvcc flags (setup.py:216-220: -O3 -DWITH_CUDA).  Only possible in the build container
   (the GPU box has no /root/reference; it uses the prebuilt .so that travels with the snapshot).
@@ -54,8 +54,9 @@ def build_ref_C(force=False):
     import torch
     from torch.utils import cpp_extension
     cpp = [os.path.join(srcdir, "rasterization.cpp"), os.path.join(srcdir, "dibr_soft_mask.cpp"),
-           os.path.join(HERE, "ref_bindings.cpp")]
-    cu = [os.path.join(srcdir, "rasterization_cuda.cu"), os.path.join(srcdir, "dibr_soft_mask_cuda.cu")]
+           os.path.join(srcdir, "deftet.cpp"), os.path.join(HERE, "ref_bindings.cpp")]
+    cu = [os.path.join(srcdir, "rasterization_cuda.cu"), os.path.join(srcdir, "dibr_soft_mask_cuda.cu"),
+          os.path.join(srcdir, "deftet_cuda.cu")]
     if not force and _newer(out, cpp + cu):
         return out
     tmp = os.path.join(OUT, "_obj")

@@ -1,6 +1,7 @@
 // ORACLE — TEST INFRASTRUCTURE ONLY.  Not part of the product path.
 //
-// CPU restatement (C++17, OpenMP) of the four reference kernels on the DIB-R hot path.
+// CPU restatement (C++17, OpenMP) of the four reference kernels on the DIB-R hot path (and of the two DefTet
+// sparse-renderer kernels).
 // Only tests/, __graft_entry__.smoke() and bench.py's cpu_baseline / --impl reference legs may
 // load this library; kaolin_b200/ never does (the product path fails loudly without its CUDA .so).
 //
@@ -301,6 +302,94 @@ void dibr_soft_mask_backward(const T* gsoft, const T* soft, const int64_t* sel, 
   }
 }
 
+// ---------------------------------------------------------------------------------------------
+// deftet_cuda.cu:31-190  deftet_sparse_render_forward_cuda_kernel   
+// Per pixel: the first `knum` faces IN FACE ORDER whose half-open bbox contains the pixel, whose
+// barycentric weights are all >= 0 and whose interpolated depth lies in [min_depth, max_depth), written
+// in insertion order (the depth sort is torch glue, deftet.py:291-296).  Outputs pre-initialised by the
+// caller as in deftet.cpp:87-92 (idx = -1, depth = -inf, w0 = w1 = 0).
+// Contractions read from the reference's sm_100a SASS: w = fma(p, q, -(r*s)); norm = (w0+w1)+w2;
+// depth = fma(w2, cz, fma(w0, az, w1*bz)); one correctly rounded division per weight.
+// ---------------------------------------------------------------------------------------------
+template <typename T>
+void deftet_forward(const T* z, const T* img, const T* bbox, const T* pix, const T* ranges, int64_t* out_idx,
+                    T* out_depth, T* out_w0, T* out_w1, int B, int F, int P, int knum, float eps) {
+#pragma omp parallel for collapse(2) schedule(dynamic, 16)
+  for (int b = 0; b < B; ++b) {
+    for (int p = 0; p < P; ++p) {
+      const int64_t m = (int64_t)b * P + p;
+      const T x0 = pix[m * 2], y0 = pix[m * 2 + 1];
+      const T min_depth = ranges[m * 2], max_depth = ranges[m * 2 + 1];
+      int n = 0;
+      for (int f = 0; f < F && n < knum; ++f) {
+        const int64_t g = (int64_t)b * F + f;
+        const T* bb = bbox + g * 4;
+        if (!(x0 >= bb[0] && x0 < bb[2] && y0 >= bb[1] && y0 < bb[3])) continue;      // :124
+        const T* v = img + g * 6;
+        const T aex = v[0] - x0, aey = v[1] - y0, bex = v[2] - x0, bey = v[3] - y0, cex = v[4] - x0,
+                cey = v[5] - y0;                                                        // :133-138
+        const T w0n = rfma(bex, cey, -(bey * cex));                                     // :139
+        const T w1n = rfma(cex, aey, -(cey * aex));                                     // :140
+        const T w2n = rfma(aex, bey, -(aey * bex));                                     // :141
+        const T norm = (w0n + w1n) + w2n;                                               // :142
+        const T den = norm + (T)std::copysign(eps, (float)norm);                        // :143-146 (copysignf)
+        const T w0 = w0n / den, w1 = w1n / den, w2 = w2n / den;
+        if (!(w0 >= 0. && w1 >= 0. && w2 >= 0.)) continue;                              // :149
+        const T* zz = z + g * 3;
+        const T depth = rfma(w2, zz[2], rfma(w0, zz[0], w1 * zz[1]));                   // :158
+        if (!(depth < max_depth && depth >= min_depth)) continue;                       // :160
+        const int64_t o = m * knum + n;
+        out_idx[o] = f; out_w0[o] = w0; out_w1[o] = w1; out_depth[o] = depth;           // :181-185
+        ++n;
+      }
+    }
+  }
+}
+
+// ---------------------------------------------------------------------------------------------
+// deftet_cuda.cu:240-410  deftet_sparse_render_backward_cuda_kernel.  One (pixel, k) entry at a time; the
+// gradients are accumulated serially here (atomicAdd order is unspecified in the reference), tolerance parity.
+// ---------------------------------------------------------------------------------------------
+template <typename T>
+void deftet_backward(const T* grad, const int64_t* idx, const T* wts, const T* img, const T* feat, T* grad_img,
+                     T* grad_feat, int B, int F, int P, int knum, int C, float eps) {
+  for (int64_t e = 0; e < (int64_t)B * P * knum; ++e) {
+    const int64_t f = idx[e];
+    if (f < 0) continue;
+    const int b = (int)(e / ((int64_t)P * knum));
+    const int64_t g = (int64_t)b * F + f;
+    const T* w = wts + e * 3;
+    const T* go = grad + e * C;
+    const T* ff = feat + g * 3 * C;
+    for (int ii = 0; ii < 3; ++ii)
+      for (int c = 0; c < C; ++c) grad_feat[g * 3 * C + ii * C + c] += go[c] * w[ii];   // :277-288
+    const T* v = img + g * 6;
+    const T ax = v[0], ay = v[1], bx = v[2], by = v[3], cx = v[4], cy = v[5];
+    const T x0 = w[0] * ax + w[1] * bx + w[2] * cx, y0 = w[0] * ay + w[1] * by + w[2] * cy;   // :305-306
+    const T m = bx - ax, p = by - ay, n = cx - ax, q = cy - ay, s = x0 - ax, t = y0 - ay;
+    const T k1 = s * q - n * t, k2 = m * t - s * p;
+    T k3 = m * q - n * p;
+    k3 += (T)std::copysign((double)eps, (double)k3);                                     // :326-328
+    const T dw1dm = -q * k1, dw1dn = -t * k3 + p * k1, dw1dp = n * k1, dw1dq = s * k3 - m * k1,
+            dw1ds = q * k3, dw1dt = -n * k3;                                             // :352-357
+    const T dw2dm = t * k3 - q * k2, dw2dn = p * k2, dw2dp = -s * k3 + n * k2, dw2dq = -m * k2,
+            dw2ds = -p * k3, dw2dt = m * k3;                                             // :359-364
+    const T dw1dax = -(dw1dm + dw1dn + dw1ds), dw1day = -(dw1dp + dw1dq + dw1dt);
+    const T dw2dax = -(dw2dm + dw2dn + dw2ds), dw2day = -(dw2dp + dw2dq + dw2dt);
+    for (int c = 0; c < C; ++c) {
+      const T c0 = ff[c], c1 = ff[C + c], c2 = ff[2 * C + c];
+      const T dldI = go[c] / (k3 * k3);                                                  // :394
+      T* gi = grad_img + g * 6;
+      gi[0] += dldI * ((c1 - c0) * dw1dax + (c2 - c0) * dw2dax);
+      gi[1] += dldI * ((c1 - c0) * dw1day + (c2 - c0) * dw2day);
+      gi[2] += dldI * ((c1 - c0) * dw1dm + (c2 - c0) * dw2dm);
+      gi[3] += dldI * ((c1 - c0) * dw1dp + (c2 - c0) * dw2dp);
+      gi[4] += dldI * ((c1 - c0) * dw1dn + (c2 - c0) * dw2dn);
+      gi[5] += dldI * ((c1 - c0) * dw1dq + (c2 - c0) * dw2dq);
+    }
+  }
+}
+
 }  // namespace
 
 #define ORACLE_API extern "C" __attribute__((visibility("default")))
@@ -332,6 +421,17 @@ void dibr_soft_mask_backward(const T* gsoft, const T* soft, const int64_t* sel, 
       float sigmainv, float multiplier, int row_begin, int row_end) {                               \
     dibr_soft_mask_backward<T>(gsoft, soft, sel, prob, cidx, ctype, img, grad_img, B, H, W, F,      \
                                knum, sigmainv, multiplier, row_begin, row_end);                     \
+  }                                                                                                 \
+  ORACLE_API void oracle_deftet_forward_##SUF(                                                      \
+      const T* z, const T* img, const T* bbox, const T* pix, const T* ranges, int64_t* out_idx,     \
+      T* out_depth, T* out_w0, T* out_w1, int B, int F, int P, int knum, float eps) {               \
+    deftet_forward<T>(z, img, bbox, pix, ranges, out_idx, out_depth, out_w0, out_w1, B, F, P, knum, \
+                      eps);                                                                         \
+  }                                                                                                 \
+  ORACLE_API void oracle_deftet_backward_##SUF(                                                     \
+      const T* grad, const int64_t* idx, const T* wts, const T* img, const T* feat, T* grad_img,    \
+      T* grad_feat, int B, int F, int P, int knum, int C, float eps) {                              \
+    deftet_backward<T>(grad, idx, wts, img, feat, grad_img, grad_feat, B, F, P, knum, C, eps);      \
   }
 
 DEFINE_ALL(f32, float)

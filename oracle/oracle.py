@@ -140,7 +140,42 @@ def dibr_soft_mask_backward_cuda(grad_soft_mask, soft_mask, selected_face_idx, c
     return gi
 
 
+def deftet_sparse_render_forward_cuda(face_vertices_z, face_vertices_image, face_bboxes, pixel_coords,
+                                      pixel_depth_ranges, knum, eps):
+    """deftet.cpp:47-109 (checks + allocation) and deftet_cuda.cu:31-190."""
+    _chk(face_vertices_z, face_vertices_image, face_bboxes, pixel_coords, pixel_depth_ranges)
+    b, f = face_vertices_z.shape[:2]
+    p = pixel_coords.shape[1]
+    assert face_vertices_image.shape == (b, f, 3, 2) and face_bboxes.shape == (b, f, 4)
+    assert pixel_coords.shape == (b, p, 2) and pixel_depth_ranges.shape == (b, p, 2)
+    opt = dict(dtype=face_vertices_z.dtype)
+    idx = torch.full((b, p, knum), -1, dtype=torch.long)
+    depth = torch.full((b, p, knum), -float("inf"), **opt)
+    w0 = torch.zeros((b, p, knum), **opt)
+    w1 = torch.zeros((b, p, knum), **opt)
+    fn = getattr(lib(), "oracle_deftet_forward_" + _suf(face_vertices_z))
+    fn(_p(face_vertices_z), _p(face_vertices_image), _p(face_bboxes), _p(pixel_coords), _p(pixel_depth_ranges),
+       _p(idx), _p(depth), _p(w0), _p(w1), b, f, p, int(knum), ctypes.c_float(eps))
+    return [idx, depth, w0, w1]
+
+
+def deftet_sparse_render_backward_cuda(grad_interpolated_features, face_idx, weights, face_vertices_image,
+                                       face_features, eps):
+    """deftet.cpp:111-170 and deftet_cuda.cu:240-410."""
+    _chk(grad_interpolated_features, face_idx, weights, face_vertices_image, face_features)
+    b, p, knum, c = grad_interpolated_features.shape
+    f = face_vertices_image.shape[1]
+    gi = torch.zeros_like(face_vertices_image)
+    gf = torch.zeros_like(face_features)
+    fn = getattr(lib(), "oracle_deftet_backward_" + _suf(face_vertices_image))
+    fn(_p(grad_interpolated_features), _p(face_idx), _p(weights), _p(face_vertices_image), _p(face_features),
+       _p(gi), _p(gf), b, f, p, knum, c, ctypes.c_float(eps))
+    return [gi, gf]
+
+
 _mesh = types.SimpleNamespace(
+    deftet_sparse_render_forward_cuda=deftet_sparse_render_forward_cuda,
+    deftet_sparse_render_backward_cuda=deftet_sparse_render_backward_cuda,
     packed_rasterize_forward_cuda=packed_rasterize_forward_cuda,
     rasterize_backward_cuda=rasterize_backward_cuda,
     dibr_soft_mask_forward_cuda=dibr_soft_mask_forward_cuda,
@@ -344,3 +379,45 @@ def mask_iou(lhs_mask, rhs_mask):
     iou_up = torch.sum(sil_mul.reshape(batch_size, -1), dim=1)
     iou_down = torch.sum((sil_add - sil_mul).reshape(batch_size, -1), dim=1)
     return 1.0 - torch.mean(iou_up / (iou_down + 1e-10))
+
+
+
+# ---------------------------------------------------------------------------------------------
+# deftet_sparse_render — torch glue of DeftetSparseRenderer restated on top of the
+# native-op-shaped functions above (backend=None: the C++ oracle on CPU tensors; backend=ref_C: the
+# reference's own CUDA kernels on GPU tensors).
+def deftet_sparse_render_forward(pixel_coords, render_ranges, face_vertices_z, face_vertices_image,
+                                 face_features, knum=300, eps=1e-8, backend=None):
+    """DeftetSparseRenderer.forward, deftet.py:272-318.  Returns (interpolated_features, sorted_face_idx,
+    weights).  The depth sort is made stable here (ties keep insertion = face order); torch.argsort of the
+    reference leaves the order of equal depths unspecified."""
+    b, f = face_vertices_z.shape[:2]
+    c = face_features.shape[-1]
+    p = pixel_coords.shape[1]
+    face_min = torch.min(face_vertices_image, dim=2)[0]
+    face_max = torch.max(face_vertices_image, dim=2)[0]
+    bboxes = torch.cat((face_min, face_max), dim=2)
+    mesh = OracleC.render.mesh if backend is None else backend.render.mesh
+    face_idx, depth, w0, w1 = mesh.deftet_sparse_render_forward_cuda(
+        face_vertices_z.contiguous(), face_vertices_image.contiguous(), bboxes.contiguous(),
+        pixel_coords.contiguous(), render_ranges.contiguous(), knum, eps)
+    order = torch.sort(depth, descending=True, dim=-1, stable=True)[1]
+    s_idx = torch.gather(face_idx, -1, order).contiguous()
+    s_w0 = torch.gather(w0, -1, order)
+    s_w1 = torch.gather(w1, -1, order)
+    s_w2 = (s_idx != -1).float() - (s_w0 + s_w1)
+    gidx = (s_idx + 1).reshape(b, -1, 1, 1).expand(b, p * knum, 3, c)
+    sel = torch.gather(torch.nn.functional.pad(face_features, (0, 0, 0, 0, 1, 0), value=0.), 1, gidx)
+    sel = sel.reshape(b, p, knum, 3, c)
+    weights = torch.stack([s_w0, s_w1, s_w2], dim=-1).contiguous()
+    feats = torch.sum(weights.unsqueeze(-1) * sel, dim=-2).contiguous()
+    return feats, s_idx, weights
+
+
+def deftet_sparse_render_backward(grad_features, face_idx, weights, face_vertices_image, face_features,
+                                  eps=1e-8, backend=None):
+    """DeftetSparseRenderer.backward, deftet.py:320-337."""
+    mesh = OracleC.render.mesh if backend is None else backend.render.mesh
+    return mesh.deftet_sparse_render_backward_cuda(grad_features.contiguous(), face_idx, weights,
+                                                   face_vertices_image.contiguous(), face_features.contiguous(),
+                                                   eps)

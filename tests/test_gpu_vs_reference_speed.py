@@ -72,3 +72,44 @@ def test_step_time_vs_reference_cuda_kernels(name, iters):
         with open(os.path.join(out, "vs_reference_cuda.json"), "w") as fh:
             json.dump(RESULTS, fh, indent=1)
     assert t_ours < t_ref
+
+
+@pytest.mark.gpu
+def test_deftet_time_vs_reference_cuda_kernels():
+    """deftet_sparse_render forward + backward: 100k faces, 4 x 16384 query points, knum 300 (the reference's
+    default), against DeftetSparseRenderer's torch glue on the reference's own kernels."""
+    import kaolin_b200 as kal
+    from oracle import oracle as O
+    ref_C = O.load_ref_C()
+    if ref_C is None or not hasattr(ref_C.render.mesh, "deftet_sparse_render_forward_cuda"):
+        pytest.skip("oracle/_ref/ref_C.so (with deftet) not built")
+    g = torch.Generator().manual_seed(5)
+    B, F, P, knum = 4, 100000, 16384, 300
+    centre = torch.rand(B, F, 1, 2, generator=g) * 2 - 1
+    img = (centre + (torch.rand(B, F, 3, 2, generator=g) - 0.5) * 0.05).cuda()
+    z = (-(torch.rand(B, F, 3, generator=g) * 4 + 0.5)).cuda()
+    pix = (torch.rand(B, P, 2, generator=g) * 2 - 1).cuda()
+    rr = torch.tensor([[[-10., 0.]]]).repeat(B, P, 1).cuda()
+    feats = torch.rand(B, F, 3, 4, generator=g).cuda()
+    gout = torch.rand(B, P, knum, 4, generator=g).cuda()
+
+    def ours():
+        il, fl = img.clone().requires_grad_(True), feats.clone().requires_grad_(True)
+        out, idx = kal.render.mesh.deftet_sparse_render(pix, rr, z, il, fl, knum)
+        out.backward(gout)
+        return idx
+
+    def reference():
+        out, idx, w = O.deftet_sparse_render_forward(pix, rr, z, img, feats, knum, 1e-8, backend=ref_C)
+        O.deftet_sparse_render_backward(gout, idx, w, img, feats, 1e-8, backend=ref_C)
+        return idx
+
+    assert torch.equal(ours(), reference())
+    t_ours, t_ref = _time(ours, 10, 2), _time(reference, 2, 1)
+    RESULTS["deftet"] = {"ours_ms": round(t_ours, 4), "reference_cuda_kernels_ms": round(t_ref, 3),
+                         "speedup": round(t_ref / t_ours, 1), "points": B * P, "faces": F, "knum": knum}
+    out = os.path.join(ROOT, "gpurun_out")
+    if os.path.isdir(out):
+        with open(os.path.join(out, "vs_reference_cuda.json"), "w") as fh:
+            json.dump(RESULTS, fh, indent=1)
+    assert t_ours < t_ref
