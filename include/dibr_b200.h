@@ -41,7 +41,7 @@
 extern "C" {
 #endif
 
-#define DIBR_ABI_VERSION 5
+#define DIBR_ABI_VERSION 6
 
 enum {
   DIBR_OK = 0,
@@ -149,11 +149,11 @@ int dibr_rasterize_backward_multi_f64(const double* const* grad_outs, const int6
 int dibr_soft_mask_fwd_fused_f32(const float* img, const int64_t* face_idx, int B, int F, int H, int W,
                                  float sigmainv, double boxlen, int knum, double multiplier, float* soft,
                                  float* prob, int64_t* close_idx, uint8_t* dist_type,
-                                 void* ws, size_t ws_bytes, void* stream);
+                                 void* ws, size_t ws_bytes, int keep_pairs, void* stream);
 int dibr_soft_mask_fwd_fused_f64(const double* img, const int64_t* face_idx, int B, int F, int H, int W,
                                  float sigmainv, double boxlen, int knum, double multiplier, double* soft,
                                  double* prob, int64_t* close_idx, uint8_t* dist_type,
-                                 void* ws, size_t ws_bytes, void* stream);
+                                 void* ws, size_t ws_bytes, int keep_pairs, void* stream);
 int dibr_soft_mask_forward_f32(const float* img_mult, const float* large_bboxes, const int64_t* face_idx,
                                int B, int F, int H, int W, float sigmainv, int knum, float multiplier,
                                float* soft, float* prob, int64_t* close_idx, uint8_t* dist_type,
@@ -173,8 +173,14 @@ int dibr_soft_mask_forward_f64(const double* img_mult, const double* large_bboxe
  *  UN-multiplied coordinates in both variants (the /multiplier is in-kernel, :299-302).
  *  bins_ready != 0 (fused variant): `ws` is the very workspace the matching dibr_soft_mask_fwd_fused call
  *  (same img, sizes, boxlen, multiplier) left behind, untouched since; the setup / binning kernels are then
- *  skipped (the kernels only read the workspace).  0 = rebuild the bins.
+ *  skipped (the kernels only read the workspace).  0 = rebuild the bins.  bins_ready == 2: that forward call
+ *  was made with keep_pairs != 0 and a workspace of dibr_soft_mask_workspace_bytes(..., keep_pairs = 1, ...)
+ *  bytes: it logged every evaluated (pixel, face, distance type, probability) behind the bins (12 bytes per
+ *  pair, about one pair per pixel), and the backward is then one thread per logged pair instead of a second
+ *  derivation of the k-lists; tiles whose pairs did not fit the log are recomputed as with bins_ready == 1.
  */
+size_t dibr_soft_mask_workspace_bytes(int batch_size, int64_t total_faces, int height, int width,
+                                      int keep_pairs, int elem_size);
 int dibr_soft_mask_backward_f32(const float* grad_soft, const float* soft, const int64_t* face_idx,
                                 const float* prob, const int64_t* close_idx, const uint8_t* dist_type,
                                 const float* img_mult, int B, int F, int H, int W, int knum, float sigmainv,

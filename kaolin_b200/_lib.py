@@ -35,7 +35,8 @@ _TYPED = {
     "dibr_rasterize_backward": [c_p, c_p, c_p, c_p, c_p, c_i, c_i, c_i, c_i, c_i, c_d, c_f, c_p, c_p, c_p],
     "dibr_rasterize_fwd_multi": [c_p, c_p, c_p, c_p, c_i, c_p, c_i, c_i, c_i, c_i, c_d, c_f, c_p, c_p, c_p, c_p, c_sz, c_p],
     "dibr_rasterize_backward_multi": [c_p, c_p, c_p, c_p, c_p, c_p, c_i, c_i, c_i, c_i, c_i, c_d, c_f, c_p, c_p, c_p],
-    "dibr_soft_mask_fwd_fused": [c_p, c_p, c_i, c_i, c_i, c_i, c_f, c_d, c_i, c_d, c_p, c_p, c_p, c_p, c_p, c_sz, c_p],
+    "dibr_soft_mask_fwd_fused": [c_p, c_p, c_i, c_i, c_i, c_i, c_f, c_d, c_i, c_d, c_p, c_p, c_p, c_p, c_p, c_sz, c_i,
+                                 c_p],
     "dibr_soft_mask_forward": [c_p, c_p, c_p, c_i, c_i, c_i, c_i, c_f, c_i, c_f, c_p, c_p, c_p, c_p, c_p, c_sz, c_p],
     "dibr_soft_mask_backward": [c_p, c_p, c_p, c_p, c_p, c_p, c_p, c_i, c_i, c_i, c_i, c_i, c_f, c_f, c_p, c_p],
     "dibr_soft_mask_bwd_fused": [c_p, c_p, c_p, c_p, c_i, c_i, c_i, c_i, c_f, c_d, c_i, c_d, c_p, c_p, c_sz, c_i, c_p],
@@ -52,7 +53,8 @@ _TYPED = {
 }
 EXPORTED_SYMBOLS = (["dibr_abi_version", "dibr_error_string", "dibr_last_cuda_error", "dibr_workspace_bytes",
                      "dibr_kernel_launch_count", "dibr_reset_kernel_launch_count", "dibr_profile_next_launch",
-                     "dibr_mask_iou_workspace_bytes", "dibr_deftet_workspace_bytes"] +
+                     "dibr_mask_iou_workspace_bytes", "dibr_deftet_workspace_bytes",
+                     "dibr_soft_mask_workspace_bytes"] +
                     [f"{n}_{s}" for n in _TYPED for s in ("f32", "f64")])
 
 
@@ -101,6 +103,8 @@ def load():
         lib.dibr_reset_kernel_launch_count.restype = None
         lib.dibr_mask_iou_workspace_bytes.restype = c_sz
         lib.dibr_mask_iou_workspace_bytes.argtypes = [c_i, c_i64, c_i]
+        lib.dibr_soft_mask_workspace_bytes.restype = c_sz
+        lib.dibr_soft_mask_workspace_bytes.argtypes = [c_i, c_i64, c_i, c_i, c_i, c_i]
         lib.dibr_deftet_workspace_bytes.restype = c_sz
         lib.dibr_deftet_workspace_bytes.argtypes = [c_i, c_i64]
         lib.dibr_profile_next_launch.restype = c_i
@@ -110,7 +114,7 @@ def load():
                 fn = getattr(lib, f"{name}_{suf}")
                 fn.restype = c_i
                 fn.argtypes = argtypes
-        if lib.dibr_abi_version() != 5:
+        if lib.dibr_abi_version() != 6:
             raise RuntimeError("kaolin_b200: libdibr_b200.so ABI version mismatch")
         _lib = lib
     return _lib

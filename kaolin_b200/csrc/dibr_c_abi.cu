@@ -240,11 +240,58 @@ int launch_soft(const SoftParams<T>& p, const FaceLayout& fl, const Geometry& ge
   return DIBR_OK;
 }
 
+// persistent recompute of the tiles that overflowed the pair log (MODE_BWD)
+template <typename T, int NT>
+int launch_soft_overflow(const SoftParams<T>& p, const FaceLayout& fl, const Geometry& geo, const BinLists& L,
+                         unsigned tiles, cudaStream_t s) {
+  const size_t smem = SoftSmem<T, NT>::total;
+  {
+    static std::atomic<unsigned long long> done{0};
+    int dev = 0;
+    CUDA_TRY(cudaGetDevice(&dev));
+    const unsigned long long bit = 1ull << (dev & 63);
+    if (!(done.load(std::memory_order_acquire) & bit)) {
+      CUDA_TRY(cudaFuncSetAttribute(soft_mask_overflow_kernel<T, NT>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                    (int)smem));
+      done.fetch_or(bit, std::memory_order_release);
+    }
+  }
+  const unsigned grid = tiles < 296u ? tiles : 296u;          // 2 CTAs per SM
+  soft_mask_overflow_kernel<T, NT><<<grid, NT, smem, s>>>(p, fl, geo, L);
+  return DIBR_OK;
+}
+
+// Pair log of the soft-mask forward (dibr_soft_mask.cuh), placed behind the bins in the same workspace.
+struct LogLayout { size_t counts, flags, over, pix, fk, prob, total; unsigned cap_seg; bool ok; };
+LogLayout log_layout(const Geometry& geo, size_t bins_total, size_t elem) {
+  LogLayout l;
+  const int64_t P = (int64_t)geo.B * geo.H * geo.W;
+  l.ok = P > 0 && P < ((int64_t)1 << 32);                 // pixel indices are logged as u32
+  int64_t cap = 2 * P + 65536;                            // measured: 0.5 - 1.3 pairs per pixel on configs 1-5
+  static const long long forced = [] {                    // DIBR_SOFT_LOG_CAP=<entries>: tests of the overflow path
+    const char* e = getenv("DIBR_SOFT_LOG_CAP");
+    return e ? atoll(e) : 0ll;
+  }();
+  if (forced > 0) cap = forced;
+  l.cap_seg = (unsigned)((cap + LOG_SEGMENTS - 1) / LOG_SEGMENTS);
+  const size_t n = (size_t)l.cap_seg * LOG_SEGMENTS;
+  size_t o = align_up(bins_total);
+  const size_t nt = (size_t)geo.B * geo.tiles_per_view;
+  l.counts = o; o = align_up(o + (LOG_SEGMENTS + 1) * sizeof(unsigned));     // + the overflow counter
+  l.flags = o;  o = align_up(o + nt * sizeof(unsigned));
+  l.over = o;   o = align_up(o + nt * sizeof(unsigned));
+  l.pix = o;    o = align_up(o + n * sizeof(unsigned));
+  l.fk = o;     o = align_up(o + n * sizeof(unsigned));
+  l.prob = o;   o = align_up(o + n * elem);
+  l.total = o;
+  return l;
+}
+
 template <typename T, int MODE>
 int soft_mask_impl(const T* img, const T* bbox_in, const int64_t* face_idx, int B, int F, int H, int W,
                    float sigmainv, int knum, T coord_mult, int premultiplied, T margin, float pix_mult,
                    T* soft, T* prob, int64_t* close_idx, uint8_t* dist_type, const T* grad_soft, const T* soft_in,
-                   T* grad_img, void* ws, size_t ws_bytes, void* stream, int bins_ready = 0) {
+                   T* grad_img, void* ws, size_t ws_bytes, void* stream, int bins_ready = 0, int keep_pairs = 0) {
   if (int e = check_dims(B, (int64_t)B * F, H, W)) return e;
   if (F < 0 || knum < 0 || !(pix_mult > 0.0f)) return DIBR_ERR_INVALID_ARGUMENT;
   const bool side = prob || close_idx || dist_type;
@@ -277,12 +324,43 @@ int soft_mask_impl(const T* img, const T* bbox_in, const int64_t* face_idx, int 
   p.sigmainv = sigmainv; p.F = F; p.knum = knum; p.face_idx = face_idx; p.soft = soft; p.prob = prob;
   p.close_idx = close_idx; p.dist_type = dist_type; p.grad_soft = grad_soft; p.soft_in = soft_in;
   p.grad_img = grad_img;
+  p.log_count = nullptr; p.over_count = nullptr; p.tile_flag = nullptr; p.over_list = nullptr; p.log_pix = nullptr; p.log_fk = nullptr; p.log_prob = nullptr;
+  p.log_cap = 0;
+  const bool use_log = (MODE == MODE_FWD) ? (keep_pairs != 0 && !side) : (bins_ready == 2);
+  // backward from the log = two launches (logged pairs, then the normally idle recompute kernel): one scope
+  ProfScope both(use_log && MODE == MODE_BWD ? DIBR_KERNEL_SOFT_BWD : -100, s);
+  if (use_log) {
+    const LogLayout ll = log_layout(geo, ws_layout(geo.B, fl.Ntot, geo).total, sizeof(T));
+    if (!ll.ok || ws_bytes < ll.total) return MODE == MODE_FWD ? DIBR_ERR_WORKSPACE : DIBR_ERR_INVALID_ARGUMENT;
+    unsigned char* base = static_cast<unsigned char*>(ws);
+    p.log_count = reinterpret_cast<unsigned*>(base + ll.counts);
+    p.over_count = p.log_count + LOG_SEGMENTS;
+    p.tile_flag = reinterpret_cast<unsigned*>(base + ll.flags);
+    p.over_list = reinterpret_cast<unsigned*>(base + ll.over);
+    p.log_pix = reinterpret_cast<unsigned*>(base + ll.pix);
+    p.log_fk = reinterpret_cast<unsigned*>(base + ll.fk);
+    p.log_prob = reinterpret_cast<T*>(base + ll.prob);
+    p.log_cap = ll.cap_seg;
+    if (MODE == MODE_FWD) {              // counts and flags are contiguous: one memset
+      CUDA_TRY(cudaMemsetAsync(base + ll.counts, 0, ll.over - ll.counts, s));
+    } else if (nf > 0) {                 // the logged pairs first, then the (normally idle) recompute kernel
+      // DIBR_SOFT_LOG_AGG=1: sum lanes holding the same face with shuffles before the atomics (measured slower:
+      // c2 0.121 vs 0.108 ms, c3 0.175 vs 0.154 ms — the kernel is not bound by the atomics)
+      static const bool agg = [] { const char* e = getenv("DIBR_SOFT_LOG_AGG"); return e ? atoi(e) != 0 : false; }();
+      if (agg) soft_mask_bwd_log_kernel<T, true><<<dim3(LOG_CTAS_PER_SEGMENT, LOG_SEGMENTS), 256, 0, s>>>(p, fl, geo);
+      else soft_mask_bwd_log_kernel<T, false><<<dim3(LOG_CTAS_PER_SEGMENT, LOG_SEGMENTS), 256, 0, s>>>(p, fl, geo);
+      g_launches.fetch_add(1, std::memory_order_relaxed);
+    }
+  }
   const unsigned grid = (unsigned)(B * geo.tiles_per_view);
   const int kid = MODE == MODE_FWD ? DIBR_KERNEL_SOFT_FWD : DIBR_KERNEL_SOFT_BWD;
   // threads per CTA (one CTA per tile either way): fp32 uses small CTAs (more resident tiles per SM hide the
   // barrier-separated phases); DIBR_SOFT_NT=64|128|256 overrides for experiments.  fp64: 256.
   int nt = sizeof(T) == 4 ? soft_threads_default() : 256;
-  if (sizeof(T) == 4 && nt == 64) {
+  if (MODE == MODE_BWD && use_log) {
+    if (sizeof(T) == 4) { if (int e = launch_soft_overflow<T, 128>(p, fl, geo, L, grid, s)) return e; }
+    else { if (int e = launch_soft_overflow<T, 256>(p, fl, geo, L, grid, s)) return e; }
+  } else if (sizeof(T) == 4 && nt == 64) {
     if (int e = launch_soft<T, MODE, 64>(p, fl, geo, L, grid, kid, s)) return e;
   } else if (sizeof(T) == 4 && nt == 128) {
     if (int e = launch_soft<T, MODE, 128>(p, fl, geo, L, grid, kid, s)) return e;
@@ -567,6 +645,16 @@ DIBR_API size_t dibr_workspace_bytes(int batch_size, int64_t total_faces, int he
   return ws_layout(batch_size, total_faces, make_geometry(batch_size, height, width)).total;
 }
 
+DIBR_API size_t dibr_soft_mask_workspace_bytes(int batch_size, int64_t total_faces, int height, int width,
+                                               int keep_pairs, int elem_size) {
+  if (check_dims(batch_size, total_faces, height, width) != DIBR_OK) return 0;
+  const Geometry geo = make_geometry(batch_size, height, width);
+  const size_t bins = ws_layout(batch_size, total_faces, geo).total;
+  if (!keep_pairs) return bins;
+  const LogLayout ll = log_layout(geo, bins, (size_t)elem_size);
+  return ll.ok ? ll.total : bins;
+}
+
 DIBR_API size_t dibr_deftet_workspace_bytes(int batch_size, int64_t total_faces) {
   if (batch_size <= 0 || total_faces < 0) return 256;
   const int F = (int)((total_faces + batch_size - 1) / batch_size);
@@ -625,10 +713,12 @@ DIBR_API size_t dibr_mask_iou_workspace_bytes(int B, int64_t P, int elem_size) {
   DIBR_API int dibr_soft_mask_fwd_fused_##SUF(const T* img, const int64_t* face_idx, int B, int F, int H,    \
                                               int W, float sigmainv, double boxlen, int knum,               \
                                               double multiplier, T* soft, T* prob, int64_t* close_idx,      \
-                                              uint8_t* dist_type, void* ws, size_t ws_bytes, void* stream) { \
+                                              uint8_t* dist_type, void* ws, size_t ws_bytes,                \
+                                              int keep_pairs, void* stream) {                                \
     return soft_mask_impl<T, MODE_FWD>(img, nullptr, face_idx, B, F, H, W, sigmainv, knum, (T)multiplier, 0, \
                                        (T)(boxlen * multiplier), (float)multiplier, soft, prob, close_idx,   \
-                                       dist_type, nullptr, nullptr, nullptr, ws, ws_bytes, stream);           \
+                                       dist_type, nullptr, nullptr, nullptr, ws, ws_bytes, stream, 0,         \
+                                       keep_pairs);                                                           \
   }                                                                                                           \
   DIBR_API int dibr_soft_mask_forward_##SUF(const T* img_mult, const T* large_bboxes,                        \
                                             const int64_t* face_idx, int B, int F, int H, int W,            \

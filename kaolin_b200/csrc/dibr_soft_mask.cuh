@@ -19,6 +19,7 @@
 // gradients with red.global.add.
 #pragma once
 #include "dibr_binning.cuh"
+#include "dibr_raster_bwd.cuh"      // group_partners / group_sum (warp-aggregated atomics)
 
 namespace dibr {
 
@@ -44,7 +45,22 @@ struct SoftParams {
   const T* grad_soft;         // (B,H,W)
   const T* soft_in;           // (B,H,W)
   T* grad_img;                // (B,F,3,2)
+  // pair log (optional; written by the fused forward, consumed by soft_mask_bwd_log_kernel): every evaluated
+  // (pixel, face) pair as {global pixel index, face << 3 | distance type, probability}, in LOG_SEGMENTS
+  // independent segments (a tile appends to segment hash(tile), one atomicAdd per warp and super-batch).
+  // A tile whose reservation does not fit its segment raises its flag and enters the overflow list: its logged
+  // pairs are ignored and soft_mask_overflow_kernel recomputes that tile (MODE_BWD).
+  unsigned* log_count;        // [LOG_SEGMENTS] or nullptr = no log
+  unsigned* over_count;       // [1] number of overflowed tiles
+  unsigned* tile_flag;        // [B*tiles] 1 = overflowed
+  unsigned* over_list;        // [B*tiles] the overflowed tiles (tile_global), in no particular order
+  unsigned* log_pix;          // [LOG_SEGMENTS * log_cap]
+  unsigned* log_fk;
+  T* log_prob;
+  unsigned log_cap;           // entries per segment
 };
+constexpr int LOG_SEGMENTS = 64;
+constexpr int LOG_CTAS_PER_SEGMENT = 32;
 
 // dibr_soft_mask_cuda.cu:283-347 for one (pixel, face) pair; p = multiplied coordinates.
 // Gradients need 1e-4 relative, not bit-exactness (the reference accumulates them with unordered atomics): the
@@ -80,6 +96,47 @@ __device__ __forceinline__ void soft_backward_pair(const T* p, const T x0, const
     atomicAdd(gi + o + 1, s * (x2 * dzdC - dzdA));
     atomicAdd(gi + o2, s * (y1 * dzdC - dzdB));
     atomicAdd(gi + o2 + 1, s * (dzdA - x1 * dzdC));
+  }
+}
+
+// Same gradient as soft_backward_pair, returned as the six components of the face's (3,2) coordinate gradient
+// (zeros where the pair does not contribute) so that lanes holding the same face can be summed before the atomics.
+template <typename T>
+__device__ __forceinline__ void soft_backward_vec(const T* p, const T x0, const T y0, const T prob, const int edgeid,
+                                                  const T dLdp, const T allprob, const float sigmainv,
+                                                  const float multiplier, T* out) {
+  const double EPS = 1e-7;
+#pragma unroll
+  for (int c = 0; c < 6; ++c) out[c] = (T)0;
+  const T dLdz = (T)(-1.0 * (double)sigmainv * (double)dLdp * (1.0 - (double)allprob) /
+                     (1.0 - (double)prob + EPS) * (double)prob);
+  if (dLdz == (T)0) return;
+  const T s = dLdz * ((T)1 / (T)multiplier);
+  if (edgeid >= 3) {
+    const int v = edgeid - 3;
+    const T x1 = v == 0 ? p[0] : (v == 1 ? p[2] : p[4]), y1 = v == 0 ? p[1] : (v == 1 ? p[3] : p[5]);
+    const T gx = s * 2 * (x1 - x0), gy = s * 2 * (y1 - y0);
+#pragma unroll
+    for (int c = 0; c < 3; ++c) { out[2 * c] = v == c ? gx : (T)0; out[2 * c + 1] = v == c ? gy : (T)0; }
+  } else {
+    const int e = edgeid, e2 = edgeid == 2 ? 0 : edgeid + 1;
+    const T x1 = e == 0 ? p[0] : (e == 1 ? p[2] : p[4]), y1 = e == 0 ? p[1] : (e == 1 ? p[3] : p[5]);
+    const T x2 = e2 == 0 ? p[0] : (e2 == 1 ? p[2] : p[4]), y2 = e2 == 0 ? p[1] : (e2 == 1 ? p[3] : p[5]);
+    const T A = y2 - y1, Bc = x1 - x2, Cc = x2 * y1 - x1 * y2;
+    const T up = A * x0 + Bc * y0 + Cc;
+    const T down = A * A + Bc * Bc;
+    const double rden = 1.0 / ((double)down + EPS);
+    const T dissquare = (T)((double)(up * up) * rden);
+    const T dzdA = (T)((double)(2 * (x0 * up - dissquare * A)) * rden);
+    const T dzdB = (T)((double)(2 * (y0 * up - dissquare * Bc)) * rden);
+    const T dzdC = (T)((double)(2 * up) * rden);
+    const T g1x = s * (dzdB - y2 * dzdC), g1y = s * (x2 * dzdC - dzdA);
+    const T g2x = s * (y1 * dzdC - dzdB), g2y = s * (dzdA - x1 * dzdC);
+#pragma unroll
+    for (int c = 0; c < 3; ++c) {
+      out[2 * c] = e == c ? g1x : (e2 == c ? g2x : (T)0);
+      out[2 * c + 1] = e == c ? g1y : (e2 == c ? g2y : (T)0);
+    }
   }
 }
 
@@ -199,9 +256,11 @@ __device__ __forceinline__ void rank_sort(int* s_ids, const int count) {
 // bits lo..hi (inclusive, 0 <= lo <= hi <= 15)
 __device__ __forceinline__ unsigned bit_span16(int lo, int hi) { return ((2u << hi) - 1u) & ~((1u << lo) - 1u); }
 
+// The work of one tile (tile_global = view * tiles_per_view + tile); called by the one-CTA-per-tile kernel and by
+// the persistent overflow kernel below.
 template <typename T, int MODE, int NT>
-__global__ void __launch_bounds__(NT, (sizeof(T) == 4 ? 1024 / NT : 512 / NT))
-soft_mask_kernel(SoftParams<T> sp, FaceLayout fl, Geometry geo, BinLists L) {
+__device__ __forceinline__ void soft_tile(const SoftParams<T>& sp, const FaceLayout& fl, const Geometry& geo,
+                                          const BinLists& L, const unsigned tile_global) {
   typedef typename CellInt<T>::type cell_int;
   typedef SoftSmem<T, NT> SM;
   constexpr int NW = NT / 32, CAP = SM::CAP, CELLS_TOT = SM::CELLS_TOT;
@@ -217,8 +276,8 @@ soft_mask_kernel(SoftParams<T> sp, FaceLayout fl, Geometry geo, BinLists L) {
   __shared__ int scratch[10];                                           // [0..7] warp sums, [8] append cursor, [9] U
   __shared__ float s_px[TILE], s_py[TILE];
 
-  const int tile = blockIdx.x % geo.tiles_per_view;
-  const int b = blockIdx.x / geo.tiles_per_view;
+  const int tile = (int)(tile_global % (unsigned)geo.tiles_per_view);
+  const int b = (int)(tile_global / (unsigned)geo.tiles_per_view);
   const int tx = tile % geo.tiles_x, ty = tile / geo.tiles_x;
   const int rx0 = tx * TILE, ry0 = ty * TILE, rx1 = rx0 + TILE - 1, ry1 = ry0 + TILE - 1;
   const int64_t vbase = fl.base(b);
@@ -432,6 +491,18 @@ soft_mask_kernel(SoftParams<T> sp, FaceLayout fl, Geometry geo, BinLists L) {
             const int64_t tpix = ((int64_t)b * geo.H + ry0 + (t >> 4)) * geo.W + rx0 + (t & 15);
             g = sp.grad_soft[tpix]; sft = sp.soft_in[tpix];
           }
+          unsigned lbase = 0;
+          const bool logging = MODE == MODE_FWD && sp.log_count != nullptr && nq > 0;
+          const unsigned seg = (tile_global * 0x9E3779B1u) >> 26;     // hashed: neighbouring tiles (one silhouette)
+                                                                      // spread over all LOG_SEGMENTS = 64 segments
+          if (logging) {
+            if (lane == 0) {
+              lbase = atomicAdd(&sp.log_count[seg], (unsigned)nq);
+              if (lbase + (unsigned)nq > sp.log_cap && atomicExch(&sp.tile_flag[tile_global], 1u) == 0u)
+                sp.over_list[atomicAdd(sp.over_count, 1u)] = tile_global;      // first overflow of this tile
+            }
+            lbase = __shfl_sync(0xffffffffu, lbase, 0);
+          }
           __syncwarp();
           for (int q0 = 0; q0 < nq; q0 += 32) {
             const unsigned rel = (unsigned)(start - q0);
@@ -460,6 +531,12 @@ soft_mask_kernel(SoftParams<T> sp, FaceLayout fl, Geometry geo, BinLists L) {
             const T prob = soft_prob<T>(d, sp.sigmainv, sp.pix_mult);
             if (MODE == MODE_FWD) {
               s_cell[cell] = prob;
+              if (logging && lbase + (unsigned)q < sp.log_cap) {
+                const size_t o = (size_t)seg * sp.log_cap + lbase + (unsigned)q;
+                sp.log_pix[o] = (unsigned)(((int64_t)b * geo.H + ry0 + ly) * geo.W + rx0 + lx);
+                sp.log_fk[o] = ((unsigned)f << 3) | (unsigned)edgeid;
+                sp.log_prob[o] = prob;
+              }
               if (sp.prob) {
                 const int64_t o = (((int64_t)b * geo.H + ry0 + ly) * geo.W + rx0 + lx) * K + pk0 + k;
                 sp.prob[o] = prob; sp.close_idx[o] = (int64_t)f; sp.dist_type[o] = (uint8_t)(edgeid + 1);
@@ -502,6 +579,82 @@ soft_mask_kernel(SoftParams<T> sp, FaceLayout fl, Geometry geo, BinLists L) {
         for (int k = s_ktot[u]; k < K; ++k) {
           sp.prob[tpix * K + k] = (T)0; sp.close_idx[tpix * K + k] = -1; sp.dist_type[tpix * K + k] = 0;
         }
+    }
+  }
+}
+
+template <typename T, int MODE, int NT>
+__global__ void __launch_bounds__(NT, (sizeof(T) == 4 ? 1024 / NT : 512 / NT))
+soft_mask_kernel(SoftParams<T> sp, FaceLayout fl, Geometry geo, BinLists L) {
+  soft_tile<T, MODE, NT>(sp, fl, geo, L, blockIdx.x);
+}
+
+// Backward of the tiles whose pairs did not fit the log: a small persistent grid walks the overflow list
+// (normally empty: the CTAs read one word and exit).
+template <typename T, int NT>
+__global__ void __launch_bounds__(NT, (sizeof(T) == 4 ? 1024 / NT : 512 / NT))
+soft_mask_overflow_kernel(SoftParams<T> sp, FaceLayout fl, Geometry geo, BinLists L) {
+  const unsigned n = min(*sp.over_count, (unsigned)(geo.B * geo.tiles_per_view));
+  for (unsigned i = blockIdx.x; i < n; i += gridDim.x) {
+    soft_tile<T, MODE_BWD, NT>(sp, fl, geo, L, sp.over_list[i]);
+    __syncthreads();
+  }
+}
+
+// ---------------------------------------------------------------- backward from the forward's pair log
+// grid (LOG_CTAS_PER_SEGMENT, LOG_SEGMENTS); thread = logged (pixel, face) pair.  Same per-pair gradient as the
+// recompute kernel, without re-deriving the k-lists: 12 bytes of log + one 24-byte face record per pair.
+template <typename T, bool AGG>
+__global__ void __launch_bounds__(256) soft_mask_bwd_log_kernel(SoftParams<T> sp, FaceLayout fl, Geometry geo) {
+  const unsigned seg = blockIdx.y;
+  const unsigned n = min(sp.log_count[seg], sp.log_cap);
+  const unsigned hw = (unsigned)geo.H * (unsigned)geo.W;
+  const float sx = pix_scale(sp.pix_mult, geo.W), sy = pix_scale(sp.pix_mult, geo.H);
+  const int lane = threadIdx.x & 31;
+  // warp-uniform trip count: the 32 lanes take 32 consecutive log entries (neighbouring pixels of a tile row, whose
+  // k-lists largely hold the same faces), lanes with the same face are summed with shuffles, one red per group
+  for (unsigned i0 = blockIdx.x * blockDim.x + (threadIdx.x & ~31u); i0 < n; i0 += gridDim.x * blockDim.x) {
+    const unsigned i = i0 + lane;
+    T c[6] = {0, 0, 0, 0, 0, 0};
+    int key = -1 - lane;                                    // inactive lanes: singleton groups
+    if (i < n) {
+      const size_t o = (size_t)seg * sp.log_cap + i;
+      const unsigned pix = sp.log_pix[o];
+      const unsigned fk = sp.log_fk[o];
+      const T prob = sp.log_prob[o];
+      const unsigned b = pix / hw, rem = pix - b * hw;
+      const unsigned py = rem / (unsigned)geo.W, px = rem - py * (unsigned)geo.W;
+      const T g = sp.grad_soft[pix];
+      if (g != (T)0 && !sp.tile_flag[b * geo.tiles_per_view + (py / TILE) * geo.tiles_x + px / TILE]) {
+        const int f = (int)(fk >> 3), edgeid = (int)(fk & 7u);
+        const int64_t gf = fl.base((int)b) + f;
+        T p[6];
+        load_face_xy<T>(sp.img, gf, sp.coord_mult, sp.premultiplied, p);
+        const T x0 = (T)pix_coord(sx, geo.W, (int)px), y0 = (T)pix_coord(sy, geo.H, geo.H - 1 - (int)py);
+        soft_backward_vec<T>(p, x0, y0, prob, edgeid, g, sp.soft_in[pix], sp.sigmainv, sp.pix_mult, c);
+        key = (int)gf;
+      }
+    }
+    if (!AGG) {
+      if (key >= 0) {
+#pragma unroll
+        for (int k = 0; k < 6; ++k)
+          if (c[k] != (T)0) atomicAdd(sp.grad_img + (int64_t)key * 6 + k, c[k]);
+      }
+      continue;
+    }
+    const unsigned peers = __match_any_sync(0xffffffffu, key);
+    int src[5];
+    group_partners(peers, src);
+    unsigned steps = 0;
+#pragma unroll
+    for (int st = 0; st < 5; ++st)
+      if (__any_sync(0xffffffffu, src[st] != lane)) steps |= 1u << st;
+    const bool leader = key >= 0 && ((peers & ((1u << lane) - 1u)) == 0u);
+#pragma unroll
+    for (int k = 0; k < 6; ++k) {
+      const T v = group_sum<T>(c[k], src, steps);
+      if (leader && v != (T)0) atomicAdd(sp.grad_img + (int64_t)key * 6 + k, v);
     }
   }
 }

@@ -36,12 +36,17 @@ class DibrSoftMaskCuda(Function):
         h, w = selected_face_idx.shape[1], selected_face_idx.shape[2]
         suf = _lib.suffix(face_vertices_image.dtype, fn)
         soft_mask = torch.empty((b, h, w), dtype=face_vertices_image.dtype, device=dev)
+        # with a gradient to come, the forward also logs its evaluated (pixel, face) pairs behind the bins
+        # (12 bytes per pair, about one pair per pixel) and backward runs one thread per logged pair
+        keep = 1 if ctx.needs_input_grad[0] else 0
+        lib = _lib.load()
         with torch.cuda.device(dev):
-            ws, nbytes = _lib.workspace(b, b * f, h, w, dev)
-            code = getattr(_lib.load(), "dibr_soft_mask_fwd_fused_" + suf)(
+            nbytes = lib.dibr_soft_mask_workspace_bytes(b, b * f, h, w, keep, face_vertices_image.element_size())
+            ws = torch.empty(max(int(nbytes), 256), dtype=torch.uint8, device=dev)
+            code = getattr(lib, "dibr_soft_mask_fwd_fused_" + suf)(
                 _lib.ptr(face_vertices_image), _lib.ptr(selected_face_idx), b, f, h, w, float(sigmainv),
                 float(boxlen), int(knum), float(multiplier), _lib.ptr(soft_mask), 0, 0, 0, _lib.ptr(ws), nbytes,
-                _lib.current_stream(dev))
+                keep, _lib.current_stream(dev))
         _lib.check(code, fn)
         ctx.multiplier = multiplier
         ctx.sigmainv = sigmainv
@@ -50,7 +55,7 @@ class DibrSoftMaskCuda(Function):
         ctx.save_for_backward(soft_mask, face_vertices_image, selected_face_idx)
         # the binning workspace (a few tens of bytes per face, vs the reference's 13*knum bytes per PIXEL of saved
         # side buffers) is kept for backward, which then skips the setup / binning kernels
-        ctx.bins = ws if ctx.needs_input_grad[0] else None
+        ctx.bins = ws if keep else None
         ctx.set_materialize_grads(False)
         return soft_mask
 
@@ -67,11 +72,11 @@ class DibrSoftMaskCuda(Function):
         grad_soft_mask = grad_soft_mask.contiguous()
         grad_face_vertices_image = torch.empty_like(face_vertices_image)
         with torch.cuda.device(dev):
-            ws, ready = ctx.bins, 1
+            ws, ready = ctx.bins, 2
             if ws is None:
                 (ws, _), ready = _lib.workspace(b, b * f, h, w, dev), 0
             ctx.bins = None
-            nbytes = _lib.load().dibr_workspace_bytes(b, b * f, h, w)
+            nbytes = ws.numel()
             code = getattr(_lib.load(), "dibr_soft_mask_bwd_fused_" + suf)(
                 _lib.ptr(grad_soft_mask), _lib.ptr(soft_mask), _lib.ptr(selected_face_idx),
                 _lib.ptr(face_vertices_image), b, f, h, w, float(ctx.sigmainv), float(ctx.boxlen), int(ctx.knum),

@@ -37,7 +37,7 @@ def test_header_symbols_exported(lib):
 
 
 def test_host_only_entry_points(lib):
-    assert lib.dibr_abi_version() == 5
+    assert lib.dibr_abi_version() == 6
     assert lib.dibr_error_string(0) == b"ok"
     for code in (1, 2, 3, 4, 99):
         assert len(lib.dibr_error_string(code)) > 0
@@ -61,7 +61,7 @@ def test_invalid_arguments_are_rejected_before_any_cuda_call(lib):
                                             null, null, 0, null)
     assert code == 4
     code = lib.dibr_soft_mask_fwd_fused_f32(null, null, 1, 4, 8, 8, 7000.0, 0.02, -3, 1000.0, null, null, null,
-                                            null, null, 0, null)
+                                            null, null, 0, 0, null)
     assert code == 1
     assert lib.dibr_profile_next_launch(3, null, null) == 1
     assert lib.dibr_profile_next_launch(-1, null, null) == 0

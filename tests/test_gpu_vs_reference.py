@@ -387,3 +387,36 @@ def test_c5_full_size_properties(kal):
 def test_c4_shape_two_shards(kal):
     """config 4 shape (40k faces, 512x512) on 16 of the 128 cameras."""
     _full_size_properties(kal, "c4", 16, (8, 16))
+
+
+def test_soft_mask_pair_log_overflow_falls_back_to_recompute(tmp_path):
+    """The soft-mask backward normally consumes the forward's pair log; with a log far too small for the scene
+    (DIBR_SOFT_LOG_CAP, read once per process -> subprocess) most tiles overflow and are recomputed.  Both must
+    give the gradient of the reference's kernels."""
+    import os
+    import subprocess
+    import sys
+    script = tmp_path / "run.py"
+    script.write_text('''
+import sys, torch
+sys.path.insert(0, %r)
+import kaolin_b200 as kal
+from kaolin_b200 import synth
+d = synth.make_inputs("c2", batch=2)
+img = d["face_vertices_image"].cuda().requires_grad_(True)
+z = d["face_vertices_z"].cuda()
+feats = d["face_features"][0].cuda()
+out, idx = kal.render.mesh.rasterize(d["H"], d["W"], z, img, feats, None, 1000., 1e-8)
+soft = kal.render.mesh.dibr_soft_mask(img, idx, d["sigmainv"], d["boxlen"], d["knum"], 1000.)
+g = torch.Generator().manual_seed(1)
+soft.backward(torch.rand(soft.shape, generator=g).cuda())
+torch.save(img.grad.cpu(), sys.argv[1])
+''' % os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+    grads = []
+    for cap in ("0", "20000"):
+        env = dict(os.environ, DIBR_SOFT_LOG_CAP=cap)
+        out = tmp_path / f"g{cap}.pt"
+        subprocess.run([sys.executable, str(script), str(out)], check=True, env=env, timeout=300)
+        grads.append(torch.load(out))
+    assert float(grads[0].abs().max()) > 0
+    rel_close(grads[1], grads[0], 1e-4, "overflowed log vs full log")
