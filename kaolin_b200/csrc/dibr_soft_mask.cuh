@@ -527,7 +527,9 @@ __device__ __forceinline__ void soft_tile(const SoftParams<T>& sp, const FaceLay
             T p[6];
             load_face_xy<T>(sp.img, vbase + f, sp.coord_mult, sp.premultiplied, p);
             int edgeid;
-            const T d = soft_distance<T>(p, x0, y0, sp.pix_mult, edgeid);
+            // fp32 without API-visible side buffers: reciprocal form of the per-edge divisions (dibr_common.cuh)
+            const T d = (sizeof(T) == 4 && !sp.prob) ? soft_distance<T, true>(p, x0, y0, sp.pix_mult, edgeid)
+                                                     : soft_distance<T, false>(p, x0, y0, sp.pix_mult, edgeid);
             const T prob = soft_prob<T>(d, sp.sigmainv, sp.pix_mult);
             if (MODE == MODE_FWD) {
               s_cell[cell] = prob;
