@@ -262,7 +262,7 @@ int launch_soft_overflow(const SoftParams<T>& p, const FaceLayout& fl, const Geo
 }
 
 // Pair log of the soft-mask forward (dibr_soft_mask.cuh), placed behind the bins in the same workspace.
-struct LogLayout { size_t counts, flags, over, pix, fk, prob, total; unsigned cap_seg; bool ok; };
+struct LogLayout { size_t counts, flags, over, recs, total; unsigned cap_seg; bool ok; };
 LogLayout log_layout(const Geometry& geo, size_t bins_total, size_t elem) {
   LogLayout l;
   const int64_t P = (int64_t)geo.B * geo.H * geo.W;
@@ -280,9 +280,8 @@ LogLayout log_layout(const Geometry& geo, size_t bins_total, size_t elem) {
   l.counts = o; o = align_up(o + (LOG_SEGMENTS + 1) * sizeof(unsigned));     // + the overflow counter
   l.flags = o;  o = align_up(o + nt * sizeof(unsigned));
   l.over = o;   o = align_up(o + nt * sizeof(unsigned));
-  l.pix = o;    o = align_up(o + n * sizeof(unsigned));
-  l.fk = o;     o = align_up(o + n * sizeof(unsigned));
-  l.prob = o;   o = align_up(o + n * elem);
+  (void)elem;                                              // 16-byte records for fp32 and fp64 alike
+  l.recs = o;   o = align_up(o + n * sizeof(uint4));
   l.total = o;
   return l;
 }
@@ -324,7 +323,7 @@ int soft_mask_impl(const T* img, const T* bbox_in, const int64_t* face_idx, int 
   p.sigmainv = sigmainv; p.F = F; p.knum = knum; p.face_idx = face_idx; p.soft = soft; p.prob = prob;
   p.close_idx = close_idx; p.dist_type = dist_type; p.grad_soft = grad_soft; p.soft_in = soft_in;
   p.grad_img = grad_img;
-  p.log_count = nullptr; p.over_count = nullptr; p.tile_flag = nullptr; p.over_list = nullptr; p.log_pix = nullptr; p.log_fk = nullptr; p.log_prob = nullptr;
+  p.log_count = nullptr; p.over_count = nullptr; p.tile_flag = nullptr; p.over_list = nullptr; p.log = nullptr;
   p.log_cap = 0;
   const bool use_log = (MODE == MODE_FWD) ? (keep_pairs != 0 && !side) : (bins_ready == 2);
   // backward from the log = two launches (logged pairs, then the normally idle recompute kernel): one scope
@@ -337,9 +336,7 @@ int soft_mask_impl(const T* img, const T* bbox_in, const int64_t* face_idx, int 
     p.over_count = p.log_count + LOG_SEGMENTS;
     p.tile_flag = reinterpret_cast<unsigned*>(base + ll.flags);
     p.over_list = reinterpret_cast<unsigned*>(base + ll.over);
-    p.log_pix = reinterpret_cast<unsigned*>(base + ll.pix);
-    p.log_fk = reinterpret_cast<unsigned*>(base + ll.fk);
-    p.log_prob = reinterpret_cast<T*>(base + ll.prob);
+    p.log = reinterpret_cast<uint4*>(base + ll.recs);
     p.log_cap = ll.cap_seg;
     if (MODE == MODE_FWD) {              // counts and flags are contiguous: one memset
       CUDA_TRY(cudaMemsetAsync(base + ll.counts, 0, ll.over - ll.counts, s));

@@ -46,7 +46,7 @@ struct SoftParams {
   const T* soft_in;           // (B,H,W)
   T* grad_img;                // (B,F,3,2)
   // pair log (optional; written by the fused forward, consumed by soft_mask_bwd_log_kernel): every evaluated
-  // (pixel, face) pair as {global pixel index, face << 3 | distance type, probability}, in LOG_SEGMENTS
+  // (pixel, face) pair as one 16-byte record {global pixel index, face << 3 | distance type, probability}, in LOG_SEGMENTS
   // independent segments (a tile appends to segment hash(tile), one atomicAdd per warp and super-batch).
   // A tile whose reservation does not fit its segment raises its flag and enters the overflow list: its logged
   // pairs are ignored and soft_mask_overflow_kernel recomputes that tile (MODE_BWD).
@@ -54,11 +54,21 @@ struct SoftParams {
   unsigned* over_count;       // [1] number of overflowed tiles
   unsigned* tile_flag;        // [B*tiles] 1 = overflowed
   unsigned* over_list;        // [B*tiles] the overflowed tiles (tile_global), in no particular order
-  unsigned* log_pix;          // [LOG_SEGMENTS * log_cap]
-  unsigned* log_fk;
-  T* log_prob;
+  uint4* log;                 // [LOG_SEGMENTS * log_cap] 16-byte records {pixel, face << 3 | type, prob bits (z[, w])}
   unsigned log_cap;           // entries per segment
 };
+__device__ __forceinline__ uint4 log_pack(unsigned pix, unsigned fk, float prob) {
+  return make_uint4(pix, fk, __float_as_uint(prob), 0u);
+}
+__device__ __forceinline__ uint4 log_pack(unsigned pix, unsigned fk, double prob) {
+  const unsigned long long u = (unsigned long long)__double_as_longlong(prob);
+  return make_uint4(pix, fk, (unsigned)(u & 0xffffffffull), (unsigned)(u >> 32));
+}
+template <typename T> __device__ __forceinline__ T log_prob(const uint4& r);
+template <> __device__ __forceinline__ float log_prob<float>(const uint4& r) { return __uint_as_float(r.z); }
+template <> __device__ __forceinline__ double log_prob<double>(const uint4& r) {
+  return __longlong_as_double((long long)(((unsigned long long)r.w << 32) | r.z));
+}
 constexpr int LOG_SEGMENTS = 64;
 constexpr int LOG_CTAS_PER_SEGMENT = 32;
 
@@ -76,14 +86,16 @@ __device__ __forceinline__ void soft_backward_pair(const T* p, const T x0, const
                      (1.0 - (double)prob + EPS) * (double)prob);
   if (dLdz == (T)0) return;                              // nothing to add (prob or upstream gradient is zero)
   const T s = dLdz * ((T)1 / (T)multiplier);
+  // selects instead of p[edgeid-dependent index]: keeps p[] in registers (no local-memory frame)
   if (edgeid >= 3) {
-    const int o = (edgeid - 3) * 2;
-    const T x1 = p[o], y1 = p[o + 1];
-    atomicAdd(gi + o, s * 2 * (x1 - x0));
-    atomicAdd(gi + o + 1, s * 2 * (y1 - y0));
+    const int v = edgeid - 3;
+    const T x1 = v == 0 ? p[0] : (v == 1 ? p[2] : p[4]), y1 = v == 0 ? p[1] : (v == 1 ? p[3] : p[5]);
+    atomicAdd(gi + 2 * v, s * 2 * (x1 - x0));
+    atomicAdd(gi + 2 * v + 1, s * 2 * (y1 - y0));
   } else {
-    const int o = edgeid * 2, o2 = ((edgeid + 1) % 3) * 2;
-    const T x1 = p[o], y1 = p[o + 1], x2 = p[o2], y2 = p[o2 + 1];
+    const int e = edgeid, e2 = edgeid == 2 ? 0 : edgeid + 1;
+    const T x1 = e == 0 ? p[0] : (e == 1 ? p[2] : p[4]), y1 = e == 0 ? p[1] : (e == 1 ? p[3] : p[5]);
+    const T x2 = e2 == 0 ? p[0] : (e2 == 1 ? p[2] : p[4]), y2 = e2 == 0 ? p[1] : (e2 == 1 ? p[3] : p[5]);
     const T A = y2 - y1, Bc = x1 - x2, Cc = x2 * y1 - x1 * y2;
     const T up = A * x0 + Bc * y0 + Cc;
     const T down = A * A + Bc * Bc;
@@ -92,10 +104,10 @@ __device__ __forceinline__ void soft_backward_pair(const T* p, const T x0, const
     const T dzdA = (T)((double)(2 * (x0 * up - dissquare * A)) * rden);
     const T dzdB = (T)((double)(2 * (y0 * up - dissquare * Bc)) * rden);
     const T dzdC = (T)((double)(2 * up) * rden);
-    atomicAdd(gi + o, s * (dzdB - y2 * dzdC));
-    atomicAdd(gi + o + 1, s * (x2 * dzdC - dzdA));
-    atomicAdd(gi + o2, s * (y1 * dzdC - dzdB));
-    atomicAdd(gi + o2 + 1, s * (dzdA - x1 * dzdC));
+    atomicAdd(gi + 2 * e, s * (dzdB - y2 * dzdC));
+    atomicAdd(gi + 2 * e + 1, s * (x2 * dzdC - dzdA));
+    atomicAdd(gi + 2 * e2, s * (y1 * dzdC - dzdB));
+    atomicAdd(gi + 2 * e2 + 1, s * (dzdA - x1 * dzdC));
   }
 }
 
@@ -535,9 +547,8 @@ __device__ __forceinline__ void soft_tile(const SoftParams<T>& sp, const FaceLay
               s_cell[cell] = prob;
               if (logging && lbase + (unsigned)q < sp.log_cap) {
                 const size_t o = (size_t)seg * sp.log_cap + lbase + (unsigned)q;
-                sp.log_pix[o] = (unsigned)(((int64_t)b * geo.H + ry0 + ly) * geo.W + rx0 + lx);
-                sp.log_fk[o] = ((unsigned)f << 3) | (unsigned)edgeid;
-                sp.log_prob[o] = prob;
+                sp.log[o] = log_pack((unsigned)(((int64_t)b * geo.H + ry0 + ly) * geo.W + rx0 + lx),
+                                     ((unsigned)f << 3) | (unsigned)edgeid, prob);
               }
               if (sp.prob) {
                 const int64_t o = (((int64_t)b * geo.H + ry0 + ly) * geo.W + rx0 + lx) * K + pk0 + k;
@@ -606,6 +617,30 @@ soft_mask_overflow_kernel(SoftParams<T> sp, FaceLayout fl, Geometry geo, BinList
 // ---------------------------------------------------------------- backward from the forward's pair log
 // grid (LOG_CTAS_PER_SEGMENT, LOG_SEGMENTS); thread = logged (pixel, face) pair.  Same per-pair gradient as the
 // recompute kernel, without re-deriving the k-lists: 12 bytes of log + one 24-byte face record per pair.
+// One logged pair: everything that must be fetched before the arithmetic (issued for two pairs at a time so that
+// the three dependent gathers — record -> pixel values / face record — overlap; ncu showed the kernel waiting on
+// long-scoreboard, not on the atomics).
+template <typename T>
+struct LogItem {
+  uint4 rec; T g, soft; unsigned flag, b, px, py; T p[6]; int64_t gf;
+};
+template <typename T>
+__device__ __forceinline__ void log_fetch_pixel(const SoftParams<T>& sp, const Geometry& geo, const unsigned hw,
+                                                LogItem<T>& it) {
+  const unsigned pix = it.rec.x;
+  it.b = pix / hw;
+  const unsigned rem = pix - it.b * hw;
+  it.py = rem / (unsigned)geo.W; it.px = rem - it.py * (unsigned)geo.W;
+  it.g = sp.grad_soft[pix];
+  it.soft = sp.soft_in[pix];
+  it.flag = sp.tile_flag[it.b * geo.tiles_per_view + (it.py / TILE) * geo.tiles_x + it.px / TILE];
+}
+template <typename T>
+__device__ __forceinline__ void log_fetch_face(const SoftParams<T>& sp, const FaceLayout& fl, LogItem<T>& it) {
+  it.gf = fl.base((int)it.b) + (int)(it.rec.y >> 3);
+  load_face_xy<T>(sp.img, it.gf, sp.coord_mult, sp.premultiplied, it.p);
+}
+
 template <typename T, bool AGG>
 __global__ void __launch_bounds__(256) soft_mask_bwd_log_kernel(SoftParams<T> sp, FaceLayout fl, Geometry geo) {
   const unsigned seg = blockIdx.y;
@@ -613,37 +648,49 @@ __global__ void __launch_bounds__(256) soft_mask_bwd_log_kernel(SoftParams<T> sp
   const unsigned hw = (unsigned)geo.H * (unsigned)geo.W;
   const float sx = pix_scale(sp.pix_mult, geo.W), sy = pix_scale(sp.pix_mult, geo.H);
   const int lane = threadIdx.x & 31;
-  // warp-uniform trip count: the 32 lanes take 32 consecutive log entries (neighbouring pixels of a tile row, whose
-  // k-lists largely hold the same faces), lanes with the same face are summed with shuffles, one red per group
-  for (unsigned i0 = blockIdx.x * blockDim.x + (threadIdx.x & ~31u); i0 < n; i0 += gridDim.x * blockDim.x) {
+  const uint4* log = sp.log + (size_t)seg * sp.log_cap;
+  const unsigned stride = gridDim.x * blockDim.x;
+  if (!AGG) {
+    for (unsigned i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += 2 * stride) {
+      const unsigned j = i + stride;
+      const bool two = j < n;
+      LogItem<T> a, c;
+      a.rec = log[i];
+      c.rec = log[two ? j : i];
+      log_fetch_pixel<T>(sp, geo, hw, a);
+      log_fetch_pixel<T>(sp, geo, hw, c);
+      log_fetch_face<T>(sp, fl, a);
+      log_fetch_face<T>(sp, fl, c);
+      if (a.g != (T)0 && !a.flag) {
+        const T x0 = (T)pix_coord(sx, geo.W, (int)a.px), y0 = (T)pix_coord(sy, geo.H, geo.H - 1 - (int)a.py);
+        soft_backward_pair<T>(a.p, x0, y0, log_prob<T>(a.rec), (int)(a.rec.y & 7u), a.g, a.soft, sp.sigmainv,
+                              sp.pix_mult, sp.grad_img + a.gf * 6);
+      }
+      if (two && c.g != (T)0 && !c.flag) {
+        const T x0 = (T)pix_coord(sx, geo.W, (int)c.px), y0 = (T)pix_coord(sy, geo.H, geo.H - 1 - (int)c.py);
+        soft_backward_pair<T>(c.p, x0, y0, log_prob<T>(c.rec), (int)(c.rec.y & 7u), c.g, c.soft, sp.sigmainv,
+                              sp.pix_mult, sp.grad_img + c.gf * 6);
+      }
+    }
+    return;
+  }
+  // AGG: warp-uniform trip count; the 32 lanes take 32 consecutive log entries (neighbouring pixels of a tile row,
+  // whose k-lists largely hold the same faces), lanes with the same face are summed with shuffles, one red per group
+  for (unsigned i0 = blockIdx.x * blockDim.x + (threadIdx.x & ~31u); i0 < n; i0 += stride) {
     const unsigned i = i0 + lane;
     T c[6] = {0, 0, 0, 0, 0, 0};
     int key = -1 - lane;                                    // inactive lanes: singleton groups
     if (i < n) {
-      const size_t o = (size_t)seg * sp.log_cap + i;
-      const unsigned pix = sp.log_pix[o];
-      const unsigned fk = sp.log_fk[o];
-      const T prob = sp.log_prob[o];
-      const unsigned b = pix / hw, rem = pix - b * hw;
-      const unsigned py = rem / (unsigned)geo.W, px = rem - py * (unsigned)geo.W;
-      const T g = sp.grad_soft[pix];
-      if (g != (T)0 && !sp.tile_flag[b * geo.tiles_per_view + (py / TILE) * geo.tiles_x + px / TILE]) {
-        const int f = (int)(fk >> 3), edgeid = (int)(fk & 7u);
-        const int64_t gf = fl.base((int)b) + f;
-        T p[6];
-        load_face_xy<T>(sp.img, gf, sp.coord_mult, sp.premultiplied, p);
-        const T x0 = (T)pix_coord(sx, geo.W, (int)px), y0 = (T)pix_coord(sy, geo.H, geo.H - 1 - (int)py);
-        soft_backward_vec<T>(p, x0, y0, prob, edgeid, g, sp.soft_in[pix], sp.sigmainv, sp.pix_mult, c);
-        key = (int)gf;
+      LogItem<T> a;
+      a.rec = log[i];
+      log_fetch_pixel<T>(sp, geo, hw, a);
+      if (a.g != (T)0 && !a.flag) {
+        log_fetch_face<T>(sp, fl, a);
+        const T x0 = (T)pix_coord(sx, geo.W, (int)a.px), y0 = (T)pix_coord(sy, geo.H, geo.H - 1 - (int)a.py);
+        soft_backward_vec<T>(a.p, x0, y0, log_prob<T>(a.rec), (int)(a.rec.y & 7u), a.g, a.soft, sp.sigmainv,
+                             sp.pix_mult, c);
+        key = (int)a.gf;
       }
-    }
-    if (!AGG) {
-      if (key >= 0) {
-#pragma unroll
-        for (int k = 0; k < 6; ++k)
-          if (c[k] != (T)0) atomicAdd(sp.grad_img + (int64_t)key * 6 + k, c[k]);
-      }
-      continue;
     }
     const unsigned peers = __match_any_sync(0xffffffffu, key);
     int src[5];

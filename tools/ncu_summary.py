@@ -23,7 +23,8 @@ KEYS = [("gpu__time_duration.sum", "duration"), ("dram__bytes_read.sum", "dram_r
         ("launch__registers_per_thread", "registers"), ("sm__inst_executed.sum", "warp_instructions"),
         ("smsp__thread_inst_executed_per_inst_executed.ratio", "active_threads_per_warp")]
 NAMES = {"raster_fwd_scatter_kernel": "raster_fwd", "raster_fwd_kernel": "raster_fwd", "raster_bwd_kernel": "raster_bwd",
-         "soft_mask_kernel<float, 0": "soft_fwd", "soft_mask_kernel<float, 1": "soft_bwd",
+         "soft_mask_kernel<float, 0": "soft_fwd", "soft_mask_kernel<float, 1": "soft_bwd_recompute",
+         "soft_mask_bwd_log_kernel": "soft_bwd", "soft_mask_overflow_kernel": "soft_bwd_overflow",
          "soft_mask_kernel<double, 0": "soft_fwd_f64", "soft_mask_kernel<double, 1": "soft_bwd_f64"}
 UNIT = {"byte": 1.0, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9, "ns": 1e-3, "us": 1.0, "ms": 1e3,
         "nsecond": 1e-3, "usecond": 1.0, "msecond": 1e3}
