@@ -31,6 +31,14 @@ def all_reduce_leaf_grads(params, group=None, average=False):
     params = [p for p in params if p is not None]
     if not params:
         return None
+    if len(params) == 1 and params[0].grad is not None and params[0].grad.is_contiguous():
+        # a single leaf (the usual case: the vertices): reduce its gradient in place, no packing kernels
+        g = params[0].grad
+        if dist.is_available() and dist.is_initialized():
+            dist.all_reduce(g, op=dist.ReduceOp.SUM, group=group)
+            if average:
+                g /= dist.get_world_size(group)
+        return g.view(-1)
     dtype = params[0].dtype
     device = params[0].device
     sizes = [p.numel() for p in params]

@@ -55,8 +55,12 @@ def _worker(rank, world, port, out_dir):
         if rank == 0:
             loss = loss + extra.sum()
         loss.backward()
+        single = vert.detach().clone().requires_grad_(True)          # the one-leaf path reduces in place
+        single.grad = vert.grad.clone()
         bucket = mv.all_reduce_leaf_grads([vert, extra])
         assert bucket.numel() == vert.numel() + 3
+        flat = mv.all_reduce_leaf_grads([single])
+        assert flat.data_ptr() == single.grad.data_ptr() and torch.equal(single.grad, vert.grad)
         torch.save({"vert": vert.grad.clone(), "extra": extra.grad.clone()}, os.path.join(out_dir, f"g{rank}.pt"))
     finally:
         dist.destroy_process_group()
