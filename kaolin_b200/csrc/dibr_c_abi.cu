@@ -325,12 +325,15 @@ int soft_mask_impl(const T* img, const T* bbox_in, const int64_t* face_idx, int 
   p.grad_img = grad_img;
   p.log_count = nullptr; p.over_count = nullptr; p.tile_flag = nullptr; p.over_list = nullptr; p.log = nullptr;
   p.log_cap = 0;
-  const bool use_log = (MODE == MODE_FWD) ? (keep_pairs != 0 && !side) : (bins_ready == 2);
+  // The pair log is used when it was asked for (forward: keep_pairs; backward: bins_ready == 2), the pixel
+  // indices fit 32 bits and the workspace holds it — the same test on both sides, so a forward that had to go
+  // without a log is followed by a recompute backward on the same workspace.
+  const LogLayout ll = log_layout(geo, ws_layout(geo.B, fl.Ntot, geo).total, sizeof(T));
+  const bool use_log = ((MODE == MODE_FWD) ? (keep_pairs != 0 && !side) : (bins_ready == 2)) && ll.ok && ws &&
+                       ws_bytes >= ll.total;
   // backward from the log = two launches (logged pairs, then the normally idle recompute kernel): one scope
   ProfScope both(use_log && MODE == MODE_BWD ? DIBR_KERNEL_SOFT_BWD : -100, s);
   if (use_log) {
-    const LogLayout ll = log_layout(geo, ws_layout(geo.B, fl.Ntot, geo).total, sizeof(T));
-    if (!ll.ok || ws_bytes < ll.total) return MODE == MODE_FWD ? DIBR_ERR_WORKSPACE : DIBR_ERR_INVALID_ARGUMENT;
     unsigned char* base = static_cast<unsigned char*>(ws);
     p.log_count = reinterpret_cast<unsigned*>(base + ll.counts);
     p.over_count = p.log_count + LOG_SEGMENTS;

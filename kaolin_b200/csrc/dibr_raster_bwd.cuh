@@ -87,6 +87,7 @@ __global__ void __launch_bounds__(256) raster_bwd_kernel(RasterBwdParams<T> bp, 
 
   T w0 = 0, w1 = 0, w2 = 0;
   T gv[6] = {0, 0, 0, 0, 0, 0};
+  T acc1 = 0, acc2 = 0;
   const int64_t tf = (int64_t)b * bp.F + (covered ? f : 0);
   T k3 = 1, dw1[6], dw2[6];
   if (covered) {
@@ -132,10 +133,10 @@ __global__ void __launch_bounds__(256) raster_bwd_kernel(RasterBwdParams<T> bp, 
     if (covered) {
       gd = g[d];
       const T c0 = ff[d], c1 = ff[C + d], c2 = ff[2 * C + d];
-      const T dldI = gd * inv_k3sq;                  // :389
-      const T e1 = c1 - c0, e2 = c2 - c0;
-#pragma unroll
-      for (int k = 0; k < 6; ++k) gv[k] += dldI * (e1 * dw1[k] + e2 * dw2[k]);   // :382-387
+      // :382-389: dL/dI_d * ((c1-c0) * dw1[k] + (c2-c0) * dw2[k]) summed over the channels = acc1 * dw1[k] +
+      // acc2 * dw2[k]: the six products are taken once per pixel, after the channel loop
+      acc1 += gd * (c1 - c0);
+      acc2 += gd * (c2 - c0);
     }
     // :273-285 feature gradients, aggregated per face inside the warp
     const T s0 = group_sum<T>(gd * w0, src, steps);
@@ -149,6 +150,11 @@ __global__ void __launch_bounds__(256) raster_bwd_kernel(RasterBwdParams<T> bp, 
   }
   }
   T* gi = bp.grad_img + tf * 6;
+  acc1 *= inv_k3sq; acc2 *= inv_k3sq;
+  if (covered) {                                       // dw1 / dw2 are only defined on covered lanes
+#pragma unroll
+    for (int k = 0; k < 6; ++k) gv[k] = acc1 * dw1[k] + acc2 * dw2[k];
+  }
 #pragma unroll
   for (int k = 0; k < 6; ++k) {
     const T sk = group_sum<T>(gv[k], src, steps);
