@@ -145,6 +145,14 @@ int dibr_rasterize_backward_multi_f64(const double* const* grad_outs, const int6
  *  Outputs: soft (B,H,W); the k-list side buffers prob (B,H,W,K), close_idx (B,H,W,K) int64,
  *  dist_type (B,H,W,K) uint8 are written only when all three are non-NULL (all NULL = skip them;
  *  the backward then recomputes).
+ *  keep_pairs != 0 (fused variant, side buffers NULL): a backward will follow — `ws` then has
+ *  dibr_soft_mask_workspace_bytes(..., keep_pairs = 1, elem_size) bytes and the kernel also appends every
+ *  evaluated (pixel, face, distance type, probability) to a pair log behind the bins (16 bytes per pair, room
+ *  for two pairs per pixel; see dibr_soft_mask_bwd_fused, bins_ready == 2).  If the workspace is too small for
+ *  the log, or B*H*W >= 2^32, the log is silently not kept and the matching backward recomputes.
+ *  fp32 fused variant: the three double divisions per edge of dibr_soft_mask_cuda.cu:126-138 are evaluated as
+ *  one double reciprocal and three multiplications (soft mask within a few fp32 ulp of the reference-shaped
+ *  entry point, which keeps the exact divisions because its dist_type output is API-visible).
  */
 int dibr_soft_mask_fwd_fused_f32(const float* img, const int64_t* face_idx, int B, int F, int H, int W,
                                  float sigmainv, double boxlen, int knum, double multiplier, float* soft,
