@@ -567,7 +567,14 @@ __device__ __forceinline__ void soft_tile(const SoftParams<T>& sp, const FaceLay
           if (MODE == MODE_FWD) {
             const T* row = s_cell + threadIdx.x * KS;
             T allprob = s_acc[sb0 + threadIdx.x];
-            for (int k = 0; k < kid; ++k) allprob = (T)((double)allprob * (1.0 - (double)row[k]));
+            if (sizeof(T) == 4 && !sp.prob) {
+              // fp32 fused path: the running product (:174-178, float * double rounded to float at every step in
+              // the reference) is taken in fp32 — a dependent chain of fp64 conversions / multiplies per hit
+              // otherwise; <= 1 ulp per factor, far inside the 1e-4 tolerance of the soft mask
+              for (int k = 0; k < kid; ++k) allprob = allprob * ((T)1 - row[k]);
+            } else {
+              for (int k = 0; k < kid; ++k) allprob = (T)((double)allprob * (1.0 - (double)row[k]));
+            }
             s_acc[sb0 + threadIdx.x] = allprob;
           }
           s_ktot[sb0 + threadIdx.x] += kid;

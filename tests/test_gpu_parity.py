@@ -143,8 +143,8 @@ def test_simple_dibr_soft_mask(kal, dname, sigmainv, boxlen, multiplier, knum):
     soft2 = kal.render.mesh.dibr_soft_mask(img_l, idx, sigmainv, boxlen, knum, multiplier)
     assert torch.allclose(soft2, gt_soft, atol=1e-5, rtol=1e-5)
     # the fused entry point (fp32) replaces the per-edge double divisions by one reciprocal and multiplications
-    # (dibr_common.cuh:soft_distance): agreement within a few ulp, identical for fp64
-    assert torch.allclose(soft2, soft, rtol=1e-6, atol=1e-7) if soft.dtype == torch.float32 else torch.equal(soft2, soft)
+    # (dibr_common.cuh:soft_distance) and takes the running product in fp32: a few ulp per factor, identical for fp64
+    assert torch.allclose(soft2, soft, rtol=1e-5, atol=1e-6) if soft.dtype == torch.float32 else torch.equal(soft2, soft)
     shifted = torch.nn.functional.pad(idx != -1, (0, 5))[..., 5:]
     mask_iou(soft2, shifted).backward()
     gt_grad = torch.from_numpy(g["grad_face_vertices_image_" + tag]).to("cuda", dtype)

@@ -91,8 +91,8 @@ def full_pipeline_check(kal, O, backend, d, knum=30, boxlen=0.02, sigmainv=7000.
         pmin, pmax = img_m.min(dim=-2)[0], img_m.max(dim=-2)[0]
         bb = torch.cat([pmin - boxlen * multiplier, pmax + boxlen * multiplier], -1).contiguous()
         s2, p2, c2, t2 = kal._C.render.mesh.dibr_soft_mask_forward_cuda(img_m, bb, face_idx, sigmainv, knum, multiplier)
-        # reference-shaped vs fused entry point: exact divisions vs reciprocal form in fp32 (a few ulp)
-        assert torch.allclose(s2, soft, rtol=1e-6, atol=1e-7) if soft.dtype == torch.float32 else torch.equal(s2, soft)
+        # reference-shaped vs fused entry point: exact divisions / double product vs reciprocal form / fp32 product
+        assert torch.allclose(s2, soft, rtol=1e-5, atol=1e-6) if soft.dtype == torch.float32 else torch.equal(s2, soft)
         assert torch.equal(c2.cpu(), r_cidx.cpu()), "close_face_idx mismatch"
         rel_close(p2.cpu(), r_prob.cpu(), 1e-5, "close_face_prob")
         mism = (t2.cpu() != r_ctype.cpu()).float().mean().item()
