@@ -199,19 +199,45 @@ __device__ __forceinline__ void smem_max_u64(unsigned long long* addr, const uns
 __constant__ unsigned RECIP16[17] = {0, 65536, 32768, 21846, 16384, 13108, 10923, 9363, 8192,
                                      7282, 6554, 5958, 5462, 5042, 4682, 4370, 4096};
 
+constexpr int HIT_BUF = 64;        // per-warp deferred-hit stack: < 32 left over + <= 32 appended per iteration
+
 struct ScatterShared {
   unsigned long long key[TILE_PIX];
   float px[TILE], py[TILE];       // pixel-centre coordinates of the tile's columns / rows
   int wq[8][32];                  // per-warp compaction queue for the filtered "large" faces
+  int2 hit[8][HIT_BUF];           // per-warp stack of (face, tile-local pixel) pairs awaiting the exact test
   int nan_seen;
 };
 
-// One warp, up to 32 faces (lane = face, f < 0 = none; the valid lanes must be the low lanes).
+// Exact evaluation of up to 32 deferred pairs (lane < n takes hit[lane]): the reference's barycentric weights with
+// their three IEEE divisions, inside test, depth, and the order-independent merge into the pixel's key.  All lanes
+// are busy here, whereas evaluated in the pair loop the divisions ran for the few inside lanes of each iteration.
+__device__ __forceinline__ void resolve_hits(const RasterFwdParams<float>& rp, ScatterShared& sh,
+                                             const int64_t vbase, const int2* hit, const int n) {
+  const int lane = lane_id();
+  if (lane >= n) return;
+  const int2 h = hit[lane];
+  float p[6], w0, w1, w2;
+  load_face_xy<float>(rp.img, vbase + h.x, rp.coord_mult, rp.premultiplied, p);
+  const float* zz = rp.z + (vbase + h.x) * 3;
+  const float az = __ldg(zz), bz = __ldg(zz + 1), cz = __ldg(zz + 2);
+  if (!bary_weights<float>(p[0], p[1], p[2], p[3], p[4], p[5], sh.px[h.y & (TILE - 1)], sh.py[h.y >> 4], rp.eps,
+                           w0, w1, w2))
+    return;
+  float z0 = interp3<float>(az, bz, cz, w0, w1, w2);
+  if (z0 != z0) { sh.nan_seen = 1; return; }                       // tile falls back to the in-order rule
+  z0 = __fadd_rn(z0, 0.0f);                                        // -0 -> +0: the reference compares values
+  const unsigned long long key = ((unsigned long long)ord_f32(z0) << 32) | (unsigned)(0xffffffffu - (unsigned)h.x);
+  smem_max_u64(&sh.key[h.y], key);
+}
+
+// One warp, up to 32 faces (lane = face, f < 0 = none; the valid lanes must be the low lanes).  `nhit` (warp-
+// uniform) = entries on the warp's hit stack; the caller resolves what is left after its last call.
 __device__ __forceinline__ void scatter_faces(const RasterFwdParams<float>& rp, const BinLists& L,
                                               ScatterShared& sh, const int64_t vbase, const int f,
-                                              const int rx0, const int ry0) {
+                                              const int rx0, const int ry0, int2* hit, int& nhit) {
   const int lane = lane_id();
-  float ax = 0, ay = 0, bx = 0, by = 0, cx = 0, cy = 0, az = 0, bz = 0, cz = 0;
+  float ax = 0, ay = 0, bx = 0, by = 0, cx = 0, cy = 0;
   unsigned rect = 0;
   int n = 0;
   if (f >= 0) {
@@ -225,8 +251,6 @@ __device__ __forceinline__ void scatter_faces(const RasterFwdParams<float>& rp, 
       float p[6];
       load_face_xy<float>(rp.img, vbase + f, rp.coord_mult, rp.premultiplied, p);
       ax = p[0]; ay = p[1]; bx = p[2]; by = p[3]; cx = p[4]; cy = p[5];
-      const float* zz = rp.z + (vbase + f) * 3;
-      az = __ldg(zz); bz = __ldg(zz + 1); cz = __ldg(zz + 2);
     }
   }
   // exclusive prefix of the pair counts
@@ -242,6 +266,7 @@ __device__ __forceinline__ void scatter_faces(const RasterFwdParams<float>& rp, 
   const bool holes = (nonempty & (nonempty + 1u)) != 0u;          // non-empty lanes are not a prefix (never by
                                                                   // construction; handled for robustness)
   const unsigned le_mask = 0xffffffffu >> (31 - lane);
+  const unsigned lt_mask = le_mask >> 1;
   for (int c0 = 0; c0 < total; c0 += 32) {
     const unsigned rel = (unsigned)(start - c0);
     const unsigned bit = (n > 0 && rel < 32u) ? (1u << rel) : 0u;
@@ -257,22 +282,26 @@ __device__ __forceinline__ void scatter_faces(const RasterFwdParams<float>& rp, 
     const float oax = __shfl_sync(0xffffffffu, ax, owner), oay = __shfl_sync(0xffffffffu, ay, owner);
     const float obx = __shfl_sync(0xffffffffu, bx, owner), oby = __shfl_sync(0xffffffffu, by, owner);
     const float ocx = __shfl_sync(0xffffffffu, cx, owner), ocy = __shfl_sync(0xffffffffu, cy, owner);
-    const float oaz = __shfl_sync(0xffffffffu, az, owner), obz = __shfl_sync(0xffffffffu, bz, owner);
-    const float ocz = __shfl_sync(0xffffffffu, cz, owner);
     const int of = __shfl_sync(0xffffffffu, f, owner);
-    if (!active) continue;
     const unsigned q = (unsigned)(p - ostart);
     const unsigned wq = ((orect >> 8) & 15u) + 1u;
     const unsigned row = (q * (orect >> 12)) >> 16;
     const unsigned col = q - row * wq;
-    const unsigned lx = (orect & 15u) + col, ly = ((orect >> 4) & 15u) + row;
-    float w0, w1, w2;
-    if (!bary_weights_fast(oax, oay, obx, oby, ocx, ocy, sh.px[lx], sh.py[ly], rp.eps, w0, w1, w2)) continue;
-    float z0 = interp3<float>(oaz, obz, ocz, w0, w1, w2);
-    if (z0 != z0) { sh.nan_seen = 1; continue; }                   // tile falls back to the in-order rule
-    z0 = __fadd_rn(z0, 0.0f);                                      // -0 -> +0: the reference compares values
-    const unsigned long long key = ((unsigned long long)ord_f32(z0) << 32) | (unsigned)(0xffffffffu - (unsigned)of);
-    smem_max_u64(&sh.key[ly * TILE + lx], key);
+    const unsigned lx = ((orect & 15u) + col) & 15u, ly = (((orect >> 4) & 15u) + row) & 15u;   // (& 15: inactive lanes)
+    // division-free: pairs that are not certainly outside go on the warp's stack and get the exact test in full
+    // batches of 32 (resolve_hits)
+    const bool maybe = active && !bary_certain_reject(oax, oay, obx, oby, ocx, ocy, sh.px[lx], sh.py[ly], rp.eps);
+    const unsigned hm = __ballot_sync(0xffffffffu, maybe);
+    if (hm != 0u) {                                                  // warp-uniform
+      if (maybe) hit[nhit + __popc(hm & lt_mask)] = make_int2(of, (int)(ly * TILE + lx));
+      nhit += __popc(hm);
+      __syncwarp();
+      if (nhit >= 32) {
+        nhit -= 32;
+        resolve_hits(rp, sh, vbase, hit + nhit, 32);                 // the top 32 entries
+        __syncwarp();
+      }
+    }
   }
 }
 
@@ -337,9 +366,11 @@ __global__ void __launch_bounds__(NT, 1024 / NT) raster_fwd_scatter_kernel(Raste
   // busy: the parallelism is in the pairs, not in the faces)
   const int per_warp = (n_tile + NW - 1) / NW;
   const int slice_end = min(n_tile, (warp + 1) * per_warp);
+  int2* hit = sh.hit[warp];
+  int nhit = 0;
   for (int base = warp * per_warp; base < slice_end; base += 32) {   // warp-uniform trip count
     const int k = base + lane;
-    scatter_faces(rp, L, sh, vbase, (k < slice_end) ? tile_list[k] : -1, rx0, ry0);
+    scatter_faces(rp, L, sh, vbase, (k < slice_end) ? tile_list[k] : -1, rx0, ry0, hit, nhit);
   }
   // faces binned at the coarse level / in the view's large list: filter against the tile, compact, scatter
   const int n_filt = tl.n_filtered();
@@ -356,8 +387,9 @@ __global__ void __launch_bounds__(NT, 1024 / NT) raster_fwd_scatter_kernel(Raste
     __syncwarp();
     f = (lane < __popc(m)) ? sh.wq[warp][lane] : -1;
     __syncwarp();
-    scatter_faces(rp, L, sh, vbase, f, rx0, ry0);
+    scatter_faces(rp, L, sh, vbase, f, rx0, ry0, hit, nhit);
   }
+  resolve_hits(rp, sh, vbase, hit, nhit);                             // what is left on the warp's stack (< 32)
   __syncthreads();
 
   const bool nan_seen = sh.nan_seen != 0;                             // CTA-uniform, rare
