@@ -13,7 +13,8 @@ import torch  # noqa: F401  (imported first so that libcudart.so.12 is already m
 
 _PKG = os.path.dirname(os.path.abspath(__file__))
 _ROOT = os.path.dirname(_PKG)
-LIB_PATH = os.path.join(_PKG, "libdibr_b200.so")
+# DIBR_B200_LIB selects another build of the same library (kernel-tuning experiments); the default is in-tree
+LIB_PATH = os.environ.get("DIBR_B200_LIB") or os.path.join(_PKG, "libdibr_b200.so")
 CSRC = os.path.join(_PKG, "csrc")
 SOURCES = ["dibr_c_abi.cu"]
 HEADERS = ["dibr_common.cuh", "dibr_binning.cuh", "dibr_raster_fwd.cuh", "dibr_raster_bwd.cuh",

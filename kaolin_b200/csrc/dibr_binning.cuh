@@ -29,6 +29,7 @@ struct BinLists {
   int* large_list;    // [Ntot]  view b's entries start at view_base(b)
   int* large_count;   // [B]
   int* alloc_cursor;  // [1]
+  int* tile_order;    // [B*tiles_per_view] per view: its tiles sorted by decreasing candidate count (log2 buckets)
 };
 
 constexpr int MAX_FEATS = 8;
@@ -139,6 +140,13 @@ __global__ void __launch_bounds__(256) setup_count_kernel(SetupParams<T> sp, Fac
   L.ranges[g] = rec;
 }
 
+// scheduling weight of a tile: its own list + a share of the enclosing coarse cell's list (filtered by the consumer)
+__device__ __forceinline__ int tile_weight_bucket(const int* cnt, const Geometry& geo, const int t) {
+  const int tx = t % geo.tiles_x, ty = t / geo.tiles_x;
+  const int w = cnt[t] + (cnt[geo.tiles_per_view + (ty / COARSE) * geo.coarse_x + (tx / COARSE)] >> 2);
+  return w > 0 ? 32 - __clz(w) : 0;
+}
+
 // one CTA per view
 __global__ void __launch_bounds__(1024) scan_kernel(Geometry geo, BinLists L) {
   __shared__ int warp_sums[32];
@@ -196,6 +204,33 @@ __global__ void __launch_bounds__(1024) scan_kernel(Geometry geo, BinLists L) {
     }
     running += total;
   }
+  // pass 3: launch order of the view's tiles for the per-tile kernels — heaviest first (longest-processing-time
+  // scheduling: a few tiles hold hundreds of sliver faces and would otherwise finish long after the rest of the
+  // grid).  Buckets of floor(log2(weight)) + 1; the order inside a bucket is arbitrary (it only affects scheduling).
+  __shared__ int hist[33], bbase[33];
+  if (threadIdx.x < 33) hist[threadIdx.x] = 0;
+  __syncthreads();
+  int* order = L.tile_order + (int64_t)b * geo.tiles_per_view;
+  for (int t = threadIdx.x; t < geo.tiles_per_view; t += blockDim.x)
+    atomicAdd(&hist[tile_weight_bucket(cnt, geo, t)], 1);
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    int run = 0;
+    for (int k = 32; k >= 0; --k) { bbase[k] = run; run += hist[k]; hist[k] = 0; }
+  }
+  __syncthreads();
+  for (int t = threadIdx.x; t < geo.tiles_per_view; t += blockDim.x) {
+    const int k = tile_weight_bucket(cnt, geo, t);
+    order[bbase[k] + atomicAdd(&hist[k], 1)] = t;
+  }
+}
+
+// blockIdx -> (view, tile) of the per-tile kernels: consecutive CTAs take the same rank in different views, ranks
+// go from the heaviest tile of each view to the lightest.
+__device__ __forceinline__ void scheduled_tile(const BinLists& L, const Geometry& geo, const unsigned block, int& b,
+                                               int& tile) {
+  b = (int)(block % (unsigned)geo.B);
+  tile = L.tile_order[(int64_t)b * geo.tiles_per_view + (block / (unsigned)geo.B)];
 }
 
 __global__ void __launch_bounds__(256) fill_kernel(FaceLayout fl, Geometry geo, BinLists L) {

@@ -62,7 +62,7 @@ inline size_t align_up(size_t v, size_t a = 256) { return (v + a - 1) / a * a; }
 
 // Workspace carving: two BinLists (index 0 = rasterizer, 1 = soft mask) — each entry point uses one.
 struct WsLayout {
-  size_t ranges, tile_count, tile_offset, tile_cursor, pairs, large_list, large_count, alloc_cursor;
+  size_t ranges, tile_count, tile_offset, tile_cursor, pairs, large_list, large_count, alloc_cursor, tile_order;
   size_t zero_begin, zero_end;     // [tile_count | large_count | alloc_cursor] are contiguous => one memset
   size_t total;
 };
@@ -77,6 +77,7 @@ WsLayout ws_layout(int B, int64_t Ntot, const Geometry& geo) {
   w.zero_end = o;
   w.tile_offset = o; o = align_up(o + bt * sizeof(int));
   w.tile_cursor = o; o = align_up(o + bt * sizeof(int));
+  w.tile_order = o;  o = align_up(o + (size_t)B * geo.tiles_per_view * sizeof(int));
   w.ranges = o;      o = align_up(o + (size_t)Ntot * sizeof(uint2));
   w.large_list = o;  o = align_up(o + (size_t)Ntot * sizeof(int));
   w.pairs = o;       o = align_up(o + (size_t)Ntot * PAIRS_PER_FACE * sizeof(int));
@@ -94,6 +95,7 @@ BinLists carve(void* ws, const WsLayout& w) {
   L.large_list = reinterpret_cast<int*>(p + w.large_list);
   L.large_count = reinterpret_cast<int*>(p + w.large_count);
   L.alloc_cursor = reinterpret_cast<int*>(p + w.alloc_cursor);
+  L.tile_order = reinterpret_cast<int*>(p + w.tile_order);
   return L;
 }
 

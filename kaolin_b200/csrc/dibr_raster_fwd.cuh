@@ -161,8 +161,8 @@ __global__ void __launch_bounds__(256) raster_fwd_kernel(RasterFwdParams<T> rp, 
                                                          BinLists L) {
   __shared__ StagedFace<T> st;
   __shared__ int scratch[9];
-  const int tile = blockIdx.x % geo.tiles_per_view;
-  const int b = blockIdx.x / geo.tiles_per_view;
+  int b, tile;
+  scheduled_tile(L, geo, blockIdx.x, b, tile);
   const int tx = tile % geo.tiles_x, ty = tile / geo.tiles_x;
   const int px = tx * TILE + (threadIdx.x & (TILE - 1));
   const int py = ty * TILE + (threadIdx.x / TILE);
@@ -337,13 +337,16 @@ __device__ __forceinline__ void scan_pixel_in_order_rule(const RasterFwdParams<f
 }
 
 // NT threads per CTA (one CTA per 16x16 tile whatever NT).
+#ifndef DIBR_RASTER_TPS
+#define DIBR_RASTER_TPS 1024       // resident threads per SM the register allocation aims at
+#endif
 template <int NT>
-__global__ void __launch_bounds__(NT, 1024 / NT) raster_fwd_scatter_kernel(RasterFwdParams<float> rp, FaceLayout fl,
-                                                                           Geometry geo, BinLists L) {
+__global__ void __launch_bounds__(NT, DIBR_RASTER_TPS / NT)
+raster_fwd_scatter_kernel(RasterFwdParams<float> rp, FaceLayout fl, Geometry geo, BinLists L) {
   constexpr int NW = NT / 32;
   __shared__ ScatterShared sh;
-  const int tile = blockIdx.x % geo.tiles_per_view;
-  const int b = blockIdx.x / geo.tiles_per_view;
+  int b, tile;
+  scheduled_tile(L, geo, blockIdx.x, b, tile);
   const int tx = tile % geo.tiles_x, ty = tile / geo.tiles_x;
   const int rx0 = tx * TILE, ry0 = ty * TILE;
   const int64_t vbase = fl.base(b);

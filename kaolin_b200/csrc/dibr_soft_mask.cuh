@@ -606,7 +606,9 @@ __device__ __forceinline__ void soft_tile(const SoftParams<T>& sp, const FaceLay
 template <typename T, int MODE, int NT>
 __global__ void __launch_bounds__(NT, (sizeof(T) == 4 ? 1024 / NT : 512 / NT))
 soft_mask_kernel(SoftParams<T> sp, FaceLayout fl, Geometry geo, BinLists L) {
-  soft_tile<T, MODE, NT>(sp, fl, geo, L, blockIdx.x);
+  int b, tile;
+  scheduled_tile(L, geo, blockIdx.x, b, tile);
+  soft_tile<T, MODE, NT>(sp, fl, geo, L, (unsigned)b * (unsigned)geo.tiles_per_view + (unsigned)tile);
 }
 
 // Backward of the tiles whose pairs did not fit the log: a small persistent grid walks the overflow list
