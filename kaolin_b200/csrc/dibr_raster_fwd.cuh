@@ -195,83 +195,133 @@ __device__ __forceinline__ void smem_max_u64(unsigned long long* addr, const uns
   }
 }
 
-// floor(q / w) for 0 <= q < 256, 1 <= w <= 16 is (q * RECIP16[w]) >> 16 with RECIP16[w] = ceil(65536 / w).
-__constant__ unsigned RECIP16[17] = {0, 65536, 32768, 21846, 16384, 13108, 10923, 9363, 8192,
-                                     7282, 6554, 5958, 5462, 5042, 4682, 4370, 4096};
+// ---- span rasterization (fp32).  Work items are (face, pixel row) pairs of the face's pixel range clipped to the
+// tile.  For each row a CONSERVATIVE column span is derived from the three edge functions; only the pixels of the
+// span ("candidates") get the reference's exact test with its IEEE divisions (resolve_hits), so the cost follows the
+// triangle's area instead of its bounding box (sliver meshes: < 1 % of the bbox pixels are inside).
+//
+// Why no inside pixel can be lost.  With u = 2^-24, the reference's w_i (rasterization_cuda.cu:131-139) differs
+// from the exact edge function W_i(x0,y0) by at most 5u S, S = |bex||cey| + |bey||cex| <= 2 Dx Dy, where Dx / Dy
+// bound the distance of every vertex from every pixel centre of the clipped range.  W_0 + W_1 + W_2 = N (twice the
+// signed area) for every pixel, the reference's norm differs from N by at most 42u Dx Dy and the fp32 estimate nc
+// below by at most 40u Dx Dy: if |nc| > 128u Dx Dy (+2^-38 for underflow) the reference's norm has the sign s of nc
+// at every pixel of the range (and |norm| <= 2^80 as Dx Dy, |eps| <= 1e18).  A pixel with s W_i <= -(5u S + 2^-39)
+// then has s w_i <= -2^-39: a non-zero quotient of the opposite sign, i.e. the reference rejects it.  s W_i is
+// linear along a row: t_r + a_i (x0 - xr) with t_r its value at the range's first column, which the row item
+// evaluates with the reference's own expression (error <= 5u S), a_i = s dW_i/dx.  Excluding the columns
+// d < (t_r + m2) * (-1 / (a_i pitch)) - 1/64 (a_i > 0; mirrored for a_i < 0) with m2 = 32u Dx Dy + 2^-38 leaves a
+// margin of 5u S for t_r, 5u S + 2^-39 for the claim and 1/64 pixel for the rounding of the bound (<= 2^-16 px)
+// and for the deviation of the fp32 pixel centres from an exact lattice (<= W u <= 2^-9 px for W <= 32768).
+// Faces that fail the |nc| test (degenerate or huge) keep their whole range: span = bbox, as before.
+constexpr int HIT_CAP = 32 + 32 * TILE;     // < 32 left over + one row iteration's candidates (32 rows x 16 columns)
 
-constexpr int HIT_BUF = 64;        // per-warp deferred-hit stack: < 32 left over + <= 32 appended per iteration
-
+template <int NW>
 struct ScatterShared {
   unsigned long long key[TILE_PIX];
   float px[TILE], py[TILE];       // pixel-centre coordinates of the tile's columns / rows
-  int wq[8][32];                  // per-warp compaction queue for the filtered "large" faces
-  int2 hit[8][HIT_BUF];           // per-warp stack of (face, tile-local pixel) pairs awaiting the exact test
+  int wq[NW][32];                 // per-warp compaction queue for the filtered "large" faces
+  unsigned short hit[NW][HIT_CAP];// per-warp stack of candidates: owner lane << 8 | row << 4 | column
+  float pitch;                    // x distance of neighbouring pixel centres (2 * multiplier / W)
   int nan_seen;
 };
 
-// Exact evaluation of up to 32 deferred pairs (lane < n takes hit[lane]): the reference's barycentric weights with
-// their three IEEE divisions, inside test, depth, and the order-independent merge into the pixel's key.  All lanes
-// are busy here, whereas evaluated in the pair loop the divisions ran for the few inside lanes of each iteration.
-__device__ __forceinline__ void resolve_hits(const RasterFwdParams<float>& rp, ScatterShared& sh,
-                                             const int64_t vbase, const int2* hit, const int n) {
+struct FaceRegs {                 // one face per lane (multiplied coordinates), read by shuffle from its owner lane
+  float ax, ay, bx, by, cx, cy, az, bz, cz;
+  int f;
+};
+
+// Exact evaluation of up to 32 candidates (lane < n takes hit[lane]): the reference's barycentric weights with
+// their three IEEE divisions, inside test, depth, and the order-independent merge into the pixel's key.  Called
+// with all 32 lanes (the face data comes by shuffle from the lane that owns the face).
+template <int NW>
+__device__ __forceinline__ void resolve_hits(const RasterFwdParams<float>& rp, ScatterShared<NW>& sh,
+                                             const FaceRegs& fr, const unsigned short* hit, const int n) {
   const int lane = lane_id();
-  if (lane >= n) return;
-  const int2 h = hit[lane];
-  float p[6], w0, w1, w2;
-  load_face_xy<float>(rp.img, vbase + h.x, rp.coord_mult, rp.premultiplied, p);
-  const float* zz = rp.z + (vbase + h.x) * 3;
-  const float az = __ldg(zz), bz = __ldg(zz + 1), cz = __ldg(zz + 2);
-  if (!bary_weights<float>(p[0], p[1], p[2], p[3], p[4], p[5], sh.px[h.y & (TILE - 1)], sh.py[h.y >> 4], rp.eps,
-                           w0, w1, w2))
-    return;
+  const bool act = lane < n;
+  const unsigned e = act ? (unsigned)hit[lane] : 0u;
+  const int owner = (int)(e >> 8);
+  const float ax = __shfl_sync(0xffffffffu, fr.ax, owner), ay = __shfl_sync(0xffffffffu, fr.ay, owner);
+  const float bx = __shfl_sync(0xffffffffu, fr.bx, owner), by = __shfl_sync(0xffffffffu, fr.by, owner);
+  const float cx = __shfl_sync(0xffffffffu, fr.cx, owner), cy = __shfl_sync(0xffffffffu, fr.cy, owner);
+  const float az = __shfl_sync(0xffffffffu, fr.az, owner), bz = __shfl_sync(0xffffffffu, fr.bz, owner);
+  const float cz = __shfl_sync(0xffffffffu, fr.cz, owner);
+  const int f = __shfl_sync(0xffffffffu, fr.f, owner);
+  if (!act) return;
+  float w0, w1, w2;
+  if (!bary_weights<float>(ax, ay, bx, by, cx, cy, sh.px[e & 15u], sh.py[(e >> 4) & 15u], rp.eps, w0, w1, w2)) return;
   float z0 = interp3<float>(az, bz, cz, w0, w1, w2);
   if (z0 != z0) { sh.nan_seen = 1; return; }                       // tile falls back to the in-order rule
   z0 = __fadd_rn(z0, 0.0f);                                        // -0 -> +0: the reference compares values
-  const unsigned long long key = ((unsigned long long)ord_f32(z0) << 32) | (unsigned)(0xffffffffu - (unsigned)h.x);
-  smem_max_u64(&sh.key[h.y], key);
+  const unsigned long long key = ((unsigned long long)ord_f32(z0) << 32) | (unsigned)(0xffffffffu - (unsigned)f);
+  smem_max_u64(&sh.key[e & 255u], key);
 }
 
-// One warp, up to 32 faces (lane = face, f < 0 = none; the valid lanes must be the low lanes).  `nhit` (warp-
-// uniform) = entries on the warp's hit stack; the caller resolves what is left after its last call.
+// One warp, up to 32 faces (lane = face, f < 0 = none; the valid lanes must be the low lanes).
+template <int NW>
 __device__ __forceinline__ void scatter_faces(const RasterFwdParams<float>& rp, const BinLists& L,
-                                              ScatterShared& sh, const int64_t vbase, const int f,
-                                              const int rx0, const int ry0, int2* hit, int& nhit) {
+                                              ScatterShared<NW>& sh, const int64_t vbase, const int f,
+                                              const int rx0, const int ry0, unsigned short* hit) {
+  typedef RN<float> R;
   const int lane = lane_id();
-  float ax = 0, ay = 0, bx = 0, by = 0, cx = 0, cy = 0;
+  FaceRegs fr;
+  fr.ax = fr.ay = fr.bx = fr.by = fr.cx = fr.cy = fr.az = fr.bz = fr.cz = 0.0f;
+  fr.f = f;
+  float exa = 0, exb = 0, exc = 0;       // vertex x minus the x of the range's first column (reference rounding)
+  float rn0 = 0, rn1 = 0, rn2 = 0;       // -1 / (a_i * pitch); 0 = edge i gives no bound
+  float ms = 0;                          // margin m2 carrying the sign s of the face's area
   unsigned rect = 0;
-  int n = 0;
+  int h = 0;
   if (f >= 0) {
     const uint2 r = L.ranges[vbase + f];
     const int lx0 = max((int)(r.x & 0xffffu), rx0) - rx0, lx1 = min((int)(r.x >> 16), rx0 + TILE - 1) - rx0;
     const int ly0 = max((int)(r.y & 0xffffu), ry0) - ry0, ly1 = min((int)(r.y >> 16), ry0 + TILE - 1) - ry0;
-    const int w = lx1 - lx0 + 1, h = ly1 - ly0 + 1;
-    if (w > 0 && h > 0) {
-      n = w * h;
-      rect = (unsigned)lx0 | ((unsigned)ly0 << 4) | ((unsigned)(w - 1) << 8) | (RECIP16[w] << 12);
+    const int w = lx1 - lx0 + 1, hh = ly1 - ly0 + 1;
+    if (w > 0 && hh > 0) {
+      h = hh;
+      rect = (unsigned)lx0 | ((unsigned)ly0 << 4) | ((unsigned)(w - 1) << 8);
       float p[6];
       load_face_xy<float>(rp.img, vbase + f, rp.coord_mult, rp.premultiplied, p);
-      ax = p[0]; ay = p[1]; bx = p[2]; by = p[3]; cx = p[4]; cy = p[5];
+      fr.ax = p[0]; fr.ay = p[1]; fr.bx = p[2]; fr.by = p[3]; fr.cx = p[4]; fr.cy = p[5];
+      const float* zz = rp.z + (vbase + f) * 3;
+      fr.az = __ldg(zz); fr.bz = __ldg(zz + 1); fr.cz = __ldg(zz + 2);
+      const float xl = sh.px[lx0], xh = sh.px[lx1], yl = sh.py[ly0], yh = sh.py[ly1];
+      exa = R::sub(p[0], xl); exb = R::sub(p[2], xl); exc = R::sub(p[4], xl);
+      const float dx = fmaxf(fmaxf(fmaxf(fabsf(p[0] - xl), fabsf(p[0] - xh)), fmaxf(fabsf(p[2] - xl), fabsf(p[2] - xh))),
+                             fmaxf(fabsf(p[4] - xl), fabsf(p[4] - xh)));
+      const float dy = fmaxf(fmaxf(fmaxf(fabsf(p[1] - yl), fabsf(p[1] - yh)), fmaxf(fabsf(p[3] - yl), fabsf(p[3] - yh))),
+                             fmaxf(fabsf(p[5] - yl), fabsf(p[5] - yh)));
+      const float dd = dx * dy;
+      const float nc = fmaf(p[2] - p[0], p[5] - p[1], -((p[3] - p[1]) * (p[4] - p[0])));
+      if (fabsf(nc) > fmaf(dd, 7.62939453125e-6f /* 2^-17 */, 3.637978807091713e-12f /* 2^-38 */) && dd <= 1e18f &&
+          fabsf(rp.eps) <= 1e18f) {                                  // false for NaN / inf operands
+        ms = copysignf(fmaf(dd, 1.9073486328125e-6f /* 2^-19 */, 3.637978807091713e-12f), nc);
+        const float sp = copysignf(sh.pitch, nc);                    // s * pitch
+        const float a0 = (p[3] - p[5]) * sp, a1 = (p[5] - p[1]) * sp, a2 = (p[1] - p[3]) * sp;
+        rn0 = a0 != 0.0f ? -1.0f / a0 : 0.0f;
+        rn1 = a1 != 0.0f ? -1.0f / a1 : 0.0f;
+        rn2 = a2 != 0.0f ? -1.0f / a2 : 0.0f;
+      }
     }
   }
-  // exclusive prefix of the pair counts
-  int incl = n;
+  // exclusive prefix of the row counts
+  int incl = h;
 #pragma unroll
   for (int o = 1; o < 32; o <<= 1) {
     const int t = __shfl_up_sync(0xffffffffu, incl, o);
     if (lane >= o) incl += t;
   }
-  const int start = incl - n;
+  const int start = incl - h;
   const int total = __shfl_sync(0xffffffffu, incl, 31);
-  const unsigned nonempty = __ballot_sync(0xffffffffu, n > 0);
+  const unsigned nonempty = __ballot_sync(0xffffffffu, h > 0);
   const bool holes = (nonempty & (nonempty + 1u)) != 0u;          // non-empty lanes are not a prefix (never by
                                                                   // construction; handled for robustness)
   const unsigned le_mask = 0xffffffffu >> (31 - lane);
-  const unsigned lt_mask = le_mask >> 1;
+  int nhit = 0;                                                     // warp-uniform stack height
   for (int c0 = 0; c0 < total; c0 += 32) {
     const unsigned rel = (unsigned)(start - c0);
-    const unsigned bit = (n > 0 && rel < 32u) ? (1u << rel) : 0u;
+    const unsigned bit = (h > 0 && rel < 32u) ? (1u << rel) : 0u;
     const unsigned starts = __reduce_or_sync(0xffffffffu, bit);
-    const int before = __popc(__ballot_sync(0xffffffffu, n > 0 && start < c0));
+    const int before = __popc(__ballot_sync(0xffffffffu, h > 0 && start < c0));
     int owner = before + __popc(starts & le_mask) - 1;             // rank among the non-empty faces
     if (holes) owner = __fns(nonempty, 0, owner + 1);
     const int p = c0 + lane;
@@ -279,29 +329,62 @@ __device__ __forceinline__ void scatter_faces(const RasterFwdParams<float>& rp, 
     owner = active ? owner : 0;
     const int ostart = __shfl_sync(0xffffffffu, start, owner);
     const unsigned orect = __shfl_sync(0xffffffffu, rect, owner);
-    const float oax = __shfl_sync(0xffffffffu, ax, owner), oay = __shfl_sync(0xffffffffu, ay, owner);
-    const float obx = __shfl_sync(0xffffffffu, bx, owner), oby = __shfl_sync(0xffffffffu, by, owner);
-    const float ocx = __shfl_sync(0xffffffffu, cx, owner), ocy = __shfl_sync(0xffffffffu, cy, owner);
-    const int of = __shfl_sync(0xffffffffu, f, owner);
-    const unsigned q = (unsigned)(p - ostart);
-    const unsigned wq = ((orect >> 8) & 15u) + 1u;
-    const unsigned row = (q * (orect >> 12)) >> 16;
-    const unsigned col = q - row * wq;
-    const unsigned lx = ((orect & 15u) + col) & 15u, ly = (((orect >> 4) & 15u) + row) & 15u;   // (& 15: inactive lanes)
-    // division-free: pairs that are not certainly outside go on the warp's stack and get the exact test in full
-    // batches of 32 (resolve_hits)
-    const bool maybe = active && !bary_certain_reject(oax, oay, obx, oby, ocx, ocy, sh.px[lx], sh.py[ly], rp.eps);
-    const unsigned hm = __ballot_sync(0xffffffffu, maybe);
-    if (hm != 0u) {                                                  // warp-uniform
-      if (maybe) hit[nhit + __popc(hm & lt_mask)] = make_int2(of, (int)(ly * TILE + lx));
-      nhit += __popc(hm);
-      __syncwarp();
-      if (nhit >= 32) {
-        nhit -= 32;
-        resolve_hits(rp, sh, vbase, hit + nhit, 32);                 // the top 32 entries
-        __syncwarp();
-      }
+    const float oay = __shfl_sync(0xffffffffu, fr.ay, owner), oby = __shfl_sync(0xffffffffu, fr.by, owner);
+    const float ocy = __shfl_sync(0xffffffffu, fr.cy, owner);
+    const float oxa = __shfl_sync(0xffffffffu, exa, owner), oxb = __shfl_sync(0xffffffffu, exb, owner);
+    const float oxc = __shfl_sync(0xffffffffu, exc, owner);
+    const float on0 = __shfl_sync(0xffffffffu, rn0, owner), on1 = __shfl_sync(0xffffffffu, rn1, owner);
+    const float on2 = __shfl_sync(0xffffffffu, rn2, owner);
+    const float oms = __shfl_sync(0xffffffffu, ms, owner);
+    int len = 0;
+    unsigned ebase = 0;
+    if (active) {
+      const unsigned ly = (((orect >> 4) & 15u) + (unsigned)(p - ostart)) & 15u;
+      const int wm1 = (int)((orect >> 8) & 15u);
+      const float y0 = sh.py[ly];
+      const float aey = R::sub(oay, y0), bey = R::sub(oby, y0), cey = R::sub(ocy, y0);
+      const float w0 = R::fma(oxb, cey, -R::mul(bey, oxc));          // the reference's w_i at the range's first column
+      const float w1 = R::fma(oxc, aey, -R::mul(cey, oxa));
+      const float w2 = R::fma(oxa, bey, -R::mul(aey, oxb));
+      const unsigned sbit = __float_as_uint(oms) & 0x80000000u;
+      const float m2 = fabsf(oms);
+      const float l0 = (__uint_as_float(__float_as_uint(w0) ^ sbit) + m2) * on0;
+      const float l1 = (__uint_as_float(__float_as_uint(w1) ^ sbit) + m2) * on1;
+      const float l2 = (__uint_as_float(__float_as_uint(w2) ^ sbit) + m2) * on2;
+      float lof = 0.0f, hif = (float)wm1;                            // NaN bounds fail every compare: no constraint
+      if (on0 < 0.0f && l0 > lof) lof = l0;
+      if (on0 > 0.0f && l0 < hif) hif = l0;
+      if (on1 < 0.0f && l1 > lof) lof = l1;
+      if (on1 > 0.0f && l1 < hif) hif = l1;
+      if (on2 < 0.0f && l2 > lof) lof = l2;
+      if (on2 > 0.0f && l2 < hif) hif = l2;
+      lof = fminf(lof, 32.0f); hif = fmaxf(hif, -2.0f);
+      const int dmin = max((int)ceilf(lof - 0.015625f), 0);
+      const int dmax = min((int)floorf(hif + 0.015625f), wm1);
+      len = max(dmax - dmin + 1, 0);
+      ebase = ((unsigned)owner << 8) | (ly << 4) | ((orect & 15u) + (unsigned)dmin);
     }
+    // push the candidates: exclusive prefix of the span lengths, then every lane writes its own
+    int inc2 = len;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+      const int t = __shfl_up_sync(0xffffffffu, inc2, o);
+      if (lane >= o) inc2 += t;
+    }
+    const int tot2 = __shfl_sync(0xffffffffu, inc2, 31);
+    unsigned short* dst = hit + nhit + (inc2 - len);
+    for (int j = 0; j < len; ++j) dst[j] = (unsigned short)(ebase + (unsigned)j);
+    nhit += tot2;
+    __syncwarp();
+    while (nhit >= 32) {                                             // full batches off the top of the stack
+      nhit -= 32;
+      resolve_hits<NW>(rp, sh, fr, hit + nhit, 32);
+    }
+    __syncwarp();
+  }
+  if (nhit > 0) {                                                    // the faces change with the next call
+    resolve_hits<NW>(rp, sh, fr, hit, nhit);
+    __syncwarp();
   }
 }
 
@@ -344,7 +427,7 @@ template <int NT>
 __global__ void __launch_bounds__(NT, DIBR_RASTER_TPS / NT)
 raster_fwd_scatter_kernel(RasterFwdParams<float> rp, FaceLayout fl, Geometry geo, BinLists L) {
   constexpr int NW = NT / 32;
-  __shared__ ScatterShared sh;
+  __shared__ ScatterShared<NW> sh;
   int b, tile;
   scheduled_tile(L, geo, blockIdx.x, b, tile);
   const int tx = tile % geo.tiles_x, ty = tile / geo.tiles_x;
@@ -359,7 +442,10 @@ raster_fwd_scatter_kernel(RasterFwdParams<float> rp, FaceLayout fl, Geometry geo
     const int j = threadIdx.x - TILE;
     sh.py[j] = pix_coord(pix_scale(rp.pix_mult, geo.H), geo.H, geo.H - 1 - (ry0 + j));
   }
-  if (threadIdx.x == 0) sh.nan_seen = 0;
+  if (threadIdx.x == 0) {
+    sh.nan_seen = 0;
+    sh.pitch = __fmul_rn(2.0f, pix_scale(rp.pix_mult, geo.W));
+  }
   __syncthreads();
 
   const TileLists tl = tile_lists(L, geo, fl, b, tx, ty);
@@ -369,11 +455,10 @@ raster_fwd_scatter_kernel(RasterFwdParams<float> rp, FaceLayout fl, Geometry geo
   // busy: the parallelism is in the pairs, not in the faces)
   const int per_warp = (n_tile + NW - 1) / NW;
   const int slice_end = min(n_tile, (warp + 1) * per_warp);
-  int2* hit = sh.hit[warp];
-  int nhit = 0;
+  unsigned short* hit = sh.hit[warp];
   for (int base = warp * per_warp; base < slice_end; base += 32) {   // warp-uniform trip count
     const int k = base + lane;
-    scatter_faces(rp, L, sh, vbase, (k < slice_end) ? tile_list[k] : -1, rx0, ry0, hit, nhit);
+    scatter_faces<NW>(rp, L, sh, vbase, (k < slice_end) ? tile_list[k] : -1, rx0, ry0, hit);
   }
   // faces binned at the coarse level / in the view's large list: filter against the tile, compact, scatter
   const int n_filt = tl.n_filtered();
@@ -390,9 +475,8 @@ raster_fwd_scatter_kernel(RasterFwdParams<float> rp, FaceLayout fl, Geometry geo
     __syncwarp();
     f = (lane < __popc(m)) ? sh.wq[warp][lane] : -1;
     __syncwarp();
-    scatter_faces(rp, L, sh, vbase, f, rx0, ry0, hit, nhit);
+    scatter_faces<NW>(rp, L, sh, vbase, f, rx0, ry0, hit);
   }
-  resolve_hits(rp, sh, vbase, hit, nhit);                             // what is left on the warp's stack (< 32)
   __syncthreads();
 
   const bool nan_seen = sh.nan_seen != 0;                             // CTA-uniform, rare
