@@ -148,6 +148,64 @@ def test_random_soups_vs_ref_C(kal, O, ref_C, Hh, Ww, scale):
     full_pipeline_check(kal, O, ref_C, d, knum=5, boxlen=0.05)
 
 
+def _adversarial_faces(kind, Hh, Ww, seed):
+    """Face sets aimed at the span rasterizer's conservative column bounds (dibr_raster_fwd.cuh): pixel centres
+    exactly on edges, slivers far thinner than a pixel, zero-area and huge faces."""
+    g = torch.Generator().manual_seed(seed)
+    if kind == "lattice":
+        # vertices ON pixel centres, every 3 pixels: horizontal, vertical and diagonal edges through pixel centres
+        xs = (2 * torch.arange(0, Ww, 3, dtype=torch.float32) + 1 - Ww) / Ww
+        ys = (Hh - 2 * torch.arange(0, Hh, 3, dtype=torch.float32) - 1) / Hh
+        gy, gx = torch.meshgrid(ys, xs, indexing="ij")
+        P = torch.stack([gx, gy], -1)
+        a, b, c, d = P[:-1, :-1], P[:-1, 1:], P[1:, :-1], P[1:, 1:]
+        img = torch.cat([torch.stack([a, b, c], -2).reshape(-1, 3, 2), torch.stack([b, d, c], -2).reshape(-1, 3, 2),
+                         torch.stack([a, c, b], -2).reshape(-1, 3, 2)], 0)       # both windings
+    elif kind == "slivers":
+        n = 600
+        ctr = torch.rand(n, 1, 2, generator=g) * 2 - 1
+        ang = torch.rand(n, generator=g) * 2 * math.pi
+        d = torch.stack([torch.cos(ang), torch.sin(ang)], -1)
+        nrm = torch.stack([-d[:, 1], d[:, 0]], -1)
+        length = 0.05 + 1.5 * torch.rand(n, 1, generator=g)
+        width = 10.0 ** (-6 + 5 * torch.rand(n, 1, generator=g))                # 1e-6 .. 1e-1 NDC
+        width[::7] = 0.0                                                        # exactly collinear
+        img = ctr + torch.stack([-0.5 * length * d, 0.5 * length * d, (torch.rand(n, 1, generator=g) - 0.5) * length * d
+                                 + width * nrm], 1)
+    elif kind == "huge":
+        n = 40
+        img = (torch.rand(n, 3, 2, generator=g) - 0.5) * 10.0 ** (torch.randint(0, 6, (n, 1, 1), generator=g).float())
+        img[::5] *= 1e4
+    elif kind == "on_vertex":
+        # random faces snapped so that one vertex sits on a pixel centre and one edge midpoint on another
+        n = 300
+        ix = torch.randint(0, Ww, (n,), generator=g).float(); iy = torch.randint(0, Hh, (n,), generator=g).float()
+        v0 = torch.stack([(2 * ix + 1 - Ww) / Ww, (Hh - 2 * iy - 1) / Hh], -1)
+        jx = torch.randint(0, Ww, (n,), generator=g).float(); jy = torch.randint(0, Hh, (n,), generator=g).float()
+        mid = torch.stack([(2 * jx + 1 - Ww) / Ww, (Hh - 2 * jy - 1) / Hh], -1)
+        v1 = 2 * mid - v0                                                        # pixel (jx, jy) is the midpoint of v0 v1
+        v2 = torch.rand(n, 2, generator=g) * 2 - 1
+        img = torch.stack([v0, v1, v2], 1)
+    F = img.shape[0]
+    z = -1.0 - 2 * torch.rand(1, F, 3, generator=g)
+    feat = torch.rand(1, F, 3, 3, generator=g)
+    return z.cuda(), img[None].contiguous().cuda(), feat.cuda()
+
+
+@pytest.mark.parametrize("kind", ["lattice", "slivers", "huge", "on_vertex"])
+@pytest.mark.parametrize("Hh,Ww", [(64, 64), (48, 80), (33, 21)])
+@pytest.mark.parametrize("multiplier,eps", [(1000., 1e-8), (1., 1e-8), (37.5, 0.), (1000., 1e-3)])
+def test_span_rasterizer_adversarial_vs_ref_C(kal, O, ref_C, kind, Hh, Ww, multiplier, eps):
+    """face_idx bit-exact and features 1e-5 against the reference's kernel where the conservative spans are tightest."""
+    z, img, feat = _adversarial_faces(kind, Hh, Ww, seed=Hh * 100 + Ww)
+    out, idx = kal.render.mesh.rasterize(Hh, Ww, z, img, feat, None, multiplier, eps)
+    r_feat, r_idx, r_w = O.rasterize_forward(Hh, Ww, z, img, feat, None, multiplier, eps, backend=ref_C)
+    assert torch.equal(idx, r_idx), f"face_idx mismatch on {(idx != r_idx).sum().item()} pixels"
+    assert (idx >= 0).any() or kind == "huge"
+    ok = torch.isfinite(r_feat)
+    rel_close(torch.where(ok, out, 0), torch.where(ok, r_feat, 0), 1e-5, "features")
+
+
 # ----------------------------------------------------------------------------- vs the C++ oracle
 @pytest.mark.parametrize("dtype", [torch.float32, torch.float64])
 def test_random_soup_vs_oracle_bit_exact(kal, O, dtype):
