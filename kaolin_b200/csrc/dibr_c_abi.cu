@@ -327,6 +327,10 @@ int soft_mask_impl(const T* img, const T* bbox_in, const int64_t* face_idx, int 
   p.grad_img = grad_img;
   p.log_count = nullptr; p.over_count = nullptr; p.tile_flag = nullptr; p.over_list = nullptr; p.log = nullptr;
   p.log_cap = 0;
+  {
+    static const int sel = [] { const char* e = getenv("DIBR_SOFT_SEL"); return e ? atoi(e) : 0; }();
+    p.sel_first = sel;                 // experiments: candidates taken by a tile's first pass (0 = default)
+  }
   // The pair log is used when it was asked for (forward: keep_pairs; backward: bins_ready == 2), the pixel
   // indices fit 32 bits and the workspace holds it — the same test on both sides, so a forward that had to go
   // without a log is followed by a recompute backward on the same workspace.

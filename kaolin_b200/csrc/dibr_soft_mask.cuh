@@ -56,6 +56,7 @@ struct SoftParams {
   unsigned* over_list;        // [B*tiles] the overflowed tiles (tile_global), in no particular order
   uint4* log;                 // [LOG_SEGMENTS * log_cap] 16-byte records {pixel, face << 3 | type, prob bits (z[, w])}
   unsigned log_cap;           // entries per segment
+  int sel_first;              // candidates taken by the first pass of a tile (0 = default 2 * threads per CTA)
 };
 __device__ __forceinline__ uint4 log_pack(unsigned pix, unsigned fk, float prob) {
   return make_uint4(pix, fk, __float_as_uint(prob), 0u);
@@ -236,6 +237,72 @@ __device__ __forceinline__ int count_candidates(const TileLists& tl, const uint2
   return tot;
 }
 
+// Upper face index `hi` of the next pass: the candidates with lo < id <= hi are about `target` (at most `cap`) of
+// the tile's lowest remaining ids.  One histogram sweep over the tile's lists (256 buckets of 2^shift consecutive
+// ids above lo, shared-memory atomics) instead of a bisection of count_candidates() calls; `count` returns the exact
+// number selected.  Returns lo when the first bucket alone holds more than `cap` candidates (the caller bisects
+// inside (lo, lo + 2^shift], reported through `hi_bucket`).  CTA-wide; `hist` = 256 ints, `scratch` = 9 ints.
+template <int NT>
+__device__ __forceinline__ int select_hi(const TileLists& tl, const uint2* ranges, const int lo, const int nf,
+                                         const int target, const int cap, const int rx0, const int ry0,
+                                         const int rx1, const int ry1, int* hist, int* scratch, int& count,
+                                         int& hi_bucket) {
+  const int span = nf - 1 - lo;                                   // ids lo + 1 .. nf - 1
+  int shift = 0;
+  while (((span - 1) >> shift) > 255) ++shift;
+  for (int k = threadIdx.x; k < 256; k += NT) hist[k] = 0;
+  __syncthreads();
+  for (int k = threadIdx.x; k < tl.n_fine; k += NT) {
+    const int f = tl.fine[k];
+    if (f > lo) atomicAdd(&hist[(f - lo - 1) >> shift], 1);
+  }
+  const int n_filt = tl.n_filtered();
+  for (int k = threadIdx.x; k < n_filt; k += NT) {
+    const int f = tl.filtered_at(k);
+    if (f > lo && range_hits_rect(ranges[f], rx0, ry0, rx1, ry1)) atomicAdd(&hist[(f - lo - 1) >> shift], 1);
+  }
+  __syncthreads();
+  if (threadIdx.x < 32) {                                         // warp 0: inclusive prefix over the 256 buckets
+    const int lane = threadIdx.x;
+    int c[8], sum = 0;
+#pragma unroll
+    for (int q = 0; q < 8; ++q) { c[q] = hist[lane * 8 + q]; sum += c[q]; }
+    int incl = sum;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+      const int v = __shfl_up_sync(0xffffffffu, incl, o);
+      if (lane >= o) incl += v;
+    }
+    int run = incl - sum, n_cap = 0, n_tgt = 0;                    // the prefix is non-decreasing: both are counts
+#pragma unroll                                                     // of a leading run of buckets
+    for (int q = 0; q < 8; ++q) {
+      run += c[q];
+      hist[lane * 8 + q] = run;
+      n_cap += run <= cap ? 1 : 0;
+      n_tgt += run < target ? 1 : 0;
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+      n_cap += __shfl_xor_sync(0xffffffffu, n_cap, o);
+      n_tgt += __shfl_xor_sync(0xffffffffu, n_tgt, o);
+    }
+    __syncwarp();
+    // last bucket taken: the first one that reaches `target`, but never beyond the capacity
+    const int t = min(min(n_cap - 1, n_tgt), 255);
+    if (lane == 0) {
+      scratch[0] = t; scratch[1] = t >= 0 ? hist[t] : 0; scratch[2] = shift;
+    }
+  }
+  __syncthreads();
+  const int t = scratch[0];
+  count = scratch[1];
+  const long long step = 1ll << scratch[2];
+  hi_bucket = (int)min((long long)(nf - 1), (long long)lo + step);
+  __syncthreads();                                                // scratch / hist are reused by the caller
+  if (t < 0) return lo;
+  return (int)min((long long)(nf - 1), (long long)lo + (long long)(t + 1) * step);
+}
+
 // Each thread ranks Q of the ids (k = tid + q*NT); see the call site.
 template <int Q, int NT>
 __device__ __forceinline__ void rank_sort(int* s_ids, const int count) {
@@ -351,11 +418,14 @@ __device__ __forceinline__ void soft_tile(const SoftParams<T>& sp, const FaceLay
   // (config 5) take the selection path below.
   int lo = -1;
   bool first = true;
+  int target = sp.sel_first > 0 ? min(sp.sel_first, CAP) : min(2 * NT, CAP);
   while (true) {
-    // ---- gather the candidates with lo < id <= hi: tile list + filtered large faces
+    // ---- gather the candidates with lo < id <= hi: tile list + filtered large faces.  A pass takes about `target`
+    //      of the lowest remaining ids (the k-lists are the FIRST knum hits in face order, so a pixel is usually
+    //      complete long before the tile's whole list has been looked at); the target doubles from pass to pass.
     int hi = nf - 1;
     int count = 0;
-    bool fits = first && n_tile <= CAP;
+    bool fits = first && n_tile + n_filt <= target;
     if (fits) {
       for (int k = threadIdx.x; k < n_tile; k += NT) s_ids[k] = tile_list[k];
       if (threadIdx.x == 0) scratch[8] = n_tile;
@@ -372,19 +442,20 @@ __device__ __forceinline__ void soft_tile(const SoftParams<T>& sp, const FaceLay
           int pos = 0;
           if (lane == 0) pos = atomicAdd(&scratch[8], __popc(m));
           pos = __shfl_sync(0xffffffffu, pos, 0) + __popc(m & lt_mask);
-          if (f >= 0 && pos < CAP) s_ids[pos] = f;
+          if (f >= 0) s_ids[pos] = f;
         }
       }
       __syncthreads();
       count = scratch[8];
-      if (count > CAP) fits = false;
-    }
-    if (!fits) {
-      // -- selection: largest hi with #{candidates in (lo, hi]} <= SOFT_CAP, by bisection on the face index
-      //    (ids are unique, so a range of one id always fits)
+    } else {
+      // -- selection: histogram over the remaining ids; a bisection on the face index only inside one bucket
+      //    that alone exceeds the capacity (ids are unique, so a range of one id always fits)
       __syncthreads();
-      if (count_candidates<NT>(tl, L.ranges + vbase, lo, hi, rx0, ry0, rx1, ry1, scratch) > CAP) {
-        int good = lo, bad = hi;
+      int hi_bucket;
+      hi = select_hi<NT>(tl, L.ranges + vbase, lo, nf, target, CAP, rx0, ry0, rx1, ry1,
+                         reinterpret_cast<int*>(s_mask), scratch, count, hi_bucket);
+      if (hi == lo) {
+        int good = lo, bad = hi_bucket;
         while (bad - good > 1) {
           const int mid = good + ((bad - good) >> 1);
           if (count_candidates<NT>(tl, L.ranges + vbase, lo, mid, rx0, ry0, rx1, ry1, scratch) <= CAP) good = mid; else bad = mid;
@@ -405,6 +476,7 @@ __device__ __forceinline__ void soft_tile(const SoftParams<T>& sp, const FaceLay
       __syncthreads();
       count = scratch[8];
     }
+    target = min(2 * target, CAP);
     first = false;
     if (count > 0) {
       // ---- sort by face index; order is semantic (first knum faces in face order)
