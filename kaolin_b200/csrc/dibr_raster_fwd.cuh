@@ -505,7 +505,7 @@ inline int raster_threads_default() {
   static const int nt = [] {
     const char* e = getenv("DIBR_RASTER_NT");
     const int v = e ? atoi(e) : 0;
-    return (v == 64 || v == 128 || v == 256) ? v : 128;
+    return (v == 64 || v == 128 || v == 256) ? v : 64;
   }();
   return nt;
 }
