@@ -221,16 +221,26 @@ __global__ void __launch_bounds__(1024) scan_kernel(Geometry geo, BinLists L) {
   __syncthreads();
   for (int t = threadIdx.x; t < geo.tiles_per_view; t += blockDim.x) {
     const int k = tile_weight_bucket(cnt, geo, t);
-    order[bbase[k] + atomicAdd(&hist[k], 1)] = t;
+    order[bbase[k] + atomicAdd(&hist[k], 1)] = (t % geo.tiles_x) | ((t / geo.tiles_x) << 16);   // tx | ty << 16
   }
 }
 
-// blockIdx -> (view, tile) of the per-tile kernels: consecutive CTAs take the same rank in different views, ranks
-// go from the heaviest tile of each view to the lightest.
-__device__ __forceinline__ void scheduled_tile(const BinLists& L, const Geometry& geo, const unsigned block, int& b,
-                                               int& tile) {
-  b = (int)(block % (unsigned)geo.B);
-  tile = L.tile_order[(int64_t)b * geo.tiles_per_view + (block / (unsigned)geo.B)];
+// Grid of the per-tile kernels: x = view, (y, z) = rank of the tile in its view's order — consecutive CTAs take the
+// same rank in different views, ranks go from the heaviest tile of each view to the lightest.  No integer division
+// in the consumers: the order entries are packed tile coordinates.
+constexpr unsigned SCHED_Y = 32768u;
+inline dim3 scheduled_grid(const Geometry& geo) {
+  const unsigned t = (unsigned)geo.tiles_per_view;
+  const unsigned y = t < SCHED_Y ? t : SCHED_Y;
+  return dim3((unsigned)geo.B, y, (t + y - 1) / (y ? y : 1));
+}
+__device__ __forceinline__ bool scheduled_tile(const BinLists& L, const Geometry& geo, int& b, int& tx, int& ty) {
+  const unsigned rank = blockIdx.y + blockIdx.z * gridDim.y;
+  if (rank >= (unsigned)geo.tiles_per_view) return false;
+  b = (int)blockIdx.x;
+  const unsigned e = (unsigned)L.tile_order[(int64_t)b * geo.tiles_per_view + rank];
+  tx = (int)(e & 0xffffu); ty = (int)(e >> 16);
+  return true;
 }
 
 __global__ void __launch_bounds__(256) fill_kernel(FaceLayout fl, Geometry geo, BinLists L) {

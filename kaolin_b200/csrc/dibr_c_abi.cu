@@ -168,7 +168,7 @@ int rasterize_fwd_impl(const T* z, const T* img, const T* bbox_in, const T* cons
   rp.pix_mult = pix_mult; rp.eps = eps; rp.out_feat = fout; rp.out_idx = out_idx; rp.out_w = out_w;
   {
     ProfScope ps(DIBR_KERNEL_RASTER_FWD, s);
-    launch_raster_fwd(rp, fl, geo, L, (unsigned)(B * geo.tiles_per_view), s);
+    launch_raster_fwd(rp, fl, geo, L, s);
   }
   LAUNCH_CHECK("raster_fwd_kernel");
   return DIBR_OK;
@@ -238,7 +238,8 @@ int launch_soft(const SoftParams<T>& p, const FaceLayout& fl, const Geometry& ge
     }
   }
   ProfScope ps(kernel_id, s);
-  soft_mask_kernel<T, MODE, NT><<<grid, NT, smem, s>>>(p, fl, geo, L);
+  (void)grid;
+  soft_mask_kernel<T, MODE, NT><<<scheduled_grid(geo), NT, smem, s>>>(p, fl, geo, L);
   return DIBR_OK;
 }
 

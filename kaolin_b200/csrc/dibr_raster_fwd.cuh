@@ -161,9 +161,8 @@ __global__ void __launch_bounds__(256) raster_fwd_kernel(RasterFwdParams<T> rp, 
                                                          BinLists L) {
   __shared__ StagedFace<T> st;
   __shared__ int scratch[9];
-  int b, tile;
-  scheduled_tile(L, geo, blockIdx.x, b, tile);
-  const int tx = tile % geo.tiles_x, ty = tile / geo.tiles_x;
+  int b, tx, ty;
+  if (!scheduled_tile(L, geo, b, tx, ty)) return;
   const int px = tx * TILE + (threadIdx.x & (TILE - 1));
   const int py = ty * TILE + (threadIdx.x / TILE);
   const bool in_image = px < geo.W && py < geo.H;
@@ -428,9 +427,8 @@ __global__ void __launch_bounds__(NT, DIBR_RASTER_TPS / NT)
 raster_fwd_scatter_kernel(RasterFwdParams<float> rp, FaceLayout fl, Geometry geo, BinLists L) {
   constexpr int NW = NT / 32;
   __shared__ ScatterShared<NW> sh;
-  int b, tile;
-  scheduled_tile(L, geo, blockIdx.x, b, tile);
-  const int tx = tile % geo.tiles_x, ty = tile / geo.tiles_x;
+  int b, tx, ty;
+  if (!scheduled_tile(L, geo, b, tx, ty)) return;
   const int rx0 = tx * TILE, ry0 = ty * TILE;
   const int64_t vbase = fl.base(b);
   const int lane = lane_id(), warp = threadIdx.x >> 5;
@@ -512,15 +510,15 @@ inline int raster_threads_default() {
 
 // dispatch: fp32 -> scatter, fp64 -> gather
 inline void launch_raster_fwd(const RasterFwdParams<float>& rp, const FaceLayout& fl, const Geometry& geo,
-                              const BinLists& L, unsigned grid, cudaStream_t s) {
+                              const BinLists& L, cudaStream_t s) {
   const int nt = raster_threads_default();          // DIBR_RASTER_NT=64|128|256 overrides for experiments
-  if (nt == 64) raster_fwd_scatter_kernel<64><<<grid, 64, 0, s>>>(rp, fl, geo, L);
-  else if (nt == 128) raster_fwd_scatter_kernel<128><<<grid, 128, 0, s>>>(rp, fl, geo, L);
-  else raster_fwd_scatter_kernel<256><<<grid, 256, 0, s>>>(rp, fl, geo, L);
+  if (nt == 64) raster_fwd_scatter_kernel<64><<<scheduled_grid(geo), 64, 0, s>>>(rp, fl, geo, L);
+  else if (nt == 128) raster_fwd_scatter_kernel<128><<<scheduled_grid(geo), 128, 0, s>>>(rp, fl, geo, L);
+  else raster_fwd_scatter_kernel<256><<<scheduled_grid(geo), 256, 0, s>>>(rp, fl, geo, L);
 }
 inline void launch_raster_fwd(const RasterFwdParams<double>& rp, const FaceLayout& fl, const Geometry& geo,
-                              const BinLists& L, unsigned grid, cudaStream_t s) {
-  raster_fwd_kernel<double><<<grid, 256, 0, s>>>(rp, fl, geo, L);
+                              const BinLists& L, cudaStream_t s) {
+  raster_fwd_kernel<double><<<scheduled_grid(geo), 256, 0, s>>>(rp, fl, geo, L);
 }
 
 }  // namespace dibr

@@ -23,6 +23,12 @@
 
 namespace dibr {
 
+#ifndef DIBR_SOFT_TPS
+#define DIBR_SOFT_TPS 1024       // resident threads per SM the fp32 register allocation aims at
+#endif
+#ifndef DIBR_SOFT_CELLS
+#define DIBR_SOFT_CELLS 32       // k-list cells per thread of the CTA
+#endif
 constexpr int SOFT_CAP = 2048;      // candidate faces per tile held in shared memory
 constexpr int MODE_FWD = 0;
 constexpr int MODE_BWD = 1;
@@ -198,7 +204,7 @@ template <typename T, int NT>
 struct SoftSmem {
   static constexpr int NW = NT / 32;
   static constexpr int CAP = (NT >= 256) ? 2048 : 1024;   // candidate faces per pass
-  static constexpr int CELLS_TOT = NT * 32;               // k-list cells: a super-batch is min(NT, CELLS_TOT / knum) pixels
+  static constexpr int CELLS_TOT = NT * DIBR_SOFT_CELLS;               // k-list cells: a super-batch is min(NT, CELLS_TOT / knum) pixels
   static constexpr size_t ids = 0;
   static constexpr size_t mask = ids + (CAP + 8) * sizeof(int);      // + INT_MAX padding of the rank sort
   static constexpr size_t cell = mask + (CAP + 8) * sizeof(unsigned);
@@ -363,7 +369,7 @@ __device__ __forceinline__ unsigned bit_span16(int lo, int hi) { return ((2u << 
 // the persistent overflow kernel below.
 template <typename T, int MODE, int NT>
 __device__ __forceinline__ void soft_tile(const SoftParams<T>& sp, const FaceLayout& fl, const Geometry& geo,
-                                          const BinLists& L, const unsigned tile_global) {
+                                          const BinLists& L, const int b, const int tx, const int ty) {
   typedef typename CellInt<T>::type cell_int;
   typedef SoftSmem<T, NT> SM;
   constexpr int NW = NT / 32, CAP = SM::CAP, CELLS_TOT = SM::CELLS_TOT;
@@ -379,9 +385,7 @@ __device__ __forceinline__ void soft_tile(const SoftParams<T>& sp, const FaceLay
   __shared__ int scratch[10];                                           // [0..7] warp sums, [8] append cursor, [9] U
   __shared__ float s_px[TILE], s_py[TILE];
 
-  const int tile = (int)(tile_global % (unsigned)geo.tiles_per_view);
-  const int b = (int)(tile_global / (unsigned)geo.tiles_per_view);
-  const int tx = tile % geo.tiles_x, ty = tile / geo.tiles_x;
+  const unsigned tile_global = (unsigned)b * (unsigned)geo.tiles_per_view + (unsigned)(ty * geo.tiles_x + tx);
   const int rx0 = tx * TILE, ry0 = ty * TILE, rx1 = rx0 + TILE - 1, ry1 = ry0 + TILE - 1;
   const int64_t vbase = fl.base(b);
   const int K = sp.knum;
@@ -694,21 +698,24 @@ __device__ __forceinline__ void soft_tile(const SoftParams<T>& sp, const FaceLay
 }
 
 template <typename T, int MODE, int NT>
-__global__ void __launch_bounds__(NT, (sizeof(T) == 4 ? 1024 / NT : 512 / NT))
+__global__ void __launch_bounds__(NT, (sizeof(T) == 4 ? DIBR_SOFT_TPS / NT : 512 / NT))
 soft_mask_kernel(SoftParams<T> sp, FaceLayout fl, Geometry geo, BinLists L) {
-  int b, tile;
-  scheduled_tile(L, geo, blockIdx.x, b, tile);
-  soft_tile<T, MODE, NT>(sp, fl, geo, L, (unsigned)b * (unsigned)geo.tiles_per_view + (unsigned)tile);
+  int b, tx, ty;
+  if (!scheduled_tile(L, geo, b, tx, ty)) return;
+  soft_tile<T, MODE, NT>(sp, fl, geo, L, b, tx, ty);
 }
 
 // Backward of the tiles whose pairs did not fit the log: a small persistent grid walks the overflow list
 // (normally empty: the CTAs read one word and exit).
 template <typename T, int NT>
-__global__ void __launch_bounds__(NT, (sizeof(T) == 4 ? 1024 / NT : 512 / NT))
+__global__ void __launch_bounds__(NT, (sizeof(T) == 4 ? DIBR_SOFT_TPS / NT : 512 / NT))
 soft_mask_overflow_kernel(SoftParams<T> sp, FaceLayout fl, Geometry geo, BinLists L) {
   const unsigned n = min(*sp.over_count, (unsigned)(geo.B * geo.tiles_per_view));
   for (unsigned i = blockIdx.x; i < n; i += gridDim.x) {
-    soft_tile<T, MODE_BWD, NT>(sp, fl, geo, L, sp.over_list[i]);
+    const unsigned tg = sp.over_list[i];
+    const int tile = (int)(tg % (unsigned)geo.tiles_per_view);
+    soft_tile<T, MODE_BWD, NT>(sp, fl, geo, L, (int)(tg / (unsigned)geo.tiles_per_view), tile % geo.tiles_x,
+                               tile / geo.tiles_x);
     __syncthreads();
   }
 }
