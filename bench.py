@@ -466,7 +466,7 @@ def gpu_run(args):
                                         "achieved": algo["total"] / (ms * 1e-3) / 1e9,
                                         "frac": algo["total"] / (ms * 1e-3) / 1e9 / peak},
                          "kernel_ms_all": kshare,
-                         "note": "the kernels are instruction-issue bound, not HBM bound (DESIGN.md §5)"},
+                         "note": "the kernels are latency / instruction-issue bound, not HBM bound (DESIGN.md §5)"},
             "clocks": clocks,
         }
         if world == 1 and not args.no_cpu_baseline:
