@@ -537,7 +537,7 @@ __device__ __forceinline__ void soft_tile(const SoftParams<T>& sp, const FaceLay
         const int ly0 = max((int)(r.y & 0xffffu), ry0) - ry0, ly1 = min((int)(r.y >> 16), ry1) - ry0;
         s_mask[k] = (lx0 <= lx1 && ly0 <= ly1) ? (bit_span16(lx0, lx1) | (bit_span16(ly0, ly1) << 16)) : 0u;
       }
-      if (threadIdx.x < 4) s_mask[count + threadIdx.x] = 0u;
+      for (int k = count + threadIdx.x; k < ((count + 31) & ~31); k += NT) s_mask[k] = 0u;   // pad to 32 (>= 4)
       __syncthreads();
 
       // ---- phases B-D over super-batches of NPB uncovered pixels (usually the whole tile at once):
@@ -553,29 +553,53 @@ __device__ __forceinline__ void soft_tile(const SoftParams<T>& sp, const FaceLay
       const int n4 = (count + 3) >> 2;
       for (int sb0 = 0; sb0 < U; sb0 += NPB) {
         const int nsb = min(NPB, U - sb0);
-        // -- B
-        for (int u0 = warp * 32; u0 < nsb; u0 += NT) {
-          const int u = u0 + lane;
-          const bool act = u < nsb;
-          const int t = act ? s_upix[sb0 + u] : 0;
-          const int room = act ? min(K - s_ktot[sb0 + u], KROW) : 0;
-          const unsigned mybit = (1u << (t & 15)) | (0x10000u << (t >> 4));
-          cell_int* row = s_celli + u * KS;
-          int kid = 0;
-          for (int j = 0; j < n4; ++j) {
-            const uint4 m = reinterpret_cast<const uint4*>(s_mask)[j];
-            if ((m.x & mybit) == mybit && kid < room) { row[kid] = (cell_int)(4 * j); ++kid; }
-            if ((m.y & mybit) == mybit && kid < room) { row[kid] = (cell_int)(4 * j + 1); ++kid; }
-            if ((m.z & mybit) == mybit && kid < room) { row[kid] = (cell_int)(4 * j + 2); ++kid; }
-            if ((m.w & mybit) == mybit && kid < room) { row[kid] = (cell_int)(4 * j + 3); ++kid; }
-            if ((j & 7) == 7 && __all_sync(0xffffffffu, kid >= room)) break;
-          }
-          if (act) s_knew[u] = kid;
-        }
-        __syncthreads();
-        // -- C
-        const int PW = (nsb + NW - 1) / NW;              // pixels per warp (<= 32)
+        const int PW = (nsb + NW - 1) / NW;              // pixels per warp (<= 32) in phase C
         const int ubase = warp * PW;
+        // -- B
+        if (PW <= 8) {
+          // few uncovered pixels (the usual case away from silhouettes): every warp builds the k-lists of its OWN
+          // phase-C pixels, lane = candidate — 32 coverage masks per step, hits ranked by ballot / popc — instead of
+          // one warp sweeping all candidates for all pixels while the others wait; no CTA barrier before phase C
+          const int npx = max(0, min(PW, nsb - ubase));
+          for (int i = 0; i < npx; ++i) {                // warp-uniform
+            const int u = ubase + i;
+            const int t = s_upix[sb0 + u];
+            const int room = min(K - s_ktot[sb0 + u], KROW);
+            const unsigned mybit = (1u << (t & 15)) | (0x10000u << (t >> 4));
+            cell_int* row = s_celli + u * KS;
+            int kid = 0;
+            for (int j0 = 0; j0 < count && kid < room; j0 += 32) {
+              const bool hit = (s_mask[j0 + lane] & mybit) == mybit;       // masks are zero-padded to 32
+              const unsigned hm = __ballot_sync(0xffffffffu, hit);
+              const int pos = kid + __popc(hm & lt_mask);
+              if (hit && pos < room) row[pos] = (cell_int)(j0 + lane);
+              kid = min(room, kid + __popc(hm));
+            }
+            if (lane == 0) s_knew[u] = kid;
+          }
+          __syncwarp();
+        } else {
+          for (int u0 = warp * 32; u0 < nsb; u0 += NT) {   // lane = pixel, uint4 broadcast reads of the masks
+            const int u = u0 + lane;
+            const bool act = u < nsb;
+            const int t = act ? s_upix[sb0 + u] : 0;
+            const int room = act ? min(K - s_ktot[sb0 + u], KROW) : 0;
+            const unsigned mybit = (1u << (t & 15)) | (0x10000u << (t >> 4));
+            cell_int* row = s_celli + u * KS;
+            int kid = 0;
+            for (int j = 0; j < n4; ++j) {
+              const uint4 m = reinterpret_cast<const uint4*>(s_mask)[j];
+              if ((m.x & mybit) == mybit && kid < room) { row[kid] = (cell_int)(4 * j); ++kid; }
+              if ((m.y & mybit) == mybit && kid < room) { row[kid] = (cell_int)(4 * j + 1); ++kid; }
+              if ((m.z & mybit) == mybit && kid < room) { row[kid] = (cell_int)(4 * j + 2); ++kid; }
+              if ((m.w & mybit) == mybit && kid < room) { row[kid] = (cell_int)(4 * j + 3); ++kid; }
+              if ((j & 7) == 7 && __all_sync(0xffffffffu, kid >= room)) break;
+            }
+            if (act) s_knew[u] = kid;
+          }
+          __syncthreads();
+        }
+        // -- C
         if (ubase < nsb) {
           const int npix = min(PW, nsb - ubase);
           const bool act = lane < npix;
