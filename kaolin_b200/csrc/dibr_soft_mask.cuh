@@ -26,6 +26,9 @@ namespace dibr {
 #ifndef DIBR_SOFT_TPS
 #define DIBR_SOFT_TPS 1024       // resident threads per SM the fp32 register allocation aims at
 #endif
+#ifndef DIBR_SOFT_PWB
+#define DIBR_SOFT_PWB 16         // per-warp k-list building up to this many uncovered pixels per warp
+#endif
 #ifndef DIBR_SOFT_CELLS
 #define DIBR_SOFT_CELLS 32       // k-list cells per thread of the CTA
 #endif
@@ -556,7 +559,7 @@ __device__ __forceinline__ void soft_tile(const SoftParams<T>& sp, const FaceLay
         const int PW = (nsb + NW - 1) / NW;              // pixels per warp (<= 32) in phase C
         const int ubase = warp * PW;
         // -- B
-        if (PW <= 8) {
+        if (PW <= DIBR_SOFT_PWB) {
           // few uncovered pixels (the usual case away from silhouettes): every warp builds the k-lists of its OWN
           // phase-C pixels, lane = candidate — 32 coverage masks per step, hits ranked by ballot / popc — instead of
           // one warp sweeping all candidates for all pixels while the others wait; no CTA barrier before phase C
