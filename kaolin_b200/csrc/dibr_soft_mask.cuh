@@ -551,8 +551,8 @@ __device__ __forceinline__ void soft_tile(const SoftParams<T>& sp, const FaceLay
       //         flattened (prefix sum of the list lengths; owner by REDUX/ballot/popc) and evaluated one per
       //         lane with full lanes: distance, probability (forward: stored back into the cell; backward:
       //         gradients)
-      //      D  forward, thread = pixel: multiplies the new probabilities, in face order, into the pixel's
-      //         running product (:174-182)
+      //      D  forward, lane = one of the warp's pixels: multiplies the new probabilities, in face order, into the
+      //         pixel's running product (:174-182)
       const int n4 = (count + 3) >> 2;
       for (int sb0 = 0; sb0 < U; sb0 += NPB) {
         const int nsb = min(NPB, U - sb0);
@@ -681,13 +681,14 @@ __device__ __forceinline__ void soft_tile(const SoftParams<T>& sp, const FaceLay
             }
           }
         }
-        __syncthreads();
-        // -- D
-        if ((int)threadIdx.x < nsb) {
-          const int kid = s_knew[threadIdx.x];
+        __syncwarp();
+        // -- D  (lane = one of the warp's own phase-C pixels: the probabilities it reads were written by this warp)
+        if (ubase + lane < nsb && lane < PW) {
+          const int u = ubase + lane;
+          const int kid = s_knew[u];
           if (MODE == MODE_FWD) {
-            const T* row = s_cell + threadIdx.x * KS;
-            T allprob = s_acc[sb0 + threadIdx.x];
+            const T* row = s_cell + u * KS;
+            T allprob = s_acc[sb0 + u];
             if (sizeof(T) == 4 && !sp.prob) {
               // fp32 fused path: the running product (:174-178, float * double rounded to float at every step in
               // the reference) is taken in fp32 — a dependent chain of fp64 conversions / multiplies per hit
@@ -696,9 +697,9 @@ __device__ __forceinline__ void soft_tile(const SoftParams<T>& sp, const FaceLay
             } else {
               for (int k = 0; k < kid; ++k) allprob = (T)((double)allprob * (1.0 - (double)row[k]));
             }
-            s_acc[sb0 + threadIdx.x] = allprob;
+            s_acc[sb0 + u] = allprob;
           }
-          s_ktot[sb0 + threadIdx.x] += kid;
+          s_ktot[sb0 + u] += kid;
         }
         __syncthreads();                                 // cells / s_knew are reused by the next super-batch
       }
