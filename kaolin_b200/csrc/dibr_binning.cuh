@@ -86,14 +86,81 @@ __device__ __forceinline__ void load_face_xy<float>(const float* img, int64_t g,
   }
 }
 
+// Counting (FILL = false: K0) or scattering (FILL = true: K1c) of one face per lane into the tile lists; called by
+// whole warps.  Consecutive faces of a mesh touch the same few tiles, so their atomics hit the same counters
+// (ncu: the enlarged soft-mask boxes of config 3 put ~900 atomics on every counter and fill_kernel waited 150
+// cycles per issued instruction).  When the fine-level faces of the warp lie in one view and the union of their tile
+// rectangles has at most 64 tiles, the warp walks the union: one ballot per tile, ONE atomic per (warp, tile) by
+// lane 0, positions by popc rank (face order inside the warp).  Otherwise (random soups, view boundaries) and for
+// the coarse level every lane issues its own atomics, as before.  `has` = the lane holds a face with a non-empty
+// pixel range; (tx0..tx1, ty0..ty1) its tile rectangle; `local` its index in view `b`.
+template <bool FILL>
+__device__ __forceinline__ void bin_faces_warp(const bool has, const int b, const int local, const int tx0,
+                                               const int tx1, const int ty0, const int ty1, const int64_t g,
+                                               const FaceLayout& fl, const Geometry& geo, const BinLists& L) {
+  const int lane = threadIdx.x & 31;
+  const bool fine = has && (tx1 - tx0 + 1) * (ty1 - ty0 + 1) <= PAIRS_PER_FACE;
+  const unsigned fm = __ballot_sync(0xffffffffu, fine);
+  bool done_fine = false;
+  if (fm != 0u) {
+    const int b0 = __shfl_sync(0xffffffffu, b, __ffs(fm) - 1);
+    const bool same = __all_sync(0xffffffffu, !fine || b == b0);
+    const int ux0 = __reduce_min_sync(0xffffffffu, fine ? tx0 : 0x7fffffff);
+    const int uy0 = __reduce_min_sync(0xffffffffu, fine ? ty0 : 0x7fffffff);
+    const int ux1 = __reduce_max_sync(0xffffffffu, fine ? tx1 : -1);
+    const int uy1 = __reduce_max_sync(0xffffffffu, fine ? ty1 : -1);
+    if (same && (ux1 - ux0 + 1) * (uy1 - uy0 + 1) <= 64) {
+      done_fine = true;
+      int* ctr = (FILL ? L.tile_cursor : L.tile_count) + (int64_t)b0 * geo.slots_per_view;
+      for (int ty = uy0; ty <= uy1; ++ty)
+        for (int tx = ux0; tx <= ux1; ++tx) {
+          const bool hit = fine && tx >= tx0 && tx <= tx1 && ty >= ty0 && ty <= ty1;
+          const unsigned m = __ballot_sync(0xffffffffu, hit);
+          if (m == 0u) continue;
+          int base = 0;
+          if (lane == 0) base = atomicAdd(ctr + ty * geo.tiles_x + tx, __popc(m));
+          if (FILL) {
+            base = __shfl_sync(0xffffffffu, base, 0);
+            if (hit) L.pairs[base + __popc(m & ((1u << lane) - 1u))] = local;
+          }
+        }
+    }
+  }
+  if (!has) return;
+  int* ctr = (FILL ? L.tile_cursor : L.tile_count) + (int64_t)b * geo.slots_per_view;
+  if (fine) {
+    if (done_fine) return;
+    for (int ty = ty0; ty <= ty1; ++ty)
+      for (int tx = tx0; tx <= tx1; ++tx) {
+        const int pos = atomicAdd(ctr + ty * geo.tiles_x + tx, 1);
+        if (FILL) L.pairs[pos] = local;
+      }
+    return;
+  }
+  const int cx0 = tx0 / COARSE, cx1 = tx1 / COARSE, cy0 = ty0 / COARSE, cy1 = ty1 / COARSE;
+  if ((cx1 - cx0 + 1) * (cy1 - cy0 + 1) <= PAIRS_PER_FACE) {
+    ctr += geo.tiles_per_view;
+    for (int cy = cy0; cy <= cy1; ++cy)
+      for (int cx = cx0; cx <= cx1; ++cx) {
+        const int pos = atomicAdd(ctr + cy * geo.coarse_x + cx, 1);
+        if (FILL) L.pairs[pos] = local;
+      }
+  } else if (!FILL) {                                   // per-view large list: written once, by the counting pass
+    const int64_t vb = fl.base(b);
+    const int pos = atomicAdd(L.large_count + b, 1);
+    L.large_list[vb + pos] = (int)(g - vb);
+  }
+}
+
 template <typename T>
 __global__ void __launch_bounds__(256) setup_count_kernel(SetupParams<T> sp, FaceLayout fl, Geometry geo,
                                                           BinLists L) {
   const int64_t g = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-  if (g >= fl.Ntot) return;
+  const bool in_range = g < fl.Ntot;                    // no early exit: the binning below is warp-collective
   uint2 rec = empty_range();
-  const bool is_valid = sp.valid ? (sp.valid[g] != 0) : true;
-  int b = 0;
+  const bool is_valid = in_range && (sp.valid ? (sp.valid[g] != 0) : true);
+  int b = 0, tx0 = 0, tx1 = -1, ty0 = 0, ty1 = -1;
+  bool has = false;
   if (is_valid) {
     T xmin, ymin, xmax, ymax;
     if (sp.bbox_in) {
@@ -118,26 +185,12 @@ __global__ void __launch_bounds__(256) setup_count_kernel(SetupParams<T> sp, Fac
       const int jy0 = geo.H - 1 - ky1, jy1 = geo.H - 1 - ky0;
       rec = pack_range(ix0, ix1, jy0, jy1);
       b = fl.view_of(g);
-      const int tx0 = ix0 / TILE, tx1 = ix1 / TILE, ty0 = jy0 / TILE, ty1 = jy1 / TILE;
-      int* cnt = L.tile_count + (int64_t)b * geo.slots_per_view;
-      if ((tx1 - tx0 + 1) * (ty1 - ty0 + 1) <= PAIRS_PER_FACE) {
-        for (int ty = ty0; ty <= ty1; ++ty)
-          for (int tx = tx0; tx <= tx1; ++tx) atomicAdd(cnt + ty * geo.tiles_x + tx, 1);
-      } else {
-        const int cx0 = tx0 / COARSE, cx1 = tx1 / COARSE, cy0 = ty0 / COARSE, cy1 = ty1 / COARSE;
-        if ((cx1 - cx0 + 1) * (cy1 - cy0 + 1) <= PAIRS_PER_FACE) {
-          cnt += geo.tiles_per_view;
-          for (int cy = cy0; cy <= cy1; ++cy)
-            for (int cx = cx0; cx <= cx1; ++cx) atomicAdd(cnt + cy * geo.coarse_x + cx, 1);
-        } else {
-          const int64_t vb = fl.base(b);
-          const int pos = atomicAdd(L.large_count + b, 1);
-          L.large_list[vb + pos] = (int)(g - vb);
-        }
-      }
+      tx0 = ix0 / TILE; tx1 = ix1 / TILE; ty0 = jy0 / TILE; ty1 = jy1 / TILE;
+      has = true;
     }
   }
-  L.ranges[g] = rec;
+  bin_faces_warp<false>(has, b, has ? (int)(g - fl.base(b)) : 0, tx0, tx1, ty0, ty1, g, fl, geo, L);
+  if (in_range) L.ranges[g] = rec;
 }
 
 // scheduling weight of a tile: its own list + a share of the enclosing coarse cell's list (filtered by the consumer)
@@ -245,30 +298,19 @@ __device__ __forceinline__ bool scheduled_tile(const BinLists& L, const Geometry
 
 __global__ void __launch_bounds__(256) fill_kernel(FaceLayout fl, Geometry geo, BinLists L) {
   const int64_t g = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-  if (g >= fl.Ntot) return;
-  const uint2 r = L.ranges[g];
-  if (range_empty(r)) return;
-  const int tx0 = (int)(r.x & 0xffffu) / TILE, tx1 = (int)(r.x >> 16) / TILE;
-  const int ty0 = (int)(r.y & 0xffffu) / TILE, ty1 = (int)(r.y >> 16) / TILE;
-  const int b = fl.view_of(g);
-  const int local = (int)(g - fl.base(b));
-  int* cur = L.tile_cursor + (int64_t)b * geo.slots_per_view;
-  if ((tx1 - tx0 + 1) * (ty1 - ty0 + 1) <= PAIRS_PER_FACE) {
-    for (int ty = ty0; ty <= ty1; ++ty)
-      for (int tx = tx0; tx <= tx1; ++tx) {
-        const int pos = atomicAdd(cur + ty * geo.tiles_x + tx, 1);
-        L.pairs[pos] = local;
-      }
-    return;
-  }
-  const int cx0 = tx0 / COARSE, cx1 = tx1 / COARSE, cy0 = ty0 / COARSE, cy1 = ty1 / COARSE;
-  if ((cx1 - cx0 + 1) * (cy1 - cy0 + 1) > PAIRS_PER_FACE) return;   // in the large list
-  cur += geo.tiles_per_view;
-  for (int cy = cy0; cy <= cy1; ++cy)
-    for (int cx = cx0; cx <= cx1; ++cx) {
-      const int pos = atomicAdd(cur + cy * geo.coarse_x + cx, 1);
-      L.pairs[pos] = local;
+  bool has = false;
+  int b = 0, local = 0, tx0 = 0, tx1 = -1, ty0 = 0, ty1 = -1;
+  if (g < fl.Ntot) {
+    const uint2 r = L.ranges[g];
+    if (!range_empty(r)) {
+      has = true;
+      tx0 = (int)(r.x & 0xffffu) / TILE; tx1 = (int)(r.x >> 16) / TILE;
+      ty0 = (int)(r.y & 0xffffu) / TILE; ty1 = (int)(r.y >> 16) / TILE;
+      b = fl.view_of(g);
+      local = (int)(g - fl.base(b));
     }
+  }
+  bin_faces_warp<true>(has, b, local, tx0, tx1, ty0, ty1, g, fl, geo, L);
 }
 
 // The candidate sources of one 16x16 tile: the faces binned to the tile itself (all touch it), those binned to
