@@ -94,61 +94,83 @@ __device__ __forceinline__ void load_face_xy<float>(const float* img, int64_t g,
 // lane 0, positions by popc rank (face order inside the warp).  Otherwise (random soups, view boundaries) and for
 // the coarse level every lane issues its own atomics, as before.  `has` = the lane holds a face with a non-empty
 // pixel range; (tx0..tx1, ty0..ty1) its tile rectangle; `local` its index in view `b`.
+// One level (fine tiles or coarse cells) of bin_faces_warp: lanes with `act` hold the cell rectangle (x0..x1, y0..y1)
+// of their face in a grid that is `stride` cells wide, whose counters start at `slot0` of the view's slots.
+template <bool FILL>
+__device__ __forceinline__ void bin_level_warp(const bool act, const int b, const int local, const int x0,
+                                               const int x1, const int y0, const int y1, const int slot0,
+                                               const int stride, const Geometry& geo, const BinLists& L) {
+  const int lane = threadIdx.x & 31;
+  const unsigned am = __ballot_sync(0xffffffffu, act);
+  if (am == 0u) return;
+  int* const ctr0 = (FILL ? L.tile_cursor : L.tile_count) + slot0;
+  const int b0 = __shfl_sync(0xffffffffu, b, __ffs(am) - 1);
+  const bool same = __all_sync(0xffffffffu, !act || b == b0);
+  const int ux0 = __reduce_min_sync(0xffffffffu, act ? x0 : 0x7fffffff);
+  const int uy0 = __reduce_min_sync(0xffffffffu, act ? y0 : 0x7fffffff);
+  const int ux1 = __reduce_max_sync(0xffffffffu, act ? x1 : -1);
+  const int uy1 = __reduce_max_sync(0xffffffffu, act ? y1 : -1);
+  if (same && (ux1 - ux0 + 1) * (uy1 - uy0 + 1) <= 64) {
+    int* ctr = ctr0 + (int64_t)b0 * geo.slots_per_view;
+    for (int y = uy0; y <= uy1; ++y)
+      for (int x = ux0; x <= ux1; ++x) {
+        const bool hit = act && x >= x0 && x <= x1 && y >= y0 && y <= y1;
+        const unsigned m = __ballot_sync(0xffffffffu, hit);
+        if (m == 0u) continue;                             // warp-uniform
+        int base = 0;
+        if (lane == 0) base = atomicAdd(ctr + y * stride + x, __popc(m));
+        if (FILL) {
+          base = __shfl_sync(0xffffffffu, base, 0);
+          if (hit) L.pairs[base + __popc(m & ((1u << lane) - 1u))] = local;
+        }
+      }
+    return;
+  }
+  if (!act) return;
+  int* ctr = ctr0 + (int64_t)b * geo.slots_per_view;
+  for (int y = y0; y <= y1; ++y)
+    for (int x = x0; x <= x1; ++x) {
+      const int pos = atomicAdd(ctr + y * stride + x, 1);
+      if (FILL) L.pairs[pos] = local;
+    }
+}
+
+// Counting (FILL = false: K0) or scattering (FILL = true: K1c) of one face per lane into the lists; called by whole
+// warps.  Consecutive faces of a mesh touch the same few cells, so their atomics hit the same counters (ncu: the
+// enlarged soft-mask boxes of config 3 put ~900 atomics on every tile counter and fill_kernel waited 150 cycles per
+// issued instruction; at config 5 the pole slivers put tens of thousands on a few coarse cells: 9.7 of the step's
+// 18 ms).  At each level, when the warp's faces lie in one view and the union of their cell rectangles has at most
+// 64 cells, the warp walks the union: one ballot per cell, ONE atomic per (warp, cell) by lane 0, positions by popc
+// rank (face order inside the warp).  Otherwise (random soups, view boundaries) every lane issues its own atomics.
+// `has` = the lane holds a face with a non-empty pixel range; (tx0..tx1, ty0..ty1) its tile rectangle; `local` its
+// index in view `b`.
 template <bool FILL>
 __device__ __forceinline__ void bin_faces_warp(const bool has, const int b, const int local, const int tx0,
                                                const int tx1, const int ty0, const int ty1, const int64_t g,
                                                const FaceLayout& fl, const Geometry& geo, const BinLists& L) {
   const int lane = threadIdx.x & 31;
   const bool fine = has && (tx1 - tx0 + 1) * (ty1 - ty0 + 1) <= PAIRS_PER_FACE;
-  const unsigned fm = __ballot_sync(0xffffffffu, fine);
-  bool done_fine = false;
-  if (fm != 0u) {
-    const int b0 = __shfl_sync(0xffffffffu, b, __ffs(fm) - 1);
-    const bool same = __all_sync(0xffffffffu, !fine || b == b0);
-    const int ux0 = __reduce_min_sync(0xffffffffu, fine ? tx0 : 0x7fffffff);
-    const int uy0 = __reduce_min_sync(0xffffffffu, fine ? ty0 : 0x7fffffff);
-    const int ux1 = __reduce_max_sync(0xffffffffu, fine ? tx1 : -1);
-    const int uy1 = __reduce_max_sync(0xffffffffu, fine ? ty1 : -1);
-    if (same && (ux1 - ux0 + 1) * (uy1 - uy0 + 1) <= 64) {
-      done_fine = true;
-      int* ctr = (FILL ? L.tile_cursor : L.tile_count) + (int64_t)b0 * geo.slots_per_view;
-      for (int ty = uy0; ty <= uy1; ++ty)
-        for (int tx = ux0; tx <= ux1; ++tx) {
-          const bool hit = fine && tx >= tx0 && tx <= tx1 && ty >= ty0 && ty <= ty1;
-          const unsigned m = __ballot_sync(0xffffffffu, hit);
-          if (m == 0u) continue;
-          int base = 0;
-          if (lane == 0) base = atomicAdd(ctr + ty * geo.tiles_x + tx, __popc(m));
-          if (FILL) {
-            base = __shfl_sync(0xffffffffu, base, 0);
-            if (hit) L.pairs[base + __popc(m & ((1u << lane) - 1u))] = local;
-          }
-        }
-    }
-  }
-  if (!has) return;
-  int* ctr = (FILL ? L.tile_cursor : L.tile_count) + (int64_t)b * geo.slots_per_view;
-  if (fine) {
-    if (done_fine) return;
-    for (int ty = ty0; ty <= ty1; ++ty)
-      for (int tx = tx0; tx <= tx1; ++tx) {
-        const int pos = atomicAdd(ctr + ty * geo.tiles_x + tx, 1);
-        if (FILL) L.pairs[pos] = local;
-      }
-    return;
-  }
+  bin_level_warp<FILL>(fine, b, local, tx0, tx1, ty0, ty1, 0, geo.tiles_x, geo, L);
   const int cx0 = tx0 / COARSE, cx1 = tx1 / COARSE, cy0 = ty0 / COARSE, cy1 = ty1 / COARSE;
-  if ((cx1 - cx0 + 1) * (cy1 - cy0 + 1) <= PAIRS_PER_FACE) {
-    ctr += geo.tiles_per_view;
-    for (int cy = cy0; cy <= cy1; ++cy)
-      for (int cx = cx0; cx <= cx1; ++cx) {
-        const int pos = atomicAdd(ctr + cy * geo.coarse_x + cx, 1);
-        if (FILL) L.pairs[pos] = local;
+  const bool not_fine = has && !fine;
+  const bool coarse = not_fine && (cx1 - cx0 + 1) * (cy1 - cy0 + 1) <= PAIRS_PER_FACE;
+  if (__any_sync(0xffffffffu, not_fine)) {
+    bin_level_warp<FILL>(coarse, b, local, cx0, cx1, cy0, cy1, geo.tiles_per_view, geo.coarse_x, geo, L);
+    if (!FILL) {                                         // per-view large list: written once, by the counting pass
+      const bool large = not_fine && !coarse;
+      const unsigned lm = __ballot_sync(0xffffffffu, large);
+      if (lm != 0u) {
+        const int b0 = __shfl_sync(0xffffffffu, b, __ffs(lm) - 1);
+        if (__all_sync(0xffffffffu, !large || b == b0)) {  // one reservation for the warp
+          int base = 0;
+          if (lane == 0) base = atomicAdd(L.large_count + b0, __popc(lm));
+          base = __shfl_sync(0xffffffffu, base, 0);
+          if (large) L.large_list[fl.base(b0) + base + __popc(lm & ((1u << lane) - 1u))] = local;
+        } else if (large) {
+          L.large_list[fl.base(b) + atomicAdd(L.large_count + b, 1)] = local;
+        }
       }
-  } else if (!FILL) {                                   // per-view large list: written once, by the counting pass
-    const int64_t vb = fl.base(b);
-    const int pos = atomicAdd(L.large_count + b, 1);
-    L.large_list[vb + pos] = (int)(g - vb);
+    }
   }
 }
 
