@@ -156,6 +156,22 @@ __device__ __forceinline__ void raster_epilogue(const RasterFwdParams<T>& rp, co
   }
 }
 
+// Feature store of one pixel with a compile-time channel count (the scatter kernel's epilogue dispatches on the
+// tensor's C once per tensor, outside its pixel loop: no per-channel loop control or address arithmetic).
+template <typename T, int CC>
+__device__ __forceinline__ void store_features(const T* __restrict__ feat, T* __restrict__ out, const int64_t vbase,
+                                               const int64_t pix, const int best_f, const T w0, const T w1,
+                                               const T w2) {
+  T* o = out + pix * CC;
+  if (best_f >= 0) {
+    const T* f0 = feat + (vbase + best_f) * 3 * CC;
+    interp_block<T, CC>(f0, f0 + CC, f0 + 2 * CC, o, w0, w1, w2);
+  } else {
+#pragma unroll
+    for (int d = 0; d < CC; ++d) o[d] = (T)0;
+  }
+}
+
 template <typename T>
 __global__ void __launch_bounds__(256) raster_fwd_kernel(RasterFwdParams<T> rp, FaceLayout fl, Geometry geo,
                                                          BinLists L) {
@@ -495,7 +511,38 @@ raster_fwd_scatter_kernel(RasterFwdParams<float> rp, FaceLayout fl, Geometry geo
         bary_weights<float>(p[0], p[1], p[2], p[3], p[4], p[5], x0, y0, rp.eps, bw0, bw1, bw2);
       }
     }
-    raster_epilogue<float>(rp, vbase, ((int64_t)b * geo.H + py) * geo.W + px, best_f, bw0, bw1, bw2);
+    const int64_t pix = ((int64_t)b * geo.H + py) * geo.W + px;
+    rp.out_idx[pix] = (int64_t)best_f;
+    if (rp.out_w) {
+      float* w = rp.out_w + pix * 3;
+      w[0] = bw0; w[1] = bw1; w[2] = bw2;
+    }
+    // rasterization_cuda.cu:172-189 per feature tensor; small channel counts take fully unrolled loads / stores
+    for (int ft = 0; ft < rp.feat.n; ++ft) {
+      const int C = rp.feat.ch[ft];
+      const float* feat = rp.feat.ptr[ft];
+      float* out = rp.out_feat.ptr[ft];
+      switch (C) {
+        case 1: store_features<float, 1>(feat, out, vbase, pix, best_f, bw0, bw1, bw2); break;
+        case 2: store_features<float, 2>(feat, out, vbase, pix, best_f, bw0, bw1, bw2); break;
+        case 3: store_features<float, 3>(feat, out, vbase, pix, best_f, bw0, bw1, bw2); break;
+        case 4: store_features<float, 4>(feat, out, vbase, pix, best_f, bw0, bw1, bw2); break;
+        default: {
+          float* o = out + pix * C;
+          if (best_f >= 0) {
+            const float* f0 = feat + (vbase + best_f) * 3 * C;
+            const float* f1 = f0 + C;
+            const float* f2 = f1 + C;
+            int d = 0;
+            for (; d + 4 <= C; d += 4) interp_block<float, 4>(f0 + d, f1 + d, f2 + d, o + d, bw0, bw1, bw2);
+            if (d + 2 <= C) { interp_block<float, 2>(f0 + d, f1 + d, f2 + d, o + d, bw0, bw1, bw2); d += 2; }
+            if (d < C) interp_block<float, 1>(f0 + d, f1 + d, f2 + d, o + d, bw0, bw1, bw2);
+          } else {
+            for (int d = 0; d < C; ++d) o[d] = 0.0f;
+          }
+        }
+      }
+    }
   }
 }
 
