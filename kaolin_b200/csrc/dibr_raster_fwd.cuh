@@ -2,14 +2,14 @@
 //
 // One CTA = one 16x16 pixel tile of one view.  Two formulations share the epilogue:
 //
-//  * fp32 — SCATTER (raster_fwd_scatter_kernel).  The work items are (face, pixel) pairs with the pixel
-//    inside the face's pixel range clipped to the tile.  Each warp takes 32 candidate faces (one per lane,
-//    data in registers), prefix-sums their pair counts and then walks the flattened pair list 32 pairs at
-//    a time: owner lane by REDUX/ballot/popc, face data by shuffle.  Every lane evaluates one pair with the
-//    reference's barycentric arithmetic (cheap exact sign rejection first, the three IEEE divisions only
-//    for pixels that can be inside) and merges (z0, face) into the pixel's 64-bit key in shared memory
-//    with a CAS-max.  Lanes stay full whatever the triangle size; no per-pixel walk over faces the pixel
-//    is not in.
+//  * fp32 — SCATTER (raster_fwd_scatter_kernel), span rasterization.  Each warp takes 32 candidate faces (one per
+//    lane, data in registers).  The work items are the (face, pixel row) pairs of the faces' pixel ranges clipped
+//    to the tile: flattened over the warp (prefix sum, owner lane by REDUX/ballot/popc, face data by shuffle), every
+//    lane derives a CONSERVATIVE column span for its row from the three edge functions (error-bounded margins, see
+//    the comment above HIT_CAP and DESIGN.md section 4.5).  The span's pixels are pushed on a per-warp stack in shared
+//    memory and popped in full batches of 32 for the reference's exact test (three IEEE divisions), depth, and a
+//    CAS-max of (z0, face) into the pixel's 64-bit key.  The cost follows the triangles' area, not their bounding
+//    boxes, and the divisions run with all lanes busy.
 //  * fp64, and fp32 tiles that meet a NaN depth — GATHER (gather_tile): one thread per pixel walks the
 //    staged candidates; reproduces the reference's in-order scan including its NaN behaviour.
 //

@@ -2,16 +2,16 @@
 // dibr_soft_mask_cuda.cu:27-184 and :230-353).
 //
 // One CTA = one 16x16 tile.  Only tiles with at least one uncovered pixel do any work beyond the
-// face_idx read / soft write.  The tile's candidate faces (enlarged-bbox tile list + filtered "large"
-// faces) are gathered into shared memory, bitonic-sorted by face index — the reference keeps the FIRST
-// `knum` faces in face order whose enlarged bbox contains the pixel (:80-171), so order is semantic —
-// and their pixel ranges are staged next to them.  Each uncovered pixel then walks the sorted list.
+// face_idx read / soft write.  The reference keeps the FIRST `knum` faces in face order whose enlarged bbox
+// contains the pixel (:80-171), so order is semantic: the tile's candidate faces (enlarged-bbox tile list +
+// filtered coarse / "large" faces) are taken in passes of increasing face-index ranges — a pass holds the ~2*NT
+// lowest remaining ids, chosen by one histogram sweep (select_hi) — gathered into shared memory, sorted by face
+// index (chunk_rank_sort) and turned into 32-bit coverage masks of the tile's columns and rows.
 //
-// The walk is split in phases so that the expensive part runs with full lanes even when only a few
-// pixels of the tile are uncovered: (A) compact the uncovered pixels; then, warp-locally, each uncovered pixel
-// of a warp's batch (B) gets its k-list by ballot/popc over 32 candidates at a time, appended to the warp's
-// pair queue, (C) the queued (pixel, k) pairs are evaluated one per lane, (D) one lane per pixel
-// multiplies the probabilities in face order.
+// Per pass: (A, once) compact the uncovered pixels; (B) every pixel gets the slots of its next hits, in face
+// order, until it has knum — per warp for its own pixels with lane = candidate and ballot / popc ranks when the
+// tile has few uncovered pixels, lane = pixel sweeps otherwise; (C) the (pixel, k) pairs of a warp's pixels are
+// flattened and evaluated one per lane; (D) one lane per pixel multiplies the probabilities in face order.
 //
 // MODE_FWD writes soft (+ optional k-list side buffers, API-visible through
 // _C.render.mesh.dibr_soft_mask_forward_cuda).  MODE_BWD re-derives the same k-list with the same
@@ -209,7 +209,7 @@ struct SoftSmem {
   static constexpr int CAP = (NT >= 256) ? 2048 : 1024;   // candidate faces per pass
   static constexpr int CELLS_TOT = NT * DIBR_SOFT_CELLS;               // k-list cells: a super-batch is min(NT, CELLS_TOT / knum) pixels
   static constexpr size_t ids = 0;
-  static constexpr size_t mask = ids + (CAP + 8) * sizeof(int);      // + INT_MAX padding of the rank sort
+  static constexpr size_t mask = ids + (CAP + 8) * sizeof(int);      // + padding
   static constexpr size_t cell = mask + (CAP + 8) * sizeof(unsigned);
   static constexpr size_t upix = cell + CELLS_TOT * sizeof(T);
   static constexpr size_t wtab = upix + 256 * sizeof(int);
