@@ -150,9 +150,10 @@ int dibr_rasterize_backward_multi_f64(const double* const* grad_outs, const int6
  *  evaluated (pixel, face, distance type, probability) to a pair log behind the bins (16 bytes per pair, room
  *  for two pairs per pixel; see dibr_soft_mask_bwd_fused, bins_ready == 2).  If the workspace is too small for
  *  the log, or B*H*W >= 2^32, the log is silently not kept and the matching backward recomputes.
- *  fp32 fused variant: the three double divisions per edge of dibr_soft_mask_cuda.cu:126-138 are evaluated as
- *  one double reciprocal and three multiplications (soft mask within a few fp32 ulp of the reference-shaped
- *  entry point, which keeps the exact divisions because its dist_type output is API-visible).
+ *  fp32 fused variant: the double-precision detour of dibr_soft_mask_cuda.cu:126-138 (`#define EPS 1e-7`) is
+ *  taken in fp32 — one approximate reciprocal per edge — and the probability is __expf(-(d * sigmainv / mult^2));
+ *  the soft mask stays within 1e-5 relative of the reference-shaped entry point (tested), which keeps the exact
+ *  arithmetic because its prob / dist_type outputs are API-visible.
  */
 int dibr_soft_mask_fwd_fused_f32(const float* img, const int64_t* face_idx, int B, int F, int H, int W,
                                  float sigmainv, double boxlen, int knum, double multiplier, float* soft,

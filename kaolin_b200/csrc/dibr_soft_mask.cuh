@@ -162,6 +162,27 @@ __device__ __forceinline__ void soft_backward_vec(const T* p, const T x0, const 
   }
 }
 
+// distance + probability of one (pixel, face) pair: the reference's arithmetic, or — fp32, fused path — its fp32 form
+template <typename T>
+__device__ __forceinline__ void soft_pair(const T* p, const T x0, const T y0, const float multiplier,
+                                          const float sigmainv, const bool fused, const float prob_scale, T& d,
+                                          T& prob, int& edgeid) {
+  d = soft_distance<T>(p, x0, y0, multiplier, edgeid);
+  prob = soft_prob<T>(d, sigmainv, multiplier);
+}
+template <>
+__device__ __forceinline__ void soft_pair<float>(const float* p, const float x0, const float y0,
+                                                 const float multiplier, const float sigmainv, const bool fused,
+                                                 const float prob_scale, float& d, float& prob, int& edgeid) {
+  if (fused) {
+    d = soft_distance_f32(p, x0, y0, multiplier, edgeid);
+    prob = soft_prob_f32(d, prob_scale);
+  } else {
+    d = soft_distance<float>(p, x0, y0, multiplier, edgeid);
+    prob = soft_prob<float>(d, sigmainv, multiplier);
+  }
+}
+
 template <typename T, int MODE>
 struct SoftPixel {            // per-pixel running state of the k-list walk
   T x0, y0;
@@ -637,6 +658,7 @@ __device__ __forceinline__ void soft_tile(const SoftParams<T>& sp, const FaceLay
             lbase = __shfl_sync(0xffffffffu, lbase, 0);
           }
           __syncwarp();
+          const float prob_scale = __fdiv_rn(__fdiv_rn(sp.sigmainv, sp.pix_mult), sp.pix_mult);
           for (int q0 = 0; q0 < nq; q0 += 32) {
             const unsigned rel = (unsigned)(start - q0);
             const unsigned bit = (kid > 0 && rel < 32u) ? (1u << rel) : 0u;
@@ -661,9 +683,10 @@ __device__ __forceinline__ void soft_tile(const SoftParams<T>& sp, const FaceLay
             load_face_xy<T>(sp.img, vbase + f, sp.coord_mult, sp.premultiplied, p);
             int edgeid;
             // fp32 without API-visible side buffers: reciprocal form of the per-edge divisions (dibr_common.cuh)
-            const T d = (sizeof(T) == 4 && !sp.prob) ? soft_distance<T, true>(p, x0, y0, sp.pix_mult, edgeid)
-                                                     : soft_distance<T, false>(p, x0, y0, sp.pix_mult, edgeid);
-            const T prob = soft_prob<T>(d, sp.sigmainv, sp.pix_mult);
+            // fp32 without API-visible side buffers: fp32 form of the per-edge divisions and of the exponent
+            // (dibr_common.cuh: soft_distance_f32 / soft_prob_f32)
+            T d, prob;
+            soft_pair<T>(p, x0, y0, sp.pix_mult, sp.sigmainv, !sp.prob, prob_scale, d, prob, edgeid);
             if (MODE == MODE_FWD) {
               s_cell[cell] = prob;
               if (logging && lbase + (unsigned)q < sp.log_cap) {
