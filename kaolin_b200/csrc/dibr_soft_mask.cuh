@@ -121,6 +121,39 @@ __device__ __forceinline__ void soft_backward_pair(const T* p, const T x0, const
   }
 }
 
+// fp32 instantiation: the same formulas in fp32 throughout (the double detour of `EPS 1e-7` costs a double division
+// and a dozen conversions per pair; 1 - prob is exact in fp32 for prob >= 0.5 and the gradients are judged at 1e-4).
+template <>
+__device__ __forceinline__ void soft_backward_pair<float>(const float* p, const float x0, const float y0,
+                                                          const float prob, const int edgeid, const float dLdp,
+                                                          const float allprob, const float sigmainv,
+                                                          const float multiplier, float* gi) {
+  const float dLdz = -sigmainv * dLdp * (1.0f - allprob) * __fdividef(prob, (1.0f - prob) + 1e-7f);
+  if (dLdz == 0.0f) return;
+  const float s = dLdz * __fdividef(1.0f, multiplier);
+  if (edgeid >= 3) {
+    const int v = edgeid - 3;
+    const float x1 = v == 0 ? p[0] : (v == 1 ? p[2] : p[4]), y1 = v == 0 ? p[1] : (v == 1 ? p[3] : p[5]);
+    atomicAdd(gi + 2 * v, s * 2 * (x1 - x0));
+    atomicAdd(gi + 2 * v + 1, s * 2 * (y1 - y0));
+  } else {
+    const int e = edgeid, e2 = edgeid == 2 ? 0 : edgeid + 1;
+    const float x1 = e == 0 ? p[0] : (e == 1 ? p[2] : p[4]), y1 = e == 0 ? p[1] : (e == 1 ? p[3] : p[5]);
+    const float x2 = e2 == 0 ? p[0] : (e2 == 1 ? p[2] : p[4]), y2 = e2 == 0 ? p[1] : (e2 == 1 ? p[3] : p[5]);
+    const float A = y2 - y1, Bc = x1 - x2, Cc = x2 * y1 - x1 * y2;
+    const float up = A * x0 + Bc * y0 + Cc;
+    const float rden = __fdividef(1.0f, (A * A + Bc * Bc) + 1e-7f);
+    const float dissquare = (up * up) * rden;
+    const float dzdA = 2 * (x0 * up - dissquare * A) * rden;
+    const float dzdB = 2 * (y0 * up - dissquare * Bc) * rden;
+    const float dzdC = 2 * up * rden;
+    atomicAdd(gi + 2 * e, s * (dzdB - y2 * dzdC));
+    atomicAdd(gi + 2 * e + 1, s * (x2 * dzdC - dzdA));
+    atomicAdd(gi + 2 * e2, s * (y1 * dzdC - dzdB));
+    atomicAdd(gi + 2 * e2 + 1, s * (dzdA - x1 * dzdC));
+  }
+}
+
 // Same gradient as soft_backward_pair, returned as the six components of the face's (3,2) coordinate gradient
 // (zeros where the pair does not contribute) so that lanes holding the same face can be summed before the atomics.
 template <typename T>
