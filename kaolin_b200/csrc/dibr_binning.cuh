@@ -110,20 +110,43 @@ __device__ __forceinline__ void bin_level_warp(const bool act, const int b, cons
   const int uy0 = __reduce_min_sync(0xffffffffu, act ? y0 : 0x7fffffff);
   const int ux1 = __reduce_max_sync(0xffffffffu, act ? x1 : -1);
   const int uy1 = __reduce_max_sync(0xffffffffu, act ? y1 : -1);
-  if (same && (ux1 - ux0 + 1) * (uy1 - uy0 + 1) <= 64) {
+  const int uw = ux1 - ux0 + 1, ncell = uw * (uy1 - uy0 + 1);
+  if (same && ncell <= 64) {
     int* ctr = ctr0 + (int64_t)b0 * geo.slots_per_view;
-    for (int y = uy0; y <= uy1; ++y)
-      for (int x = ux0; x <= ux1; ++x) {
+    if (!FILL) {
+      for (int y = uy0; y <= uy1; ++y)
+        for (int x = ux0; x <= ux1; ++x) {
+          const unsigned m = __ballot_sync(0xffffffffu, act && x >= x0 && x <= x1 && y >= y0 && y <= y1);
+          if (m != 0u && lane == 0) atomicAdd(ctr + y * stride + x, __popc(m));     // no return value: a RED
+        }
+      return;
+    }
+    // FILL: the reservations return a position.  Lane j makes the reservation of union cells j and j + 32, so that
+    // all of the warp's atomics are in flight together (one round trip instead of one per cell: a small scene's
+    // fill_kernel is nothing but that chain); a second walk hands every face its position — the cell's base from
+    // the lane that reserved it + the face's popc rank.
+    unsigned m_lo = 0u, m_hi = 0u;
+    {
+      int x = ux0, y = uy0;
+      for (int c = 0; c < ncell; ++c) {
+        const unsigned m = __ballot_sync(0xffffffffu, act && x >= x0 && x <= x1 && y >= y0 && y <= y1);
+        if ((c & 31) == lane) { if (c < 32) m_lo = m; else m_hi = m; }
+        if (++x > ux1) { x = ux0; ++y; }
+      }
+    }
+    int base_lo = 0, base_hi = 0;
+    if (m_lo != 0u) base_lo = atomicAdd(ctr + (uy0 + lane / uw) * stride + ux0 + lane % uw, __popc(m_lo));
+    if (m_hi != 0u) base_hi = atomicAdd(ctr + (uy0 + (lane + 32) / uw) * stride + ux0 + (lane + 32) % uw, __popc(m_hi));
+    {
+      int x = ux0, y = uy0;
+      for (int c = 0; c < ncell; ++c) {
         const bool hit = act && x >= x0 && x <= x1 && y >= y0 && y <= y1;
         const unsigned m = __ballot_sync(0xffffffffu, hit);
-        if (m == 0u) continue;                             // warp-uniform
-        int base = 0;
-        if (lane == 0) base = atomicAdd(ctr + y * stride + x, __popc(m));
-        if (FILL) {
-          base = __shfl_sync(0xffffffffu, base, 0);
-          if (hit) L.pairs[base + __popc(m & ((1u << lane) - 1u))] = local;
-        }
+        const int base = __shfl_sync(0xffffffffu, c < 32 ? base_lo : base_hi, c & 31);
+        if (hit) L.pairs[base + __popc(m & ((1u << lane) - 1u))] = local;
+        if (++x > ux1) { x = ux0; ++y; }
       }
+    }
     return;
   }
   if (!act) return;
