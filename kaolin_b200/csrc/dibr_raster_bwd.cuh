@@ -12,6 +12,10 @@
 
 namespace dibr {
 
+#ifndef DIBR_RASTER_BWD_CTAS
+#define DIBR_RASTER_BWD_CTAS 5     // resident 256-thread CTAs per SM the register allocation aims at (48 registers)
+#endif
+
 template <typename T>
 struct RasterBwdParams {
   FeatSet<const T> grad_out;   // n tensors (B,H,W,C_t)
@@ -58,8 +62,82 @@ __device__ __forceinline__ T group_sum(T v, const int* src, unsigned active_step
   return v;
 }
 
+// group_sum with a compile-time number of steps (steps 0..NS-1; a step no group needs adds nothing)
+template <typename T, int NS>
+__device__ __forceinline__ T group_sum_n(T v, const int* src) {
+  const int lane = threadIdx.x & 31;
+#pragma unroll
+  for (int s = 0; s < NS; ++s) {
+    const T o = __shfl_sync(0xffffffffu, v, src[s]);
+    if (src[s] != lane) v += o;
+  }
+  return v;
+}
+
+// CC channels (d .. d+CC-1 of a tensor with C channels) of one pixel: loads batched, :273-285 feature gradients
+// aggregated per face inside the warp, contributions to the coordinate gradient folded into acc1 / acc2.
+template <typename T, int NS, int CC>
+__device__ __forceinline__ void raster_bwd_block(const T* __restrict__ g, const T* __restrict__ ff, T* gf, const int C,
+                                                 const bool covered, const bool leader, const T w0, const T w1,
+                                                 const T w2, const int* src, T& acc1, T& acc2) {
+  T gd[CC], c0[CC], c1[CC], c2[CC];
+#pragma unroll
+  for (int d = 0; d < CC; ++d) {
+    gd[d] = 0; c0[d] = 0; c1[d] = 0; c2[d] = 0;
+    if (covered) { gd[d] = g[d]; c0[d] = ff[d]; c1[d] = ff[C + d]; c2[d] = ff[2 * C + d]; }
+  }
+#pragma unroll
+  for (int d = 0; d < CC; ++d) {
+    // :382-389: dL/dI_d * ((c1-c0) * dw1[k] + (c2-c0) * dw2[k]) summed over the channels = acc1 * dw1[k] +
+    // acc2 * dw2[k]: the six products are taken once per pixel, after the channel loop
+    acc1 += gd[d] * (c1[d] - c0[d]);
+    acc2 += gd[d] * (c2[d] - c0[d]);
+    const T s0 = group_sum_n<T, NS>(gd[d] * w0, src);
+    const T s1 = group_sum_n<T, NS>(gd[d] * w1, src);
+    const T s2 = group_sum_n<T, NS>(gd[d] * w2, src);
+    if (leader) {
+      atomicAdd(gf + d, s0);
+      atomicAdd(gf + C + d, s1);
+      atomicAdd(gf + 2 * C + d, s2);
+    }
+  }
+}
+
+// Everything after the per-pixel derivatives, for a warp whose largest group needs NS reduction steps.
+template <typename T, int NS>
+__device__ __forceinline__ void raster_bwd_tail(const RasterBwdParams<T>& bp, const int64_t pix, const int64_t tf,
+                                                const bool covered, const bool leader, const T w0, const T w1,
+                                                const T w2, const int* src, const T k3, const T* dw1,
+                                                const T* dw2) {
+  T acc1 = 0, acc2 = 0;
+  for (int ft = 0; ft < bp.feat.n; ++ft) {
+    const int C = bp.feat.ch[ft];                      // warp-uniform
+    const T* g = bp.grad_out.ptr[ft] + pix * C;
+    const T* ff = bp.feat.ptr[ft] + tf * 3 * C;
+    T* gf = bp.grad_feat.ptr[ft] + tf * 3 * C;
+    int d = 0;
+    for (; d + 4 <= C; d += 4)
+      raster_bwd_block<T, NS, 4>(g + d, ff + d, gf + d, C, covered, leader, w0, w1, w2, src, acc1, acc2);
+    if (d + 2 <= C) {
+      raster_bwd_block<T, NS, 2>(g + d, ff + d, gf + d, C, covered, leader, w0, w1, w2, src, acc1, acc2);
+      d += 2;
+    }
+    if (d < C) raster_bwd_block<T, NS, 1>(g + d, ff + d, gf + d, C, covered, leader, w0, w1, w2, src, acc1, acc2);
+  }
+  const T inv_k3sq = (T)1 / (k3 * k3);               // one reciprocal instead of a division per channel (:389;
+                                                     // gradients are judged at 1e-4 relative)
+  acc1 *= inv_k3sq; acc2 *= inv_k3sq;
+  T* gi = bp.grad_img + tf * 6;
+#pragma unroll
+  for (int k = 0; k < 6; ++k) {
+    const T gk = covered ? acc1 * dw1[k] + acc2 * dw2[k] : (T)0;   // dw1 / dw2 are only defined on covered lanes
+    const T sk = group_sum_n<T, NS>(gk, src);
+    if (leader) atomicAdd(gi + k, sk);               // :391-398
+  }
+}
+
 template <typename T>
-__global__ void __launch_bounds__(256) raster_bwd_kernel(RasterBwdParams<T> bp, Geometry geo) {
+__global__ void __launch_bounds__(256, DIBR_RASTER_BWD_CTAS) raster_bwd_kernel(RasterBwdParams<T> bp, Geometry geo) {
   const int tile = blockIdx.x % geo.tiles_per_view;
   const int b = blockIdx.x / geo.tiles_per_view;
   const int tx = tile % geo.tiles_x, ty = tile / geo.tiles_x;
@@ -86,8 +164,6 @@ __global__ void __launch_bounds__(256) raster_bwd_kernel(RasterBwdParams<T> bp, 
   const bool leader = covered && ((peers & ((1u << (threadIdx.x & 31)) - 1u)) == 0u);
 
   T w0 = 0, w1 = 0, w2 = 0;
-  T gv[6] = {0, 0, 0, 0, 0, 0};
-  T acc1 = 0, acc2 = 0;
   const int64_t tf = (int64_t)b * bp.F + (covered ? f : 0);
   T k3 = 1, dw1[6], dw2[6];
   if (covered) {
@@ -121,45 +197,11 @@ __global__ void __launch_bounds__(256) raster_bwd_kernel(RasterBwdParams<T> bp, 
     dw2[0] = -(dw2dm + dw2dn + dw2ds); dw2[1] = -(dw2dp + dw2dq + dw2dt);
     dw2[2] = dw2dm; dw2[3] = dw2dp; dw2[4] = dw2dn; dw2[5] = dw2dq;
   }
-  const T inv_k3sq = (T)1 / (k3 * k3);               // one reciprocal instead of a division per channel (:389;
-                                                     // gradients are judged at 1e-4 relative)
-  for (int ft = 0; ft < bp.feat.n; ++ft) {
-  const int C = bp.feat.ch[ft];
-  const T* g = bp.grad_out.ptr[ft] + pix * C;
-  const T* ff = bp.feat.ptr[ft] + tf * 3 * C;
-  T* gf = bp.grad_feat.ptr[ft] + tf * 3 * C;
-  for (int d = 0; d < C; ++d) {                     // C is warp-uniform
-    T gd = 0;
-    if (covered) {
-      gd = g[d];
-      const T c0 = ff[d], c1 = ff[C + d], c2 = ff[2 * C + d];
-      // :382-389: dL/dI_d * ((c1-c0) * dw1[k] + (c2-c0) * dw2[k]) summed over the channels = acc1 * dw1[k] +
-      // acc2 * dw2[k]: the six products are taken once per pixel, after the channel loop
-      acc1 += gd * (c1 - c0);
-      acc2 += gd * (c2 - c0);
-    }
-    // :273-285 feature gradients, aggregated per face inside the warp
-    const T s0 = group_sum<T>(gd * w0, src, steps);
-    const T s1 = group_sum<T>(gd * w1, src, steps);
-    const T s2 = group_sum<T>(gd * w2, src, steps);
-    if (leader) {
-      atomicAdd(gf + d, s0);
-      atomicAdd(gf + C + d, s1);
-      atomicAdd(gf + 2 * C + d, s2);
-    }
-  }
-  }
-  T* gi = bp.grad_img + tf * 6;
-  acc1 *= inv_k3sq; acc2 *= inv_k3sq;
-  if (covered) {                                       // dw1 / dw2 are only defined on covered lanes
-#pragma unroll
-    for (int k = 0; k < 6; ++k) gv[k] = acc1 * dw1[k] + acc2 * dw2[k];
-  }
-#pragma unroll
-  for (int k = 0; k < 6; ++k) {
-    const T sk = group_sum<T>(gv[k], src, steps);
-    if (leader) atomicAdd(gi + k, sk);               // :391-398
-  }
+  // the reduction depth of the warp's largest group, dispatched once: no per-step branches in the channel loops
+  const int ns = 32 - __clz(steps);
+  if (ns <= 3) raster_bwd_tail<T, 3>(bp, pix, tf, covered, leader, w0, w1, w2, src, k3, dw1, dw2);
+  else if (ns == 4) raster_bwd_tail<T, 4>(bp, pix, tf, covered, leader, w0, w1, w2, src, k3, dw1, dw2);
+  else raster_bwd_tail<T, 5>(bp, pix, tf, covered, leader, w0, w1, w2, src, k3, dw1, dw2);
 }
 
 }  // namespace dibr
