@@ -47,7 +47,7 @@ struct FaceLayout {   // batched (B,F) layout or packed layout with first_idx (B
   int B;
   __device__ __forceinline__ int64_t base(int b) const { return first_idx ? first_idx[b] : (int64_t)b * F; }
   __device__ __forceinline__ int view_of(int64_t g) const {
-    if (!first_idx) return (int)(g / F);
+    if (!first_idx) return (int)((unsigned)g / (unsigned)F);     // Ntot < 2^31 (check_dims): 32-bit division
     int lo = 0, hi = B;                // largest b with first_idx[b] <= g
     while (hi - lo > 1) {
       const int mid = (lo + hi) >> 1;
