@@ -221,7 +221,7 @@ inline int soft_threads_default() {
 }
 
 template <typename T, int MODE, int NT>
-int launch_soft(const SoftParams<T>& p, const FaceLayout& fl, const Geometry& geo, const BinLists& L, unsigned grid,
+int launch_soft(const SoftParams<T>& p, const FaceLayout& fl, const Geometry& geo, const BinLists& L,
                 int kernel_id, cudaStream_t s) {
   const size_t smem = SoftSmem<T, NT>::total;
   {
@@ -238,7 +238,6 @@ int launch_soft(const SoftParams<T>& p, const FaceLayout& fl, const Geometry& ge
     }
   }
   ProfScope ps(kernel_id, s);
-  (void)grid;
   soft_mask_kernel<T, MODE, NT><<<scheduled_grid(geo), NT, smem, s>>>(p, fl, geo, L);
   return DIBR_OK;
 }
@@ -368,11 +367,11 @@ int soft_mask_impl(const T* img, const T* bbox_in, const int64_t* face_idx, int 
     if (sizeof(T) == 4) { if (int e = launch_soft_overflow<T, 128>(p, fl, geo, L, grid, s)) return e; }
     else { if (int e = launch_soft_overflow<T, 256>(p, fl, geo, L, grid, s)) return e; }
   } else if (sizeof(T) == 4 && nt == 64) {
-    if (int e = launch_soft<T, MODE, 64>(p, fl, geo, L, grid, kid, s)) return e;
+    if (int e = launch_soft<T, MODE, 64>(p, fl, geo, L, kid, s)) return e;
   } else if (sizeof(T) == 4 && nt == 128) {
-    if (int e = launch_soft<T, MODE, 128>(p, fl, geo, L, grid, kid, s)) return e;
+    if (int e = launch_soft<T, MODE, 128>(p, fl, geo, L, kid, s)) return e;
   } else {
-    if (int e = launch_soft<T, MODE, 256>(p, fl, geo, L, grid, kid, s)) return e;
+    if (int e = launch_soft<T, MODE, 256>(p, fl, geo, L, kid, s)) return e;
   }
   LAUNCH_CHECK("soft_mask_kernel");
   return DIBR_OK;
