@@ -67,10 +67,12 @@ struct SoftParams {
   unsigned log_cap;           // entries per segment
   int sel_first;              // candidates taken by the first pass of a tile (0 = default 2 * threads per CTA)
 };
-__device__ __forceinline__ uint4 log_pack(unsigned pix, unsigned fk, float prob) {
-  return make_uint4(pix, fk, __float_as_uint(prob), 0u);
+// fp32 records carry the pixel's column | row << 16 in their fourth word (H, W <= 32768), which saves the
+// backward two integer divisions per pair; fp64 records need that word for the probability.
+__device__ __forceinline__ uint4 log_pack(unsigned pix, unsigned fk, float prob, unsigned pxpy) {
+  return make_uint4(pix, fk, __float_as_uint(prob), pxpy);
 }
-__device__ __forceinline__ uint4 log_pack(unsigned pix, unsigned fk, double prob) {
+__device__ __forceinline__ uint4 log_pack(unsigned pix, unsigned fk, double prob, unsigned) {
   const unsigned long long u = (unsigned long long)__double_as_longlong(prob);
   return make_uint4(pix, fk, (unsigned)(u & 0xffffffffull), (unsigned)(u >> 32));
 }
@@ -725,7 +727,8 @@ __device__ __forceinline__ void soft_tile(const SoftParams<T>& sp, const FaceLay
               if (logging && lbase + (unsigned)q < sp.log_cap) {
                 const size_t o = (size_t)seg * sp.log_cap + lbase + (unsigned)q;
                 sp.log[o] = log_pack((unsigned)(((int64_t)b * geo.H + ry0 + ly) * geo.W + rx0 + lx),
-                                     ((unsigned)f << 3) | (unsigned)edgeid, prob);
+                                     ((unsigned)f << 3) | (unsigned)edgeid, prob,
+                                     (unsigned)(rx0 + lx) | ((unsigned)(ry0 + ly) << 16));
               }
               if (sp.prob) {
                 const int64_t o = (((int64_t)b * geo.H + ry0 + ly) * geo.W + rx0 + lx) * K + pk0 + k;
@@ -815,15 +818,27 @@ struct LogItem {
   uint4 rec; T g, soft; unsigned flag, b, px, py; T p[6]; int64_t gf;
 };
 template <typename T>
+__device__ __forceinline__ void log_pixel_coords(const uint4& rec, const Geometry& geo, const unsigned hw, unsigned& b,
+                                                 unsigned& px, unsigned& py) {
+  b = rec.x / hw;
+  const unsigned rem = rec.x - b * hw;
+  py = rem / (unsigned)geo.W; px = rem - py * (unsigned)geo.W;
+}
+template <>
+__device__ __forceinline__ void log_pixel_coords<float>(const uint4& rec, const Geometry&, const unsigned hw,
+                                                        unsigned& b, unsigned& px, unsigned& py) {
+  b = rec.x / hw;
+  px = rec.w & 0xffffu; py = rec.w >> 16;
+}
+// `any_over`: some tile overflowed the log (normally none: the per-pair flag gather is skipped)
+template <typename T>
 __device__ __forceinline__ void log_fetch_pixel(const SoftParams<T>& sp, const Geometry& geo, const unsigned hw,
-                                                LogItem<T>& it) {
+                                                const bool any_over, LogItem<T>& it) {
   const unsigned pix = it.rec.x;
-  it.b = pix / hw;
-  const unsigned rem = pix - it.b * hw;
-  it.py = rem / (unsigned)geo.W; it.px = rem - it.py * (unsigned)geo.W;
+  log_pixel_coords<T>(it.rec, geo, hw, it.b, it.px, it.py);
   it.g = sp.grad_soft[pix];
   it.soft = sp.soft_in[pix];
-  it.flag = sp.tile_flag[it.b * geo.tiles_per_view + (it.py / TILE) * geo.tiles_x + it.px / TILE];
+  it.flag = any_over ? sp.tile_flag[it.b * geo.tiles_per_view + (it.py / TILE) * geo.tiles_x + it.px / TILE] : 0u;
 }
 template <typename T>
 __device__ __forceinline__ void log_fetch_face(const SoftParams<T>& sp, const FaceLayout& fl, LogItem<T>& it) {
@@ -836,6 +851,7 @@ __global__ void __launch_bounds__(256) soft_mask_bwd_log_kernel(SoftParams<T> sp
   const unsigned seg = blockIdx.y;
   const unsigned n = min(sp.log_count[seg], sp.log_cap);
   const unsigned hw = (unsigned)geo.H * (unsigned)geo.W;
+  const bool any_over = *sp.over_count != 0u;
   const float sx = pix_scale(sp.pix_mult, geo.W), sy = pix_scale(sp.pix_mult, geo.H);
   const int lane = threadIdx.x & 31;
   const uint4* log = sp.log + (size_t)seg * sp.log_cap;
@@ -847,8 +863,8 @@ __global__ void __launch_bounds__(256) soft_mask_bwd_log_kernel(SoftParams<T> sp
       LogItem<T> a, c;
       a.rec = log[i];
       c.rec = log[two ? j : i];
-      log_fetch_pixel<T>(sp, geo, hw, a);
-      log_fetch_pixel<T>(sp, geo, hw, c);
+      log_fetch_pixel<T>(sp, geo, hw, any_over, a);
+      log_fetch_pixel<T>(sp, geo, hw, any_over, c);
       log_fetch_face<T>(sp, fl, a);
       log_fetch_face<T>(sp, fl, c);
       if (a.g != (T)0 && !a.flag) {
@@ -873,7 +889,7 @@ __global__ void __launch_bounds__(256) soft_mask_bwd_log_kernel(SoftParams<T> sp
     if (i < n) {
       LogItem<T> a;
       a.rec = log[i];
-      log_fetch_pixel<T>(sp, geo, hw, a);
+      log_fetch_pixel<T>(sp, geo, hw, any_over, a);
       if (a.g != (T)0 && !a.flag) {
         log_fetch_face<T>(sp, fl, a);
         const T x0 = (T)pix_coord(sx, geo.W, (int)a.px), y0 = (T)pix_coord(sy, geo.H, geo.H - 1 - (int)a.py);
