@@ -30,6 +30,21 @@
  *     reference's error behaviour (c10::Error -> RuntimeError).
  *   - face_idx semantics are the reference's: int64, index of the face inside its mesh, -1 = none;
  *     ties in depth go to the lowest face index (rasterization_cuda.cu:162-169).
+ *
+ * Process-wide state (all of it; none affects results)
+ *   - two diagnostic counters / hooks: dibr_kernel_launch_count() and dibr_profile_next_launch()
+ *     (measurement only, off by default);
+ *   - once-per-device cudaFuncSetAttribute calls for the kernels that use > 48 KB of shared memory (made on the
+ *     first call per device, so that later calls are CUDA-graph capturable).
+ *
+ * Tuning switches (kernel experiments; results are identical, see tests/test_gpu_vs_reference.py::
+ * test_kernel_variants_give_identical_results).  They are read from the environment ONCE per process and ONLY
+ * when DIBR_B200_TUNING=1 is set — without that single switch the library never looks at its environment:
+ *     DIBR_RASTER_NT    = 64 | 128 | 256   threads per 16x16 tile of the rasterizer forward kernel (default 64)
+ *     DIBR_SOFT_NT      = 64 | 128 | 256   threads per tile of the soft-mask kernels (default 128)
+ *     DIBR_SOFT_SEL     = n                candidates taken by the first selection pass of a soft-mask tile
+ *     DIBR_SOFT_LOG_CAP = n                entries of the soft-mask pair log (default 2 per pixel + 65536); a small
+ *                                          value forces the overflow (recompute) path — used by the tests
  */
 #ifndef DIBR_B200_H_
 #define DIBR_B200_H_
@@ -41,7 +56,7 @@
 extern "C" {
 #endif
 
-#define DIBR_ABI_VERSION 6
+#define DIBR_ABI_VERSION 7
 
 enum {
   DIBR_OK = 0,
@@ -221,7 +236,10 @@ int dibr_soft_mask_bwd_fused_f64(const double* grad_soft, const double* soft, co
  *  camera_proj (3); exactly one of {rot (B,3,3) + trans (B,3)} or {transform (B,4,3)} non-NULL.
  *  Outputs: face_vertices_camera (B,F,3,3), face_vertices_image (B,F,3,2), face_normals (B,F,3).
  *  _bwd: any of the three upstream gradients may be NULL (= zeros); grad_vertices (Bv,V,3) is zero-filled
- *  and accumulated by the library (summed over views when Bv == 1).  Camera tensors get no gradient.
+ *  and accumulated by the library (summed over views when Bv == 1).  grad_camera_proj (3), grad_rot (B,3,3),
+ *  grad_trans (B,3), grad_transform (B,4,3): optional gradients of the camera tensors (NULL = not wanted; only
+ *  those of the camera form in use may be non-NULL; zero-filled and accumulated by the library) — the reference
+ *  is pure torch and differentiates through all of them.  grad_vertices may be NULL when a camera gradient is asked.
  *  Floating point: agrees with the reference within 1e-5 relative (fp32) — its matmul has no fixed order.
  */
 int dibr_prepare_vertices_fwd_f32(const float* vertices, const int64_t* faces, const float* camera_proj,
@@ -235,12 +253,14 @@ int dibr_prepare_vertices_fwd_f64(const double* vertices, const int64_t* faces, 
 int dibr_prepare_vertices_bwd_f32(const float* grad_camera, const float* grad_image, const float* grad_normals,
                                   const float* vertices, const int64_t* faces, const float* camera_proj,
                                   const float* rot, const float* trans, const float* transform,
-                                  int B, int Bv, int V, int F, float* grad_vertices, void* stream);
+                                  int B, int Bv, int V, int F, float* grad_vertices, float* grad_camera_proj,
+                                  float* grad_rot, float* grad_trans, float* grad_transform, void* stream);
 int dibr_prepare_vertices_bwd_f64(const double* grad_camera, const double* grad_image,
                                   const double* grad_normals, const double* vertices, const int64_t* faces,
                                   const double* camera_proj, const double* rot, const double* trans,
                                   const double* transform, int B, int Bv, int V, int F,
-                                  double* grad_vertices, void* stream);
+                                  double* grad_vertices, double* grad_camera_proj, double* grad_rot,
+                                  double* grad_trans, double* grad_transform, void* stream);
 
 /* ---------------------------------------------------------------------------------------------
  * texture_mapping — the consumer of the rasterizer's interpolated uv map.

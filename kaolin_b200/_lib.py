@@ -42,7 +42,8 @@ _TYPED = {
     "dibr_soft_mask_backward": [c_p, c_p, c_p, c_p, c_p, c_p, c_p, c_i, c_i, c_i, c_i, c_i, c_f, c_f, c_p, c_p],
     "dibr_soft_mask_bwd_fused": [c_p, c_p, c_p, c_p, c_i, c_i, c_i, c_i, c_f, c_d, c_i, c_d, c_p, c_p, c_sz, c_i, c_p],
     "dibr_prepare_vertices_fwd": [c_p, c_p, c_p, c_p, c_p, c_p, c_i, c_i, c_i, c_i, c_p, c_p, c_p, c_p],
-    "dibr_prepare_vertices_bwd": [c_p, c_p, c_p, c_p, c_p, c_p, c_p, c_p, c_p, c_i, c_i, c_i, c_i, c_p, c_p],
+    "dibr_prepare_vertices_bwd": [c_p, c_p, c_p, c_p, c_p, c_p, c_p, c_p, c_p, c_i, c_i, c_i, c_i, c_p, c_p, c_p, c_p,
+                                  c_p, c_p],
     "dibr_texture_mapping_fwd": [c_p, c_p, c_p, c_i, c_i64, c_i, c_i, c_i, c_i, c_i, c_p, c_p],
     "dibr_texture_mapping_bwd": [c_p, c_p, c_p, c_p, c_i, c_i64, c_i, c_i, c_i, c_i, c_i, c_p, c_p, c_p, c_p],
     "dibr_mask_iou_fwd": [c_p, c_p, c_i, c_i64, c_p, c_p, c_p, c_sz, c_p],
@@ -115,7 +116,7 @@ def load():
                 fn = getattr(lib, f"{name}_{suf}")
                 fn.restype = c_i
                 fn.argtypes = argtypes
-        if lib.dibr_abi_version() != 6:
+        if lib.dibr_abi_version() != 7:
             raise RuntimeError("kaolin_b200: libdibr_b200.so ABI version mismatch")
         _lib = lib
     return _lib

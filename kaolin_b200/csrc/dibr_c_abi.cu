@@ -60,6 +60,13 @@ struct ProfScope {
 
 inline size_t align_up(size_t v, size_t a = 256) { return (v + a - 1) / a * a; }
 
+// Kernel-tuning knobs (include/dibr_b200.h, "Tuning switches"): read once per process, and only when the single
+// documented switch DIBR_B200_TUNING=1 is set — a plain process never changes behaviour through its environment.
+inline const char* tuning_env(const char* name) {
+  static const bool on = [] { const char* e = getenv("DIBR_B200_TUNING"); return e && e[0] == '1' && e[1] == 0; }();
+  return on ? getenv(name) : nullptr;
+}
+
 // Workspace carving: two BinLists (index 0 = rasterizer, 1 = soft mask) — each entry point uses one.
 struct WsLayout {
   size_t ranges, tile_count, tile_offset, tile_cursor, pairs, large_list, large_count, alloc_cursor, tile_order;
@@ -213,7 +220,7 @@ int rasterize_bwd_impl(const T* const* grad_outs, const int64_t* face_idx, const
 
 inline int soft_threads_default() {
   static const int nt = [] {
-    const char* e = getenv("DIBR_SOFT_NT");
+    const char* e = tuning_env("DIBR_SOFT_NT");
     const int v = e ? atoi(e) : 0;
     return (v == 64 || v == 128 || v == 256) ? v : 128;
   }();
@@ -271,7 +278,7 @@ LogLayout log_layout(const Geometry& geo, size_t bins_total, size_t elem) {
   l.ok = P > 0 && P < ((int64_t)1 << 32);                 // pixel indices are logged as u32
   int64_t cap = 2 * P + 65536;                            // measured: 0.5 - 1.3 pairs per pixel on configs 1-5
   static const long long forced = [] {                    // DIBR_SOFT_LOG_CAP=<entries>: tests of the overflow path
-    const char* e = getenv("DIBR_SOFT_LOG_CAP");
+    const char* e = tuning_env("DIBR_SOFT_LOG_CAP");
     return e ? atoll(e) : 0ll;
   }();
   if (forced > 0) cap = forced;
@@ -328,7 +335,7 @@ int soft_mask_impl(const T* img, const T* bbox_in, const int64_t* face_idx, int 
   p.log_count = nullptr; p.over_count = nullptr; p.tile_flag = nullptr; p.over_list = nullptr; p.log = nullptr;
   p.log_cap = 0;
   {
-    static const int sel = [] { const char* e = getenv("DIBR_SOFT_SEL"); return e ? atoi(e) : 0; }();
+    static const int sel = [] { const char* e = tuning_env("DIBR_SOFT_SEL"); return e ? atoi(e) : 0; }();
     p.sel_first = sel;                 // experiments: candidates taken by a tile's first pass (0 = default)
   }
   // The pair log is used when it was asked for (forward: keep_pairs; backward: bins_ready == 2), the pixel
@@ -350,11 +357,7 @@ int soft_mask_impl(const T* img, const T* bbox_in, const int64_t* face_idx, int 
     if (MODE == MODE_FWD) {              // counts and flags are contiguous: one memset
       CUDA_TRY(cudaMemsetAsync(base + ll.counts, 0, ll.over - ll.counts, s));
     } else if (nf > 0) {                 // the logged pairs first, then the (normally idle) recompute kernel
-      // DIBR_SOFT_LOG_AGG=1: sum lanes holding the same face with shuffles before the atomics (measured slower:
-      // c2 0.121 vs 0.108 ms, c3 0.175 vs 0.154 ms — the kernel is not bound by the atomics)
-      static const bool agg = [] { const char* e = getenv("DIBR_SOFT_LOG_AGG"); return e ? atoi(e) != 0 : false; }();
-      if (agg) soft_mask_bwd_log_kernel<T, true><<<dim3(LOG_CTAS_PER_SEGMENT, LOG_SEGMENTS), 256, 0, s>>>(p, fl, geo);
-      else soft_mask_bwd_log_kernel<T, false><<<dim3(LOG_CTAS_PER_SEGMENT, LOG_SEGMENTS), 256, 0, s>>>(p, fl, geo);
+      soft_mask_bwd_log_kernel<T><<<dim3(LOG_CTAS_PER_SEGMENT, LOG_SEGMENTS), 256, 0, s>>>(p, fl, geo);
       g_launches.fetch_add(1, std::memory_order_relaxed);
     }
   }
@@ -404,7 +407,8 @@ int soft_mask_bwd_sidebuf_impl(const T* grad_soft, const T* soft, const int64_t*
 template <typename T>
 int prepare_impl(bool backward, const T* g_cam, const T* g_img, const T* g_nrm, const T* vertices,
                  const int64_t* faces, const T* proj, const T* rot, const T* trans, const T* transform, int B,
-                 int Bv, int V, int F, T* face_cam, T* face_img, T* face_nrm, T* g_vertices, void* stream) {
+                 int Bv, int V, int F, T* face_cam, T* face_img, T* face_nrm, T* g_vertices, T* g_proj, T* g_rot,
+                 T* g_trans, T* g_transform, void* stream) {
   if (B < 0 || V < 0 || F < 0 || (Bv != 1 && Bv != B)) return DIBR_ERR_INVALID_ARGUMENT;
   if ((int64_t)B * F >= (int64_t)1 << 40 || (int64_t)Bv * V >= (int64_t)1 << 40) return DIBR_ERR_TOO_LARGE;
   const bool by_matrix = transform != nullptr;
@@ -412,11 +416,15 @@ int prepare_impl(bool backward, const T* g_cam, const T* g_img, const T* g_nrm, 
   if (!by_matrix && (!rot || !trans)) return DIBR_ERR_INVALID_ARGUMENT;
   cudaStream_t s = static_cast<cudaStream_t>(stream);
   const int64_t n = (int64_t)B * F;
+  const bool cam_grad = g_proj || g_rot || g_trans || g_transform;
   if (backward) {
-    if ((int64_t)Bv * V > 0) {
-      if (!g_vertices) return DIBR_ERR_INVALID_ARGUMENT;
-      CUDA_TRY(cudaMemsetAsync(g_vertices, 0, (size_t)Bv * V * 3 * sizeof(T), s));
-    }
+    if ((by_matrix && (g_rot || g_trans)) || (!by_matrix && g_transform)) return DIBR_ERR_INVALID_ARGUMENT;
+    if (!g_vertices && !cam_grad) return DIBR_ERR_INVALID_ARGUMENT;
+    if (g_vertices && (int64_t)Bv * V > 0) CUDA_TRY(cudaMemsetAsync(g_vertices, 0, (size_t)Bv * V * 3 * sizeof(T), s));
+    if (g_proj) CUDA_TRY(cudaMemsetAsync(g_proj, 0, 3 * sizeof(T), s));
+    if (g_rot && B > 0) CUDA_TRY(cudaMemsetAsync(g_rot, 0, (size_t)B * 9 * sizeof(T), s));
+    if (g_trans && B > 0) CUDA_TRY(cudaMemsetAsync(g_trans, 0, (size_t)B * 3 * sizeof(T), s));
+    if (g_transform && B > 0) CUDA_TRY(cudaMemsetAsync(g_transform, 0, (size_t)B * 12 * sizeof(T), s));
   } else if (n > 0 && (!face_cam || !face_img || !face_nrm)) {
     return DIBR_ERR_INVALID_ARGUMENT;
   }
@@ -427,10 +435,13 @@ int prepare_impl(bool backward, const T* g_cam, const T* g_img, const T* g_nrm, 
   pp.transform = transform; pp.B = B; pp.Bv = Bv; pp.V = V; pp.F = F;
   pp.face_cam = face_cam; pp.face_img = face_img; pp.face_nrm = face_nrm;
   pp.g_cam = g_cam; pp.g_img = g_img; pp.g_nrm = g_nrm; pp.g_vertices = g_vertices;
+  pp.g_proj = g_proj; pp.g_rot = g_rot; pp.g_trans = g_trans; pp.g_transform = g_transform;
   const unsigned nb = (unsigned)((n + 255) / 256);
   if (backward) {
     if (!g_cam && !g_img && !g_nrm) return DIBR_OK;                 // all-zero upstream: the memset is the answer
-    { ProfScope ps(DIBR_KERNEL_PREPARE_BWD, s); prepare_vertices_bwd_kernel<T><<<nb, 256, 0, s>>>(pp); }
+    { ProfScope ps(DIBR_KERNEL_PREPARE_BWD, s);
+      if (cam_grad) prepare_vertices_bwd_kernel<T, true><<<nb, 256, 0, s>>>(pp);
+      else prepare_vertices_bwd_kernel<T, false><<<nb, 256, 0, s>>>(pp); }
     LAUNCH_CHECK("prepare_vertices_bwd_kernel");
   } else {
     { ProfScope ps(DIBR_KERNEL_PREPARE_FWD, s); prepare_vertices_fwd_kernel<T><<<nb, 256, 0, s>>>(pp); }
@@ -759,15 +770,17 @@ DIBR_API size_t dibr_mask_iou_workspace_bytes(int B, int64_t P, int elem_size) {
                                                T* face_vertices_image, T* face_normals, void* stream) {      \
     return prepare_impl<T>(false, nullptr, nullptr, nullptr, vertices, faces, camera_proj, rot, trans,       \
                            transform, B, Bv, V, F, face_vertices_camera, face_vertices_image, face_normals,  \
-                           nullptr, stream);                                                                  \
+                           nullptr, nullptr, nullptr, nullptr, nullptr, stream);                              \
   }                                                                                                           \
   DIBR_API int dibr_prepare_vertices_bwd_##SUF(const T* grad_camera, const T* grad_image,                    \
                                                const T* grad_normals, const T* vertices,                     \
                                                const int64_t* faces, const T* camera_proj, const T* rot,     \
                                                const T* trans, const T* transform, int B, int Bv, int V,     \
-                                               int F, T* grad_vertices, void* stream) {                      \
+                                               int F, T* grad_vertices, T* grad_proj, T* grad_rot,           \
+                                               T* grad_trans, T* grad_transform, void* stream) {             \
     return prepare_impl<T>(true, grad_camera, grad_image, grad_normals, vertices, faces, camera_proj, rot,   \
-                           trans, transform, B, Bv, V, F, nullptr, nullptr, nullptr, grad_vertices, stream); \
+                           trans, transform, B, Bv, V, F, nullptr, nullptr, nullptr, grad_vertices,          \
+                           grad_proj, grad_rot, grad_trans, grad_transform, stream);                          \
   }                                                                                                           \
   DIBR_API int dibr_texture_mapping_fwd_##SUF(const T* uv, const T* texture_maps, const T* mask, int B,      \
                                               int64_t N, int Bt, int C, int Ht, int Wt, int mode, T* out,    \

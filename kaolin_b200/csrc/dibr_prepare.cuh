@@ -34,7 +34,13 @@ struct PrepareParams {
   const T* g_cam;           // (B,F,3,3)
   const T* g_img;           // (B,F,3,2)
   const T* g_nrm;           // (B,F,3)
-  T* g_vertices;            // (Bv,V,3), zero-filled by the host wrapper
+  T* g_vertices;            // (Bv,V,3), zero-filled by the host wrapper; nullptr = not wanted
+  // optional camera gradients (zero-filled by the host wrapper; nullptr = not wanted): the reference is pure
+  // torch and differentiates through every camera tensor (utils.py:160-172)
+  T* g_proj;                // (3)
+  T* g_rot;                 // (B,3,3)
+  T* g_trans;               // (B,3)
+  T* g_transform;           // (B,4,3)
 };
 
 template <typename T>
@@ -116,10 +122,42 @@ __global__ void __launch_bounds__(256) prepare_vertices_fwd_kernel(PrepareParams
   on[0] = nx / len; on[1] = ny / len; on[2] = nz / len;
 }
 
+template <typename T, bool CAMGRAD>
+__device__ __forceinline__ void prepare_bwd_body(const PrepareParams<T>& pp, const int64_t g, const bool active,
+                                                 const bool uniform);
+
+// Sum of `v` over the lanes of a warp whose active lanes all belong to view `b`; one atomic by lane 0.  Warps that
+// straddle two views (or hold inactive lanes) fall back to one atomic per lane.
 template <typename T>
+__device__ __forceinline__ void warp_accumulate(T* dst, T v, const bool uniform) {
+  if (uniform) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+    if ((threadIdx.x & 31) == 0 && v != (T)0) atomicAdd(dst, v);
+  } else if (v != (T)0) {
+    atomicAdd(dst, v);
+  }
+}
+
+template <typename T, bool CAMGRAD>
 __global__ void __launch_bounds__(256) prepare_vertices_bwd_kernel(PrepareParams<T> pp) {
   const int64_t g = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-  if (g >= (int64_t)pp.B * pp.F) return;
+  const bool in_range = g < (int64_t)pp.B * pp.F;
+  if (!CAMGRAD && !in_range) return;
+  if (CAMGRAD) {                     // the camera sums are warp-collective: out-of-range lanes contribute zeros
+    const int64_t gl = in_range ? g : (int64_t)pp.B * pp.F - 1;
+    const int bl = (int)(gl / pp.F);
+    const int b0 = __shfl_sync(0xffffffffu, bl, 0);
+    const bool uniform = __all_sync(0xffffffffu, bl == b0);
+    prepare_bwd_body<T, true>(pp, gl, in_range, uniform);
+  } else {
+    prepare_bwd_body<T, false>(pp, g, true, false);
+  }
+}
+
+template <typename T, bool CAMGRAD>
+__device__ __forceinline__ void prepare_bwd_body(const PrepareParams<T>& pp, const int64_t g, const bool active,
+                                                 const bool uniform) {
   const int b = (int)(g / pp.F), f = (int)(g % pp.F);
   const ViewCamera<T> cam = load_camera<T>(pp, b);
   const int64_t voff = pp.Bv == 1 ? (int64_t)0 : (int64_t)b * pp.V * 3;
@@ -127,15 +165,21 @@ __global__ void __launch_bounds__(256) prepare_vertices_bwd_kernel(PrepareParams
   const T p0 = pp.proj[0], p1 = pp.proj[1], p2 = pp.proj[2];
   int64_t vi[3];
   T q[3][3], gq[3][3];
+  T gp0 = 0, gp1 = 0, gp2 = 0;
+  bool ok = active;
 #pragma unroll
   for (int k = 0; k < 3; ++k) {
     vi[k] = pp.faces[(int64_t)f * 3 + k];
-    if ((uint64_t)vi[k] >= (uint64_t)pp.V) return;     // forward wrote NaN for this face; nothing to scatter
+    if ((uint64_t)vi[k] >= (uint64_t)pp.V) { ok = false; vi[k] = 0; }  // forward wrote NaN for this face: no gradient
+  }
+  if (!CAMGRAD && !ok) return;
+#pragma unroll
+  for (int k = 0; k < 3; ++k) {
     to_camera<T>(cam, vb + vi[k] * 3, q[k]);
 #pragma unroll
-    for (int j = 0; j < 3; ++j) gq[k][j] = pp.g_cam ? pp.g_cam[g * 9 + k * 3 + j] : (T)0;
+    for (int j = 0; j < 3; ++j) gq[k][j] = (ok && pp.g_cam) ? pp.g_cam[g * 9 + k * 3 + j] : (T)0;
   }
-  if (pp.g_img) {                     // img_x = (x p0) / (z p2),  img_y = (y p1) / (z p2)
+  if (ok && pp.g_img) {               // img_x = (x p0) / (z p2),  img_y = (y p1) / (z p2)
 #pragma unroll
     for (int k = 0; k < 3; ++k) {
       const T gx = pp.g_img[g * 6 + k * 2], gy = pp.g_img[g * 6 + k * 2 + 1];
@@ -144,9 +188,14 @@ __global__ void __launch_bounds__(256) prepare_vertices_bwd_kernel(PrepareParams
       gq[k][0] += gx * p0 / pz;
       gq[k][1] += gy * p1 / pz;
       gq[k][2] -= (gx * ix + gy * iy) / q[k][2];
+      if (CAMGRAD) {                  // d ix / d p0 = x / pz,  d ix / d p2 = -ix / p2
+        gp0 += gx * q[k][0] / pz;
+        gp1 += gy * q[k][1] / pz;
+        gp2 -= (gx * ix + gy * iy) / p2;
+      }
     }
   }
-  if (pp.g_nrm) {                     // n = c / (|c| + 1e-10), c = e0 x e1
+  if (ok && pp.g_nrm) {               // n = c / (|c| + 1e-10), c = e0 x e1
     const T e0x = q[1][0] - q[0][0], e0y = q[1][1] - q[0][1], e0z = q[1][2] - q[0][2];
     const T e1x = q[2][0] - q[0][0], e1y = q[2][1] - q[0][1], e1z = q[2][2] - q[0][2];
     const T cx = e0y * e1z - e0z * e1y, cy = e0z * e1x - e0x * e1z, cz = e0x * e1y - e0y * e1x;
@@ -163,13 +212,43 @@ __global__ void __launch_bounds__(256) prepare_vertices_bwd_kernel(PrepareParams
     gq[2][0] += b0; gq[2][1] += b1; gq[2][2] += b2;
     gq[0][0] -= a0 + b0; gq[0][1] -= a1 + b1; gq[0][2] -= a2 + b2;
   }
-  T* gv = pp.g_vertices + voff;
+  T gt[3] = {0, 0, 0};                // sum over the face's vertices of dL/dp (rot/trans form: dL/dtrans = -that)
 #pragma unroll
   for (int k = 0; k < 3; ++k) {
 #pragma unroll
     for (int c = 0; c < 3; ++c) {     // cam_j = sum_c (p_c - t_c) m[j][c]  =>  dL/dp_c = sum_j gq_j m[j][c]
       const T v = gq[k][0] * cam.m[0][c] + gq[k][1] * cam.m[1][c] + gq[k][2] * cam.m[2][c];
-      atomicAdd(gv + vi[k] * 3 + c, v);
+      if (ok && pp.g_vertices) atomicAdd(pp.g_vertices + voff + vi[k] * 3 + c, v);
+      gt[c] += v;
+    }
+  }
+  if (!CAMGRAD) return;
+  if (pp.g_proj) {
+    warp_accumulate<T>(pp.g_proj + 0, gp0, true);
+    warp_accumulate<T>(pp.g_proj + 1, gp1, true);
+    warp_accumulate<T>(pp.g_proj + 2, gp2, true);
+  }
+  if (pp.g_trans) {
+#pragma unroll
+    for (int c = 0; c < 3; ++c) warp_accumulate<T>(pp.g_trans + (int64_t)b * 3 + c, ok ? -gt[c] : (T)0, uniform);
+  }
+  if (pp.g_rot || pp.g_transform) {
+    // dL/dm[j][c] = sum over the face's vertices of gq[.][j] * (p_c - t_c)
+#pragma unroll
+    for (int j = 0; j < 3; ++j) {
+#pragma unroll
+      for (int c = 0; c < 3; ++c) {
+        T v = 0;
+#pragma unroll
+        for (int k = 0; k < 3; ++k) v += gq[k][j] * (vb[vi[k] * 3 + c] - cam.t[c]);
+        v = ok ? v : (T)0;
+        if (pp.g_rot) warp_accumulate<T>(pp.g_rot + (int64_t)b * 9 + j * 3 + c, v, uniform);
+        else warp_accumulate<T>(pp.g_transform + (int64_t)b * 12 + c * 3 + j, v, uniform);      // M[c][j]
+      }
+      if (pp.g_transform) {           // cam_j += M[3][j]
+        const T v = ok ? gq[0][j] + gq[1][j] + gq[2][j] : (T)0;
+        warp_accumulate<T>(pp.g_transform + (int64_t)b * 12 + 9 + j, v, uniform);
+      }
     }
   }
 }

@@ -15,8 +15,12 @@
 //
 // Winner rule (order independent, equals the reference's in-order scan rasterization_cuda.cu:88-171):
 //   * among faces whose z0 is not NaN: the largest z0 (> -inf), lowest face index on ties;
-//   * if any inside face has a NaN z0 the reference's `z0 <= max_z0` is false from then on, so the
-//     LAST inside face in index order wins — tracked as (has_nan, max inside index) by the gather path.
+//   * a NaN never compares: `z0 <= max_z0` (:162) is false both for a NaN z0 (the face is accepted and max_z0 becomes
+//     NaN) and for any z0 against a NaN max_z0 (the next inside face is accepted whatever its depth, after which the
+//     normal compare resumes).  With n = the largest index among the inside faces with a NaN depth, the winner is
+//     therefore the normal rule restricted to the inside faces of index > n (any depth, -inf included, beats "none"),
+//     or n itself when there are none — resolve_after_nan() below, a second per-pixel pass taken only by pixels
+//     that met a NaN depth.
 #pragma once
 #include "dibr_binning.cuh"
 #include <cstdlib>
@@ -45,6 +49,33 @@ struct StagedFace {        // SoA in shared memory, one slot per staged face
   int id[256];
 };
 
+// ---------------------------------------------------------------------------------- NaN depths (rare)
+// One pixel that met an inside face with a NaN depth, n = the largest index of such a face: the reference's in-order
+// scan (:106-170) ends with the best face among the inside faces of index > n — largest z0, lowest index on ties,
+// the first of them accepted whatever its depth — or with n itself.  Walks the tile's (unordered) candidate lists.
+template <typename T>
+__device__ __noinline__ void resolve_after_nan(const RasterFwdParams<T>& rp, const BinLists& L, const TileLists& tl,
+                                               const int64_t vbase, const int px, const int py, const T x0,
+                                               const T y0, const int n, int& best_f, T& bw0, T& bw1, T& bw2) {
+  T best_z = 0;
+  best_f = -1;
+  const int n_total = tl.n_fine + tl.n_filtered();
+  for (int k = 0; k < n_total; ++k) {
+    const int f = k < tl.n_fine ? tl.fine[k] : tl.filtered_at(k - tl.n_fine);
+    if (f <= n || !range_hits_pixel(L.ranges[vbase + f], px, py)) continue;
+    T p[6], w0, w1, w2;
+    load_face_xy<T>(rp.img, vbase + f, rp.coord_mult, rp.premultiplied, p);
+    if (!bary_weights<T>(p[0], p[1], p[2], p[3], p[4], p[5], x0, y0, rp.eps, w0, w1, w2)) continue;
+    const T* zz = rp.z + (vbase + f) * 3;
+    const T z0 = interp3<T>(zz[0], zz[1], zz[2], w0, w1, w2);           // not NaN: f > n
+    if (best_f < 0 || z0 > best_z || (z0 == best_z && f < best_f)) { best_z = z0; best_f = f; }
+  }
+  if (best_f < 0) best_f = n;
+  T p[6];
+  load_face_xy<T>(rp.img, vbase + best_f, rp.coord_mult, rp.premultiplied, p);
+  bary_weights<T>(p[0], p[1], p[2], p[3], p[4], p[5], x0, y0, rp.eps, bw0, bw1, bw2);
+}
+
 // ---------------------------------------------------------------------------------- gather (per pixel)
 template <typename T>
 __device__ __forceinline__ void gather_tile(const RasterFwdParams<T>& rp, const FaceLayout& fl, const Geometry& geo,
@@ -56,8 +87,7 @@ __device__ __forceinline__ void gather_tile(const RasterFwdParams<T>& rp, const 
   T best_z = -RN<T>::inf();
   best_f = -1;
   bw0 = 0; bw1 = 0; bw2 = 0;
-  bool has_nan = false;
-  int last_inside = -1;
+  int nan_idx = -1;                 // largest index among the inside faces with a NaN depth
 
   const TileLists tl = tile_lists(L, geo, fl, b, tx, ty);
   const int n_tile = tl.n_fine;
@@ -100,8 +130,7 @@ __device__ __forceinline__ void gather_tile(const RasterFwdParams<T>& rp, const 
           continue;
         const int fid = st.id[s];
         const T z0 = interp3<T>(st.z[0][s], st.z[1][s], st.z[2][s], w0, w1, w2);
-        last_inside = max(last_inside, fid);
-        if (z0 != z0) { has_nan = true; continue; }
+        if (z0 != z0) { nan_idx = max(nan_idx, fid); continue; }
         if (z0 > best_z || (z0 == best_z && fid < best_f)) {
           best_z = z0; best_f = fid; bw0 = w0; bw1 = w1; bw2 = w2;
         }
@@ -109,12 +138,8 @@ __device__ __forceinline__ void gather_tile(const RasterFwdParams<T>& rp, const 
     }
     // the next iteration's block_compact_256 starts with a __syncthreads() before `st` is rewritten
   }
-  if (in_image && has_nan) {      // rare: reproduce the in-order scan's outcome (see header)
-    best_f = last_inside;
-    T p[6];
-    load_face_xy<T>(rp.img, vbase + best_f, rp.coord_mult, rp.premultiplied, p);
-    bary_weights<T>(p[0], p[1], p[2], p[3], p[4], p[5], x0, y0, rp.eps, bw0, bw1, bw2);
-  }
+  if (in_image && nan_idx >= 0)     // rare: reproduce the in-order scan's outcome (see header)
+    resolve_after_nan<T>(rp, L, tl, vbase, px, py, x0, y0, nan_idx, best_f, bw0, bw1, bw2);
 }
 
 // ---------------------------------------------------------------------------------- epilogue (per pixel)
@@ -410,8 +435,7 @@ __device__ __forceinline__ void scan_pixel_in_order_rule(const RasterFwdParams<f
                                                          const int py, const float x0, const float y0, int& best_f,
                                                          float& bw0, float& bw1, float& bw2) {
   float best_z = -RN<float>::inf();
-  bool has_nan = false;
-  int last_inside = -1;
+  int nan_idx = -1;
   best_f = -1; bw0 = 0; bw1 = 0; bw2 = 0;
   const int n_total = tl.n_fine + tl.n_filtered();
   for (int k = 0; k < n_total; ++k) {
@@ -422,16 +446,10 @@ __device__ __forceinline__ void scan_pixel_in_order_rule(const RasterFwdParams<f
     if (!bary_weights<float>(p[0], p[1], p[2], p[3], p[4], p[5], x0, y0, rp.eps, w0, w1, w2)) continue;
     const float* zz = rp.z + (vbase + f) * 3;
     const float z0 = interp3<float>(zz[0], zz[1], zz[2], w0, w1, w2);
-    last_inside = max(last_inside, f);
-    if (z0 != z0) { has_nan = true; continue; }
+    if (z0 != z0) { nan_idx = max(nan_idx, f); continue; }
     if (z0 > best_z || (z0 == best_z && f < best_f)) { best_z = z0; best_f = f; bw0 = w0; bw1 = w1; bw2 = w2; }
   }
-  if (has_nan) {
-    best_f = last_inside;
-    float p[6];
-    load_face_xy<float>(rp.img, vbase + best_f, rp.coord_mult, rp.premultiplied, p);
-    bary_weights<float>(p[0], p[1], p[2], p[3], p[4], p[5], x0, y0, rp.eps, bw0, bw1, bw2);
-  }
+  if (nan_idx >= 0) resolve_after_nan<float>(rp, L, tl, vbase, px, py, x0, y0, nan_idx, best_f, bw0, bw1, bw2);
 }
 
 // NT threads per CTA (one CTA per 16x16 tile whatever NT).
@@ -548,7 +566,8 @@ raster_fwd_scatter_kernel(RasterFwdParams<float> rp, FaceLayout fl, Geometry geo
 
 inline int raster_threads_default() {
   static const int nt = [] {
-    const char* e = getenv("DIBR_RASTER_NT");
+    const char* on = getenv("DIBR_B200_TUNING");       // the one documented switch (include/dibr_b200.h)
+    const char* e = (on && on[0] == '1' && on[1] == 0) ? getenv("DIBR_RASTER_NT") : nullptr;
     const int v = e ? atoi(e) : 0;
     return (v == 64 || v == 128 || v == 256) ? v : 64;
   }();

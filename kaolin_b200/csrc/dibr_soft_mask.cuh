@@ -156,47 +156,6 @@ __device__ __forceinline__ void soft_backward_pair<float>(const float* p, const 
   }
 }
 
-// Same gradient as soft_backward_pair, returned as the six components of the face's (3,2) coordinate gradient
-// (zeros where the pair does not contribute) so that lanes holding the same face can be summed before the atomics.
-template <typename T>
-__device__ __forceinline__ void soft_backward_vec(const T* p, const T x0, const T y0, const T prob, const int edgeid,
-                                                  const T dLdp, const T allprob, const float sigmainv,
-                                                  const float multiplier, T* out) {
-  const double EPS = 1e-7;
-#pragma unroll
-  for (int c = 0; c < 6; ++c) out[c] = (T)0;
-  const T dLdz = (T)(-1.0 * (double)sigmainv * (double)dLdp * (1.0 - (double)allprob) /
-                     (1.0 - (double)prob + EPS) * (double)prob);
-  if (dLdz == (T)0) return;
-  const T s = dLdz * ((T)1 / (T)multiplier);
-  if (edgeid >= 3) {
-    const int v = edgeid - 3;
-    const T x1 = v == 0 ? p[0] : (v == 1 ? p[2] : p[4]), y1 = v == 0 ? p[1] : (v == 1 ? p[3] : p[5]);
-    const T gx = s * 2 * (x1 - x0), gy = s * 2 * (y1 - y0);
-#pragma unroll
-    for (int c = 0; c < 3; ++c) { out[2 * c] = v == c ? gx : (T)0; out[2 * c + 1] = v == c ? gy : (T)0; }
-  } else {
-    const int e = edgeid, e2 = edgeid == 2 ? 0 : edgeid + 1;
-    const T x1 = e == 0 ? p[0] : (e == 1 ? p[2] : p[4]), y1 = e == 0 ? p[1] : (e == 1 ? p[3] : p[5]);
-    const T x2 = e2 == 0 ? p[0] : (e2 == 1 ? p[2] : p[4]), y2 = e2 == 0 ? p[1] : (e2 == 1 ? p[3] : p[5]);
-    const T A = y2 - y1, Bc = x1 - x2, Cc = x2 * y1 - x1 * y2;
-    const T up = A * x0 + Bc * y0 + Cc;
-    const T down = A * A + Bc * Bc;
-    const double rden = 1.0 / ((double)down + EPS);
-    const T dissquare = (T)((double)(up * up) * rden);
-    const T dzdA = (T)((double)(2 * (x0 * up - dissquare * A)) * rden);
-    const T dzdB = (T)((double)(2 * (y0 * up - dissquare * Bc)) * rden);
-    const T dzdC = (T)((double)(2 * up) * rden);
-    const T g1x = s * (dzdB - y2 * dzdC), g1y = s * (x2 * dzdC - dzdA);
-    const T g2x = s * (y1 * dzdC - dzdB), g2y = s * (dzdA - x1 * dzdC);
-#pragma unroll
-    for (int c = 0; c < 3; ++c) {
-      out[2 * c] = e == c ? g1x : (e2 == c ? g2x : (T)0);
-      out[2 * c + 1] = e == c ? g1y : (e2 == c ? g2y : (T)0);
-    }
-  }
-}
-
 // distance + probability of one (pixel, face) pair: the reference's arithmetic, or — fp32, fused path — its fp32 form
 template <typename T>
 __device__ __forceinline__ void soft_pair(const T* p, const T x0, const T y0, const float multiplier,
@@ -846,70 +805,36 @@ __device__ __forceinline__ void log_fetch_face(const SoftParams<T>& sp, const Fa
   load_face_xy<T>(sp.img, it.gf, sp.coord_mult, sp.premultiplied, it.p);
 }
 
-template <typename T, bool AGG>
+template <typename T>
 __global__ void __launch_bounds__(256) soft_mask_bwd_log_kernel(SoftParams<T> sp, FaceLayout fl, Geometry geo) {
   const unsigned seg = blockIdx.y;
   const unsigned n = min(sp.log_count[seg], sp.log_cap);
   const unsigned hw = (unsigned)geo.H * (unsigned)geo.W;
   const bool any_over = *sp.over_count != 0u;
   const float sx = pix_scale(sp.pix_mult, geo.W), sy = pix_scale(sp.pix_mult, geo.H);
-  const int lane = threadIdx.x & 31;
   const uint4* log = sp.log + (size_t)seg * sp.log_cap;
   const unsigned stride = gridDim.x * blockDim.x;
-  if (!AGG) {
-    for (unsigned i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += 2 * stride) {
-      const unsigned j = i + stride;
-      const bool two = j < n;
-      LogItem<T> a, c;
-      a.rec = log[i];
-      c.rec = log[two ? j : i];
-      log_fetch_pixel<T>(sp, geo, hw, any_over, a);
-      log_fetch_pixel<T>(sp, geo, hw, any_over, c);
-      log_fetch_face<T>(sp, fl, a);
-      log_fetch_face<T>(sp, fl, c);
-      if (a.g != (T)0 && !a.flag) {
-        const T x0 = (T)pix_coord(sx, geo.W, (int)a.px), y0 = (T)pix_coord(sy, geo.H, geo.H - 1 - (int)a.py);
-        soft_backward_pair<T>(a.p, x0, y0, log_prob<T>(a.rec), (int)(a.rec.y & 7u), a.g, a.soft, sp.sigmainv,
-                              sp.pix_mult, sp.grad_img + a.gf * 6);
-      }
-      if (two && c.g != (T)0 && !c.flag) {
-        const T x0 = (T)pix_coord(sx, geo.W, (int)c.px), y0 = (T)pix_coord(sy, geo.H, geo.H - 1 - (int)c.py);
-        soft_backward_pair<T>(c.p, x0, y0, log_prob<T>(c.rec), (int)(c.rec.y & 7u), c.g, c.soft, sp.sigmainv,
-                              sp.pix_mult, sp.grad_img + c.gf * 6);
-      }
+  // (summing lanes that hold the same face with shuffles before the atomics was measured slower: c2 0.121 vs
+  // 0.108 ms, c3 0.175 vs 0.154 ms — the kernel waits on its gathers, not on the atomics)
+  for (unsigned i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += 2 * stride) {
+    const unsigned j = i + stride;
+    const bool two = j < n;
+    LogItem<T> a, c;
+    a.rec = log[i];
+    c.rec = log[two ? j : i];
+    log_fetch_pixel<T>(sp, geo, hw, any_over, a);
+    log_fetch_pixel<T>(sp, geo, hw, any_over, c);
+    log_fetch_face<T>(sp, fl, a);
+    log_fetch_face<T>(sp, fl, c);
+    if (a.g != (T)0 && !a.flag) {
+      const T x0 = (T)pix_coord(sx, geo.W, (int)a.px), y0 = (T)pix_coord(sy, geo.H, geo.H - 1 - (int)a.py);
+      soft_backward_pair<T>(a.p, x0, y0, log_prob<T>(a.rec), (int)(a.rec.y & 7u), a.g, a.soft, sp.sigmainv,
+                            sp.pix_mult, sp.grad_img + a.gf * 6);
     }
-    return;
-  }
-  // AGG: warp-uniform trip count; the 32 lanes take 32 consecutive log entries (neighbouring pixels of a tile row,
-  // whose k-lists largely hold the same faces), lanes with the same face are summed with shuffles, one red per group
-  for (unsigned i0 = blockIdx.x * blockDim.x + (threadIdx.x & ~31u); i0 < n; i0 += stride) {
-    const unsigned i = i0 + lane;
-    T c[6] = {0, 0, 0, 0, 0, 0};
-    int key = -1 - lane;                                    // inactive lanes: singleton groups
-    if (i < n) {
-      LogItem<T> a;
-      a.rec = log[i];
-      log_fetch_pixel<T>(sp, geo, hw, any_over, a);
-      if (a.g != (T)0 && !a.flag) {
-        log_fetch_face<T>(sp, fl, a);
-        const T x0 = (T)pix_coord(sx, geo.W, (int)a.px), y0 = (T)pix_coord(sy, geo.H, geo.H - 1 - (int)a.py);
-        soft_backward_vec<T>(a.p, x0, y0, log_prob<T>(a.rec), (int)(a.rec.y & 7u), a.g, a.soft, sp.sigmainv,
-                             sp.pix_mult, c);
-        key = (int)a.gf;
-      }
-    }
-    const unsigned peers = __match_any_sync(0xffffffffu, key);
-    int src[5];
-    group_partners(peers, src);
-    unsigned steps = 0;
-#pragma unroll
-    for (int st = 0; st < 5; ++st)
-      if (__any_sync(0xffffffffu, src[st] != lane)) steps |= 1u << st;
-    const bool leader = key >= 0 && ((peers & ((1u << lane) - 1u)) == 0u);
-#pragma unroll
-    for (int k = 0; k < 6; ++k) {
-      const T v = group_sum<T>(c[k], src, steps);
-      if (leader && v != (T)0) atomicAdd(sp.grad_img + (int64_t)key * 6 + k, v);
+    if (two && c.g != (T)0 && !c.flag) {
+      const T x0 = (T)pix_coord(sx, geo.W, (int)c.px), y0 = (T)pix_coord(sy, geo.H, geo.H - 1 - (int)c.py);
+      soft_backward_pair<T>(c.p, x0, y0, log_prob<T>(c.rec), (int)(c.rec.y & 7u), c.g, c.soft, sp.sigmainv,
+                            sp.pix_mult, sp.grad_img + c.gf * 6);
     }
   }
 }

@@ -74,16 +74,6 @@ def look_at(eye, at, up):
     return torch.stack([cx, cy, -cz], dim=1), eye
 
 
-def mask_iou(lhs_mask, rhs_mask):
-    """kaolin/metrics/render.py:18-40."""
-    b = lhs_mask.shape[0]
-    mul = lhs_mask * rhs_mask
-    add = lhs_mask + rhs_mask
-    up = torch.sum(mul.reshape(b, -1), dim=1)
-    down = torch.sum((add - mul).reshape(b, -1), dim=1)
-    return 1.0 - torch.mean(up / (down + 1e-10))
-
-
 class MultiViewOptimizer:
     """Multi-view DIB-R shape optimisation (BASELINE.json config 4).  Each rank owns a contiguous shard of the
     cameras; the mesh (vertices leaf, faces, per-vertex features) is replicated.  One step = prepare_vertices (fused CUDA kernel)

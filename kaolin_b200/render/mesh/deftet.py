@@ -65,6 +65,7 @@ class DeftetSparseRenderer(Function):
                 knum, float(eps), _lib.ptr_array(outs), _lib.ptr(face_idx), _lib.ptr(weights), _lib.ptr(ws), nbytes,
                 _lib.current_stream(dev))
         _lib.check(code, fn)
+        ctx.need_bwd = need_bwd
         if need_bwd:
             ctx.save_for_backward(face_idx, weights, face_vertices_image, *feats)
         ctx.mark_non_differentiable(face_idx)
@@ -77,7 +78,9 @@ class DeftetSparseRenderer(Function):
     def backward(ctx, *grads):
         fn = "deftet_sparse_render_backward_cuda"
         n_in = 6 + len(grads) - 1
-        if all(g is None for g in grads[:-1]):
+        # nothing differentiable asked for (e.g. only face_vertices_z / pixel_coords / render_ranges require grad:
+        # the reference returns None for those, deftet.py:337): no tensors were saved
+        if not ctx.need_bwd or all(g is None for g in grads[:-1]):
             return (None,) * n_in
         face_idx, weights, face_vertices_image = ctx.saved_tensors[:3]
         feats = list(ctx.saved_tensors[3:])

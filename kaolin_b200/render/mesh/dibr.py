@@ -36,13 +36,23 @@ class DibrSoftMaskCuda(Function):
         h, w = selected_face_idx.shape[1], selected_face_idx.shape[2]
         suf = _lib.suffix(face_vertices_image.dtype, fn)
         soft_mask = torch.empty((b, h, w), dtype=face_vertices_image.dtype, device=dev)
-        # with a gradient to come, the forward also logs its evaluated (pixel, face) pairs behind the bins
-        # (12 bytes per pair, about one pair per pixel) and backward runs one thread per logged pair
+        # with a gradient to come, the forward also logs its evaluated (pixel, face) pairs behind the bins and
+        # backward runs one thread per logged pair.  Records are 16 bytes and the log holds 2 per pixel (+64 Ki):
+        # about 32 bytes per pixel (0.5 GB at 64 x 512^2, 2.1 GB at 64 x 1024^2) held on ctx until backward, next to
+        # the bins — the reference holds 13 * knum = 390 bytes per pixel of side buffers instead.  If that allocation
+        # fails the forward goes without a log (keep = 0) and backward re-derives the k-lists (recompute kernel).
         keep = 1 if ctx.needs_input_grad[0] else 0
         lib = _lib.load()
         with torch.cuda.device(dev):
             nbytes = lib.dibr_soft_mask_workspace_bytes(b, b * f, h, w, keep, face_vertices_image.element_size())
-            ws = torch.empty(max(int(nbytes), 256), dtype=torch.uint8, device=dev)
+            try:
+                ws = torch.empty(max(int(nbytes), 256), dtype=torch.uint8, device=dev)
+            except torch.cuda.OutOfMemoryError:
+                if not keep:
+                    raise
+                keep = 0
+                nbytes = lib.dibr_soft_mask_workspace_bytes(b, b * f, h, w, 0, face_vertices_image.element_size())
+                ws = torch.empty(max(int(nbytes), 256), dtype=torch.uint8, device=dev)
             code = getattr(lib, "dibr_soft_mask_fwd_fused_" + suf)(
                 _lib.ptr(face_vertices_image), _lib.ptr(selected_face_idx), b, f, h, w, float(sigmainv),
                 float(boxlen), int(knum), float(multiplier), _lib.ptr(soft_mask), 0, 0, 0, _lib.ptr(ws), nbytes,
@@ -53,8 +63,8 @@ class DibrSoftMaskCuda(Function):
         ctx.boxlen = boxlen
         ctx.knum = knum
         ctx.save_for_backward(soft_mask, face_vertices_image, selected_face_idx)
-        # the binning workspace (a few tens of bytes per face, vs the reference's 13*knum bytes per PIXEL of saved
-        # side buffers) is kept for backward, which then skips the setup / binning kernels
+        # the workspace (bins: <= 80 bytes per face; pair log: see above) is kept for backward, which then skips the
+        # setup / binning kernels; without a log nothing is kept and backward bins again
         ctx.bins = ws if keep else None
         ctx.set_materialize_grads(False)
         return soft_mask

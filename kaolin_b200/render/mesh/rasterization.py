@@ -16,16 +16,11 @@ from torch.autograd import Function
 from ... import _C  # noqa: F401  (kept importable like `from kaolin import _C`)
 from ... import _lib
 
-try:
-    import nvdiffrast.torch as nvdiff
-    _has_nvdiffrast = True
-    _device2glctx = {}
-except ImportError:
-    # reference: rasterization.py:25-33.  The OpenGL backends are unavailable on this box (no graphics stack).
-    _has_nvdiffrast = False
-    nvdiff = None
-    logger = logging.getLogger(__name__)
-    logger.info("Cannot import nvdiffrast")
+# reference: rasterization.py:25-33 tries `import nvdiffrast.torch`.  The OpenGL backends are unavailable on this
+# box (no graphics stack); the names stay importable and every nvdiffrast entry raises the reference's ValueError.
+_has_nvdiffrast = False
+nvdiff = None
+logging.getLogger(__name__).info("Cannot import nvdiffrast")
 
 __all__ = [
     'rasterize',
@@ -36,27 +31,14 @@ _NVDIFF_MSG = ("nvdiffrast must be installed to be used as backend, but failed t
 
 
 def _get_nvdiff_glctx(device):
-    # reference: rasterization.py:35-39
-    if not _has_nvdiffrast:
-        raise ValueError(_NVDIFF_MSG)
-    if device not in _device2glctx:
-        _device2glctx[device] = nvdiff.RasterizeGLContext(output_db=False, device=device)
-    return _device2glctx[device]
+    """reference: rasterization.py:35-39.  OpenGL contexts are unavailable on this box (no graphics stack):
+    the name stays importable (dibr.py:20 of the reference imports it) and raises the reference's error."""
+    raise ValueError(_NVDIFF_MSG)
 
 
 def _legacy_to_opengl(face_vertices_image, face_vertices_z, valid_faces=None):
-    """Kaolin legacy coordinates -> OpenGL clip space (reference: rasterization.py:46-82). Pure torch."""
-    z = -face_vertices_z / (abs(face_vertices_z).max() + 1e-6)
-    _img = face_vertices_image.reshape(*face_vertices_image.shape[:-3], -1, 2)
-    pos = torch.stack([_img[..., 0], -_img[..., 1], z.reshape(*z.shape[:-2], -1)], dim=-1)
-    if valid_faces is None:
-        pos = torch.nn.functional.pad(pos, (0, 1), value=1.)
-    else:
-        pad = (valid_faces.unsqueeze(-1) * 2. - 1.).expand(*valid_faces.shape, 3)
-        pad = pad.reshape(*valid_faces.shape[:-1], -1, 1)
-        pos = torch.cat([pos, pad], dim=-1)
-    tri = torch.arange(pos.shape[-2], device=pos.device, dtype=torch.int).reshape(-1, 3)
-    return pos, tri
+    """reference: rasterization.py:46-82 (feeds the nvdiffrast backends only) — unavailable on this box."""
+    raise ValueError(_NVDIFF_MSG)
 
 
 def _require_cuda(fn, **tensors):
@@ -94,27 +76,12 @@ def _rasterize_backward(grad_interpolated_features, face_idx, output_weights, fa
 
 
 class NvdiffRasterizeFwdCudaBwd(Function):
-    """backend 'nvdiffrast_fwd' (reference: rasterization.py:145-241): OpenGL forward through nvdiffrast,
-    this library's backward.  The forward needs OpenGL — unavailable on this box — and raises the
-    reference's ValueError when nvdiffrast cannot be imported."""
+    """backend 'nvdiffrast_fwd' (reference: rasterization.py:145-241): OpenGL forward through nvdiffrast, this
+    library's backward.  The forward needs OpenGL — unavailable on this box — and raises the reference's
+    ValueError; the backward is the same native op as RasterizeCuda's (rasterization.py:230-238)."""
     @staticmethod
     def forward(ctx, height, width, face_vertices_z, face_vertices_image, face_features, valid_faces, eps):
-        if not _has_nvdiffrast:
-            raise ValueError(_NVDIFF_MSG)
-        device = face_vertices_z.device
-        glctx = _get_nvdiff_glctx(device)
-        pos, tri = _legacy_to_opengl(face_vertices_image, face_vertices_z, valid_faces)
-        rast = nvdiff.rasterize(glctx, pos, tri, (height, width), grad_db=False)
-        _face_features = face_features.reshape(*face_features.shape[:-3], face_features.shape[-3] * 3, -1)
-        interpolated_features = nvdiff.interpolate(_face_features, rast[0], tri)[0]
-        face_idx = (rast[0][..., -1].long() - 1).contiguous()
-        output_weights = torch.cat([rast[0][..., :2],
-                                    1. - torch.sum(rast[0][..., :2], dim=-1, keepdims=True)], dim=-1)
-        ctx.save_for_backward(face_idx, output_weights.contiguous(), face_vertices_image.contiguous(),
-                              face_features.contiguous())
-        ctx.mark_non_differentiable(face_idx)
-        ctx.eps = eps
-        return interpolated_features, face_idx
+        raise ValueError(_NVDIFF_MSG)
 
     @staticmethod
     def backward(ctx, grad_interpolated_features, grad_face_idx):
@@ -125,17 +92,8 @@ class NvdiffRasterizeFwdCudaBwd(Function):
 
 
 def _nvdiff_rasterize(height, width, face_vertices_z, face_vertices_image, face_features, valid_faces):
-    # reference: rasterization.py:84-143
-    if not _has_nvdiffrast:
-        raise ValueError(_NVDIFF_MSG)
-    device = face_vertices_z.device
-    glctx = _get_nvdiff_glctx(device)
-    pos, tri = _legacy_to_opengl(face_vertices_image, face_vertices_z, valid_faces)
-    rast = nvdiff.rasterize(glctx, pos, tri, (height, width), grad_db=False)
-    _face_features = face_features.reshape(*face_features.shape[:-3], face_features.shape[-3] * 3, -1)
-    interpolated_features = nvdiff.interpolate(_face_features, rast[0], tri)[0]
-    face_idx = (rast[0][..., -1].long() - 1).contiguous()
-    return interpolated_features, face_idx
+    # reference: rasterization.py:84-143 — needs OpenGL: unavailable on this box
+    raise ValueError(_NVDIFF_MSG)
 
 
 class RasterizeCuda(Function):

@@ -8,8 +8,9 @@ per-vertex camera / image coordinates and two expanded gathers on the way.  Here
 thread = (camera, face) gathers its three vertices, transforms, projects, and writes the three outputs;
 backward scatters into ``vertices.grad`` (summed over cameras when one mesh is broadcast over the batch).
 
-Only ``vertices`` is differentiable: a camera tensor that requires grad raises (the multi-view fitting loop
-of the reference, examples/tutorial/ian_dibr.py, optimises vertices / textures, not cameras).
+Every floating-point input is differentiable, as in the reference (pure torch): ``vertices`` and, when they
+require grad, ``camera_proj`` / ``camera_rot`` / ``camera_trans`` / ``camera_transform`` (warp-reduced sums in
+the same backward kernel).
 """
 import torch
 from torch.autograd import Function
@@ -50,21 +51,27 @@ class PrepareVerticesCuda(Function):
     def backward(ctx, g_cam, g_img, g_nrm):
         fn = "prepare_vertices_backward"
         vertices, faces, proj, rot, trans, transform = ctx.saved_tensors
-        if not ctx.needs_input_grad[0]:
+        need = ctx.needs_input_grad
+        if not any(need[:1] + need[2:6]):
             return (None,) * 7
         dev = vertices.device
         suf = _lib.suffix(vertices.dtype, fn)
         g_cam = None if g_cam is None else g_cam.contiguous()
         g_img = None if g_img is None else g_img.contiguous()
         g_nrm = None if g_nrm is None else g_nrm.contiguous()
-        grad_vertices = torch.empty_like(vertices)
+        grad_vertices = torch.empty_like(vertices) if need[0] else None
+        g_proj = torch.empty_like(proj) if need[2] else None
+        g_rot = torch.empty_like(rot) if rot is not None and need[3] else None
+        g_trans = torch.empty_like(trans) if trans is not None and need[4] else None
+        g_transform = torch.empty_like(transform) if transform is not None and need[5] else None
         with torch.cuda.device(dev):
             code = getattr(_lib.load(), "dibr_prepare_vertices_bwd_" + suf)(
                 _lib.ptr(g_cam), _lib.ptr(g_img), _lib.ptr(g_nrm), _lib.ptr(vertices), _lib.ptr(faces),
                 _lib.ptr(proj), *_cam_ptrs(rot, trans, transform), ctx.batch, vertices.shape[0],
-                vertices.shape[1], faces.shape[0], _lib.ptr(grad_vertices), _lib.current_stream(dev))
+                vertices.shape[1], faces.shape[0], _lib.ptr(grad_vertices), _lib.ptr(g_proj), _lib.ptr(g_rot),
+                _lib.ptr(g_trans), _lib.ptr(g_transform), _lib.current_stream(dev))
         _lib.check(code, fn)
-        return grad_vertices, None, None, None, None, None, None
+        return grad_vertices, None, g_proj, g_rot, g_trans, g_transform, None
 
 
 def _camera_tensor(name, t, shape_tail, like):
@@ -75,9 +82,6 @@ def _camera_tensor(name, t, shape_tail, like):
         raise RuntimeError(f"prepare_vertices: {name} must be on {like.device}, got {t.device}")
     if t.dtype != like.dtype:
         raise RuntimeError(f"prepare_vertices: {name} must be of dtype {like.dtype}, got {t.dtype}")
-    if t.requires_grad and torch.is_grad_enabled():
-        raise RuntimeError(f"prepare_vertices: gradients w.r.t. {name} are not implemented "
-                           "(only `vertices` is differentiable)")
     return t.contiguous()
 
 

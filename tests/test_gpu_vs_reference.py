@@ -277,6 +277,38 @@ def test_edge_cases(kal, O):
     assert torch.equal(idx.cpu(), o_idx)
 
 
+@pytest.mark.parametrize("dtype", [torch.float32, torch.float64])
+def test_nan_depth_in_order_rule(kal, O, ref_C, dtype):
+    """rasterization_cuda.cu:162 `if (z0 <= max_z0) continue;` with NaN depths: a NaN-depth face is always accepted,
+    the next inside face after it too, then the normal compare resumes.  Stacked identical triangles with NaN
+    depths at chosen / random positions, against the oracle's in-order scan and the reference's kernel."""
+    tri = torch.tensor([[-.6, -.6], [.6, -.6], [0., .7]])
+    # face 0 NaN, face 1 z=-1, face 2 z=-2: the reference keeps face 1 (face 2 is behind it)
+    cases = [[float("nan"), -1., -2.], [float("nan"), -2., -1.], [-1., float("nan")], [-1., float("nan"), -5., -3., -4.],
+             [float("nan"), float("-inf"), float("-inf")], [-1., float("nan"), float("nan")]]
+    g = torch.Generator().manual_seed(3)
+    for _ in range(6):
+        zz = (-1 - 3 * torch.rand(40, generator=g))
+        zz[torch.randint(0, 40, (4,), generator=g)] = float("nan")
+        cases.append(zz.tolist())
+    for zs in cases:
+        F = len(zs)
+        img = tri.view(1, 1, 3, 2).repeat(1, F, 1, 1)
+        img = (img + 0.02 * torch.rand(1, F, 3, 2, generator=g)).to("cuda", dtype)      # not all pixels see all faces
+        z = torch.tensor(zs).view(1, F, 1).repeat(1, 1, 3).to("cuda", dtype)
+        feat = torch.rand(1, F, 3, 2, generator=g).to("cuda", dtype)
+        out, idx = kal.render.mesh.rasterize(40, 36, z, img, feat)
+        o_feat, o_idx, _ = O.rasterize_forward(40, 36, z.cpu(), img.cpu(), feat.cpu())
+        r_feat, r_idx, _ = O.rasterize_forward(40, 36, z, img, feat, None, 1000., 1e-8, backend=ref_C)
+        assert torch.equal(o_idx, r_idx.cpu()), "oracle vs reference kernel"
+        assert torch.equal(idx.cpu(), o_idx), f"depths {zs[:6]}: {(idx.cpu() != o_idx).sum().item()} pixels differ"
+    # the first case, spelled out
+    img = tri.view(1, 1, 3, 2).repeat(1, 3, 1, 1).to("cuda", dtype)
+    z = torch.tensor([float("nan"), -1., -2.]).view(1, 3, 1).repeat(1, 1, 3).to("cuda", dtype)
+    _, idx = kal.render.mesh.rasterize(32, 32, z, img, torch.ones(1, 3, 3, 1, device="cuda", dtype=dtype))
+    assert int(idx.max()) == 1 and set(idx.unique().tolist()) == {-1, 1}
+
+
 def test_error_behaviour(kal):
     z = torch.zeros(1, 2, 3); img = torch.zeros(1, 2, 3, 2); feat = torch.zeros(1, 2, 3, 1)
     with pytest.raises(RuntimeError):
@@ -473,7 +505,7 @@ torch.save(img.grad.cpu(), sys.argv[1])
 ''' % os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
     grads = []
     for cap in ("0", "20000"):
-        env = dict(os.environ, DIBR_SOFT_LOG_CAP=cap)
+        env = dict(os.environ, DIBR_B200_TUNING="1", DIBR_SOFT_LOG_CAP=cap)
         out = tmp_path / f"g{cap}.pt"
         subprocess.run([sys.executable, str(script), str(out)], check=True, env=env, timeout=300)
         grads.append(torch.load(out))
@@ -517,6 +549,7 @@ torch.save({"idx": idx.cpu(), "out": out.detach().cpu(), "soft": soft.detach().c
     for name, extra in (("default", {}), ("variant", knobs)):
         env = {k: v for k, v in os.environ.items() if not k.startswith("DIBR_")}
         env.update(extra)
+        env["DIBR_B200_TUNING"] = "1"            # the one switch that makes the library read its tuning knobs
         out = tmp_path / f"{name}.pt"
         subprocess.run([sys.executable, str(script), str(out)], check=True, env=env, timeout=600)
         res.append(torch.load(out))

@@ -145,6 +145,50 @@ def test_cuda_matches_oracle_random(dname, shared, which):
 
 
 @pytest.mark.gpu
+@pytest.mark.parametrize("dname", ["f32", "f64"])
+@pytest.mark.parametrize("mode", ["rt", "tf"])
+@pytest.mark.parametrize("shared", [False, True])
+def test_cuda_camera_gradients_match_torch(dname, mode, shared):
+    """The reference differentiates through camera_proj / camera_rot / camera_trans / camera_transform (pure torch,
+    utils.py:160-172): the backward kernel returns those gradients too (warp-reduced sums), with or without a
+    gradient for the vertices.  F is not a multiple of 32, so warps straddle two views."""
+    from kaolin_b200.render.mesh import prepare_vertices
+    dtype = DT[dname]
+    B, V, F = 3, 400, 1003
+    verts, faces, rot, trans, proj = _random_scene(dtype, B, V, F, 21, "cuda")
+    if shared:
+        verts = verts[:1].contiguous()
+    m = torch.cat([rot.permute(0, 2, 1), -(trans.unsqueeze(1) @ rot.permute(0, 2, 1))], dim=1).contiguous()
+    for verts_grad in (True, False):
+        la = verts.clone().requires_grad_(verts_grad)
+        lb = verts.double().clone().requires_grad_(verts_grad)
+        pa = proj.clone().requires_grad_(True)
+        pb = proj.double().clone().requires_grad_(True)
+        if mode == "rt":
+            ca = [rot.clone().requires_grad_(True), trans.clone().requires_grad_(True)]
+            cb = [t.detach().double().clone().requires_grad_(True) for t in ca]
+            got = prepare_vertices(la, faces, pa, ca[0], ca[1])
+            ref = O.prepare_vertices(lb.expand(B, -1, -1), faces, pb, cb[0], cb[1])
+        else:
+            ca = [m.clone().requires_grad_(True)]
+            cb = [m.double().clone().requires_grad_(True)]
+            got = prepare_vertices(la, faces, pa, camera_transform=ca[0])
+            ref = O.prepare_vertices(lb.expand(B, -1, -1), faces, pb, camera_transform=cb[0])
+        g = torch.Generator().manual_seed(5)
+        ups = [torch.randn(o.shape, generator=g, dtype=torch.float64).to("cuda") for o in ref]
+        torch.autograd.backward(list(got), [u.to(dtype) for u in ups])
+        torch.autograd.backward(list(ref), ups)
+        tol = TOL_ILL[dname]
+        assert rel_close(pa.grad, pb.grad, tol), (pa.grad, pb.grad)
+        for a, b in zip(ca, cb):
+            assert a.grad.shape == a.shape and rel_close(a.grad, b.grad, tol)
+        if verts_grad:
+            assert rel_close(la.grad, lb.grad, tol)
+        else:
+            assert la.grad is None
+
+
+@pytest.mark.gpu
 def test_cuda_transform_equals_rot_trans():
     from kaolin_b200.render.mesh import prepare_vertices
     verts, faces, rot, trans, proj = _random_scene(torch.float64, 4, 300, 900, 3, "cuda")
@@ -170,8 +214,6 @@ def test_cuda_empty_and_errors():
         prepare_vertices(verts, torch.zeros(4, 4, dtype=torch.long, device="cuda"), proj, rot, trans)
     with pytest.raises(RuntimeError):
         prepare_vertices(verts.cpu(), faces.cpu(), proj.cpu(), rot.cpu(), trans.cpu())
-    with pytest.raises(RuntimeError):
-        prepare_vertices(verts, faces, proj, rot.clone().requires_grad_(True), trans)
     with pytest.raises(RuntimeError):
         prepare_vertices(verts.half(), faces, proj.half(), rot.half(), trans.half())
     bad = faces.clone()
