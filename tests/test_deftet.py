@@ -303,3 +303,17 @@ def test_cuda_gradients_only_for_requested_inputs():
     assert pl.grad is None and rl.grad is None and zl.grad is None
     assert fl.grad is not None and float(fl.grad.abs().sum()) > 0
     assert not idx.requires_grad
+
+
+@pytest.mark.gpu
+def test_cuda_backward_with_only_non_differentiable_inputs_requiring_grad():
+    """Only face_vertices_z (or pixel_coords / render_ranges) requires grad: the outputs require grad, backward is
+    called, and — like the reference, deftet.py:337 — returns None for those inputs without error."""
+    import kaolin_b200 as kal
+    img, z, pix, rr, feats = random_scene(1, 300, 100, 0.4, 4, torch.float32)
+    for which in range(3):
+        leaves = [t.clone().requires_grad_(i == which) for i, t in enumerate((pix, rr, z))]
+        out, idx = kal.render.mesh.deftet_sparse_render(leaves[0], leaves[1], leaves[2], img, feats, 6)
+        assert out.requires_grad
+        out.sum().backward()
+        assert all(t.grad is None for t in leaves)
