@@ -36,3 +36,30 @@ def golden(name):
     if name not in _CACHE:
         _CACHE[name] = np.load(os.path.join(GOLDEN_DIR, name + ".npz"))
     return _CACHE[name]
+
+
+def elem_close(a, b, rel, name, atol=1e-6):
+    """|a - b| <= rel * |b| + atol for EVERY element (north_star: "within 1e-5 / 1e-4 relative"); reports the
+    worst element.  `atol` covers values that cancel to ~0 (soft = 1 - prod(1 - prob) near 0)."""
+    import torch
+    a, b = a.detach().double().cpu(), b.detach().double().cpu()
+    assert a.shape == b.shape, (name, tuple(a.shape), tuple(b.shape))
+    if b.numel() == 0:
+        return
+    excess = ((a - b).abs() - (rel * b.abs() + atol)).reshape(-1)
+    excess = torch.where(torch.isnan(excess), torch.full_like(excess, float("inf")), excess)
+    both_nan = (torch.isnan(a) & torch.isnan(b)).reshape(-1)
+    excess = torch.where(both_nan, torch.full_like(excess, -1.0), excess)
+    worst = int(excess.argmax())
+    idx = tuple(int(i) for i in torch.unravel_index(torch.tensor(worst), b.shape))
+    assert float(excess[worst]) <= 0, (f"{name}: worst element {idx}: got {float(a.reshape(-1)[worst]):.9g}, "
+                                       f"reference {float(b.reshape(-1)[worst]):.9g} (rel {rel}, atol {atol})")
+
+
+def norm_close(a, b, rel, name):
+    """max|a - b| <= rel * max|b|: for gradients, which the reference accumulates with unordered atomics (its own
+    tests use rtol 1e-3 / atol 1e-2, test_dibr.py:351-394)."""
+    a, b = a.detach().double().cpu(), b.detach().double().cpu()
+    scale = max(1e-30, float(b.abs().max()))
+    err = float((a - b).abs().max())
+    assert err <= rel * scale, f"{name}: max abs err {err:.3e} > {rel} * {scale:.3e}"

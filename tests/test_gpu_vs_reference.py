@@ -8,6 +8,8 @@ import math
 import pytest
 import torch
 
+from helpers import elem_close
+
 pytestmark = pytest.mark.gpu
 
 
@@ -74,8 +76,9 @@ def full_pipeline_check(kal, O, backend, d, knum=30, boxlen=0.02, sigmainv=7000.
                                                                          multiplier, backend=backend)
     assert torch.equal(face_idx.cpu(), r_idx.cpu()), \
         f"face_idx mismatch on {(face_idx.cpu() != r_idx.cpu()).sum().item()} pixels"
-    rel_close(out_feat.cpu(), r_feat.cpu(), 1e-5, "features")
-    rel_close(soft.cpu(), r_soft.cpu(), 1e-4, "soft_mask")
+    # deterministic per-pixel outputs: ELEMENTWISE relative (|a-b| <= rel*|b| + tiny), worst pixel reported
+    elem_close(out_feat, r_feat, 1e-5, "features", atol=1e-6 if out_feat.dtype == torch.float32 else 1e-12)
+    elem_close(soft, r_soft, 1e-4, "soft_mask", atol=1e-6 if soft.dtype == torch.float32 else 1e-12)
     # ---- backward: raster and soft-mask gradients separately, then through autograd together
     r_gi, r_gf = O.rasterize_backward(mv(g_feat), r_idx, r_w, mv(img), mv(feats), eps, backend=backend,
                                       interpolated_features=r_feat)
