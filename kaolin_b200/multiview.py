@@ -98,6 +98,17 @@ class MultiViewOptimizer:
         # the per-face features do not depend on the vertices being optimised: gathered once
         self.face_features = vertex_features[faces].unsqueeze(0).expand(rot.shape[0], -1, -1, -1).contiguous()
         self.opt = torch.optim.Adam([self.vertices], lr=lr)
+        self.last_grad = None               # the all-reduced vertices.grad of the last step
+        self.launch_mode = "eager launches (optimizer step + NCCL all-reduce are not captured)"
+        self.time_all_reduce = False        # measurement: CUDA events around the collective on the compute stream
+        self._ar_events = []
+
+    def all_reduce_ms(self):
+        """Durations of the all-reduce calls made while ``time_all_reduce`` was set (synchronises)."""
+        torch.cuda.synchronize()
+        ms = [a.elapsed_time(b) for a, b in self._ar_events]
+        self._ar_events = []
+        return ms or [0.0]
 
     def loss(self):
         from .render.mesh import dibr_rasterization, prepare_vertices
@@ -119,6 +130,14 @@ class MultiViewOptimizer:
         self.opt.zero_grad(set_to_none=True)
         loss, _, _ = self.loss()
         loss.backward()
-        all_reduce_leaf_grads([self.vertices], group=self.group)
+        if self.time_all_reduce and self.vertices.is_cuda:
+            a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            a.record()
+            all_reduce_leaf_grads([self.vertices], group=self.group)
+            b.record()
+            self._ar_events.append((a, b))
+        else:
+            all_reduce_leaf_grads([self.vertices], group=self.group)
+        self.last_grad = self.vertices.grad
         self.opt.step()
         return loss.detach()
