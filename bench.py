@@ -1,5 +1,6 @@
 #!/usr/bin/env python
-"""bench.py — rasterized Mpixels/s (fwd+bwd of rasterize + dibr_soft_mask) on N B200s, one JSON line.
+"""bench.py — rasterized Mpixels/s (fwd+bwd of rasterize + dibr_soft_mask = dibr_rasterization) on N B200s, one JSON
+line.
 
   python bench.py [--gpus N] [--steps K] [--warmup W] [--workload c3] [--impl ours|reference]
 
@@ -217,6 +218,7 @@ class RenderWorkload:
         self.d_z, self.d_img = d["face_vertices_z"].to(dev), d["face_vertices_image"].to(dev)
         self.d_feat = [f.contiguous().to(dev) for f in d["face_features"]]
         self.d_nz = None if not self.culling else d["face_normals_z"].to(dev)
+        self.ones_nz = None if self.culling else torch.ones(self.B, self.F, device=dev)
         self.desc = {"total_views": self.total, "per_gpu_batch": self.B, "faces": self.F, "height": self.H,
                      "width": self.W, "channels": self.C, "knum": d["knum"], "sigmainv": d["sigmainv"],
                      "sharding": "the job's views are sharded contiguously over the ranks (multiview.shard_range); "
@@ -227,9 +229,11 @@ class RenderWorkload:
         import kaolin_b200 as kal
         d = self.d
         feats = feat if len(feat) > 1 else feat[0]
-        valid = None if nz is None else (nz >= 0.)
-        out, face_idx = kal.render.mesh.rasterize(self.H, self.W, z, img, feats, valid, d["multiplier"], d["eps"])
-        soft = kal.render.mesh.dibr_soft_mask(img, face_idx, d["sigmainv"], d["boxlen"], d["knum"], d["multiplier"])
+        # dibr_rasterization = rasterize(valid_faces = normals_z >= 0) + dibr_soft_mask (dibr.py:119-209); workloads
+        # without culling pass normals_z = 1 (every face valid)
+        out, soft, face_idx = kal.render.mesh.dibr_rasterization(
+            self.H, self.W, z, img, feats, self.ones_nz if nz is None else nz, d["sigmainv"], d["boxlen"], d["knum"],
+            d["multiplier"], d["eps"])
         outs = list(out) if isinstance(out, tuple) else [out]
         self.torch.autograd.backward(outs + [soft], self.g_feats + [self.g_soft])
         return outs, soft, face_idx

@@ -223,6 +223,47 @@ int dibr_soft_mask_bwd_fused_f64(const double* grad_soft, const double* soft, co
                                  void* ws, size_t ws_bytes, int bins_ready, void* stream);
 
 /* ---------------------------------------------------------------------------------------------
+ * dibr_rasterization in ONE call — kaolin/render/mesh/dibr.py:119-209:
+ *     rasterize(h, w, z, img, feats, valid_faces = face_normals_z >= 0, multiplier, eps) followed by
+ *     dibr_soft_mask(img, face_idx, sigmainv, boxlen, knum, multiplier)
+ *  Both face-list sets (the rasterizer's: tight bboxes of the valid faces; the soft mask's: bboxes enlarged by
+ *  boxlen * multiplier, all faces) are built from a single read of the coordinates — one memset and three binning
+ *  launches instead of two and six — then the two per-tile kernels run.  Results are bit-identical to the two
+ *  separate calls (the reference's own requirement, tests/python/kaolin/render/mesh/test_dibr.py:527-529).
+ *  `normals_z` (B,F): valid = normals_z >= 0, evaluated in the setup kernel; or `valid` (B,F) uint8 (both NULL = all
+ *  faces).  feats / out_feats: HOST arrays of n_feat device pointers, channels: HOST array (as in _multi).
+ *  ws: dibr_rasterization_workspace_bytes(B, B*F, H, W, keep_pairs) bytes.  keep_pairs != 0: the soft-mask kernel also
+ *  logs its evaluated pairs into `ws` for the backward call below (which must then get the same `ws`, untouched).
+ *  _bwd: grad_outs (HOST array; NULL or all-NULL = no upstream feature gradient) and grad_soft (NULL = none) ->
+ *  grad_img (B,F,3,2) = the SUM of both paths' gradients, accumulated in place by both kernels (zero-filled once by
+ *  the library), and grad_feats.  bins_ready: 6 = `ws` comes from the forward call with keep_pairs (bins + log);
+ *  5 = bins only; 0 = `ws` is scratch of dibr_soft_mask_workspace_bytes(..., 0, ...) bytes, bin again.
+ */
+size_t dibr_rasterization_workspace_bytes(int batch_size, int64_t total_faces, int height, int width, int keep_pairs);
+int dibr_rasterization_fwd_fused_f32(const float* z, const float* img, const float* const* feats,
+                                     const int* channels, int n_feat, const float* normals_z, const uint8_t* valid,
+                                     int B, int F, int H, int W, double multiplier, float eps, float sigmainv,
+                                     double boxlen, int knum, float* const* out_feats, int64_t* out_face_idx,
+                                     float* soft, void* ws, size_t ws_bytes, int keep_pairs, void* stream);
+int dibr_rasterization_fwd_fused_f64(const double* z, const double* img, const double* const* feats,
+                                     const int* channels, int n_feat, const double* normals_z, const uint8_t* valid,
+                                     int B, int F, int H, int W, double multiplier, float eps, float sigmainv,
+                                     double boxlen, int knum, double* const* out_feats, int64_t* out_face_idx,
+                                     double* soft, void* ws, size_t ws_bytes, int keep_pairs, void* stream);
+int dibr_rasterization_bwd_fused_f32(const float* const* grad_outs, const float* grad_soft, const float* soft,
+                                     const int64_t* face_idx, const float* img, const float* const* feats,
+                                     const int* channels, int n_feat, int B, int F, int H, int W, double multiplier,
+                                     float eps, float sigmainv, double boxlen, int knum, float* grad_img,
+                                     float* const* grad_feats, void* ws, size_t ws_bytes, int bins_ready,
+                                     void* stream);
+int dibr_rasterization_bwd_fused_f64(const double* const* grad_outs, const double* grad_soft, const double* soft,
+                                     const int64_t* face_idx, const double* img, const double* const* feats,
+                                     const int* channels, int n_feat, int B, int F, int H, int W, double multiplier,
+                                     float eps, float sigmainv, double boxlen, int knum, double* grad_img,
+                                     double* const* grad_feats, void* ws, size_t ws_bytes, int bins_ready,
+                                     void* stream);
+
+/* ---------------------------------------------------------------------------------------------
  * prepare_vertices — the producer of the path's inputs (first "next" row).
  *  Replaces the torch composition of kaolin/render/mesh/utils.py:128-175:
  *    camera transform      rotate_translate_points (kaolin/render/camera/legacy.py:22-37) when rot/trans are

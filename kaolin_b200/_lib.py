@@ -20,7 +20,7 @@ SOURCES = ["dibr_c_abi.cu"]
 HEADERS = ["dibr_common.cuh", "dibr_binning.cuh", "dibr_raster_fwd.cuh", "dibr_raster_bwd.cuh",
            "dibr_soft_mask.cuh", "dibr_prepare.cuh", "dibr_texture.cuh", "dibr_losses.cuh", "dibr_deftet.cuh"]
 NVCC_FLAGS = ["-O3", "-std=c++17", "-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo",
-              "-cudart", "shared", "-Xcompiler", "-fPIC,-fvisibility=hidden"]
+              "-cudart", "shared", "-Xcompiler", "-fPIC,-fvisibility=hidden", "-ldl"]
 
 _lock = threading.Lock()
 _lib = None
@@ -41,6 +41,10 @@ _TYPED = {
     "dibr_soft_mask_forward": [c_p, c_p, c_p, c_i, c_i, c_i, c_i, c_f, c_i, c_f, c_p, c_p, c_p, c_p, c_p, c_sz, c_p],
     "dibr_soft_mask_backward": [c_p, c_p, c_p, c_p, c_p, c_p, c_p, c_i, c_i, c_i, c_i, c_i, c_f, c_f, c_p, c_p],
     "dibr_soft_mask_bwd_fused": [c_p, c_p, c_p, c_p, c_i, c_i, c_i, c_i, c_f, c_d, c_i, c_d, c_p, c_p, c_sz, c_i, c_p],
+    "dibr_rasterization_fwd_fused": [c_p, c_p, c_p, c_p, c_i, c_p, c_p, c_i, c_i, c_i, c_i, c_d, c_f, c_f, c_d, c_i, c_p,
+                                     c_p, c_p, c_p, c_sz, c_i, c_p],
+    "dibr_rasterization_bwd_fused": [c_p, c_p, c_p, c_p, c_p, c_p, c_p, c_i, c_i, c_i, c_i, c_i, c_d, c_f, c_f, c_d,
+                                     c_i, c_p, c_p, c_p, c_sz, c_i, c_p],
     "dibr_prepare_vertices_fwd": [c_p, c_p, c_p, c_p, c_p, c_p, c_i, c_i, c_i, c_i, c_p, c_p, c_p, c_p],
     "dibr_prepare_vertices_bwd": [c_p, c_p, c_p, c_p, c_p, c_p, c_p, c_p, c_p, c_i, c_i, c_i, c_i, c_p, c_p, c_p, c_p,
                                   c_p, c_p],
@@ -56,7 +60,7 @@ _TYPED = {
 EXPORTED_SYMBOLS = (["dibr_abi_version", "dibr_error_string", "dibr_last_cuda_error", "dibr_workspace_bytes",
                      "dibr_kernel_launch_count", "dibr_reset_kernel_launch_count", "dibr_profile_next_launch",
                      "dibr_mask_iou_workspace_bytes", "dibr_deftet_workspace_bytes",
-                     "dibr_soft_mask_workspace_bytes"] +
+                     "dibr_soft_mask_workspace_bytes", "dibr_rasterization_workspace_bytes"] +
                     [f"{n}_{s}" for n in _TYPED for s in ("f32", "f64")])
 
 
@@ -107,6 +111,8 @@ def load():
         lib.dibr_mask_iou_workspace_bytes.argtypes = [c_i, c_i64, c_i]
         lib.dibr_soft_mask_workspace_bytes.restype = c_sz
         lib.dibr_soft_mask_workspace_bytes.argtypes = [c_i, c_i64, c_i, c_i, c_i, c_i]
+        lib.dibr_rasterization_workspace_bytes.restype = c_sz
+        lib.dibr_rasterization_workspace_bytes.argtypes = [c_i, c_i64, c_i, c_i, c_i]
         lib.dibr_deftet_workspace_bytes.restype = c_sz
         lib.dibr_deftet_workspace_bytes.argtypes = [c_i, c_i64]
         lib.dibr_profile_next_launch.restype = c_i

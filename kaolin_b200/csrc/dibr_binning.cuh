@@ -6,8 +6,15 @@
 //         with one coalesced pass: multiplied coordinates -> bbox -> EXACT inclusive pixel range of the
 //         reference's half-open float test (rasterization_cuda.cu:115) -> 8-byte range record, and
 //         counts the face into every 16x16 tile it can touch.
-// K1b     scan        : per-view exclusive scan of the tile counters, segment base by one atomic.
-// K1c     fill        : scatter face ids into the per-tile lists.
+// K1b     scan        : list offsets.  Every 1024 counters are scanned by their own CTA, whose segment base comes from
+//         one atomicAdd on the allocation cursor: a tile's list only has to be contiguous in itself, not with its
+//         neighbours', so no cross-CTA prefix (no look-back) is needed and a view's counters are spread over
+//         several SMs instead of one.  Also counts, per view, the tiles in every log2 weight bucket.
+// K1c     fill        : scatter face ids into the per-tile lists, and write each view's tile launch order
+//         (heaviest bucket first) from the bucket counts.
+// One call can build TWO sets of lists from a single read of the coordinates (`DUAL`): the rasterizer's (tight
+// bboxes, valid faces only) and the soft mask's (bboxes enlarged by boxlen * multiplier, all faces) — the
+// dibr_rasterization entry point; 3 launches + 1 memset instead of 6 + 2.
 //
 // Two levels.  A face touching at most PAIRS_PER_FACE (16) tiles is listed in each of them; otherwise it is
 // listed in the coarse cells (4 x 4 tiles) it touches if those are at most 16; otherwise it goes to a per-view
@@ -30,7 +37,11 @@ struct BinLists {
   int* large_count;   // [B]
   int* alloc_cursor;  // [1]
   int* tile_order;    // [B*tiles_per_view] per view: its tiles sorted by decreasing candidate count (log2 buckets)
+  int* bucket_hist;   // [B*NBUCKET] tiles per weight bucket (zeroed with the counters)
+  int* bucket_cursor; // [B*NBUCKET] placement cursors of fill's ordering step (zeroed with the counters)
 };
+constexpr int NBUCKET = 33;            // floor(log2(weight)) + 1, weight < 2^32
+struct BinLists2 { BinLists l[2]; };   // [0] rasterizer, [1] soft mask (or one set twice)
 
 constexpr int MAX_FEATS = 8;
 template <typename T>
@@ -62,6 +73,7 @@ struct SetupParams {
   const T* img;            // (Ntot,3,2)
   const T* bbox_in;        // (Ntot,4) already multiplied/enlarged, or nullptr => computed here
   const uint8_t* valid;    // (Ntot) or nullptr
+  const T* normals_z;      // (Ntot) or nullptr: valid = normals_z >= 0 (dibr_rasterization, dibr.py:195)
   T coord_mult;            // img is multiplied by this (1 when already multiplied)
   int premultiplied;
   T margin;                // bbox enlargement in multiplied units (0 for the rasterizer)
@@ -197,16 +209,38 @@ __device__ __forceinline__ void bin_faces_warp(const bool has, const int b, cons
   }
 }
 
+// bbox (multiplied coordinates) -> exact inclusive pixel range of the reference's half-open test, record + tile rect
 template <typename T>
-__global__ void __launch_bounds__(256) setup_count_kernel(SetupParams<T> sp, FaceLayout fl, Geometry geo,
-                                                          BinLists L) {
+__device__ __forceinline__ bool face_pixel_range(const T xmin, const T ymin, const T xmax, const T ymax,
+                                                 const float pix_mult, const Geometry& geo, uint2& rec, int& tx0,
+                                                 int& tx1, int& ty0, int& ty1) {
+  const float sx = pix_scale(pix_mult, geo.W), sy = pix_scale(pix_mult, geo.H);
+  int ix0, ix1, ky0, ky1;
+  pass_range<T>(sx, geo.W, xmin, xmax, ix0, ix1);
+  pass_range<T>(sy, geo.H, ymin, ymax, ky0, ky1);      // k counts rows from the bottom
+  if (ix0 > ix1 || ky0 > ky1) return false;
+  const int jy0 = geo.H - 1 - ky1, jy1 = geo.H - 1 - ky0;
+  rec = pack_range(ix0, ix1, jy0, jy1);
+  tx0 = ix0 / TILE; tx1 = ix1 / TILE; ty0 = jy0 / TILE; ty1 = jy1 / TILE;
+  return true;
+}
+
+// DUAL = false: one set of lists (L.l[0]) with sp.margin / sp.valid as given.  DUAL = true: L.l[0] = rasterizer lists
+// (margin 0, only faces with valid != 0 / normals_z >= 0), L.l[1] = soft-mask lists (margin soft_margin, ALL
+// faces: dibr.py:75-117 takes no valid mask), both from one read of the coordinates.
+template <typename T, bool DUAL>
+__global__ void __launch_bounds__(256) setup_count_kernel(SetupParams<T> sp, const T soft_margin, FaceLayout fl,
+                                                          Geometry geo, BinLists2 L) {
   const int64_t g = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
   const bool in_range = g < fl.Ntot;                    // no early exit: the binning below is warp-collective
-  uint2 rec = empty_range();
-  const bool is_valid = in_range && (sp.valid ? (sp.valid[g] != 0) : true);
+  bool is_valid = in_range;
+  if (in_range && sp.valid) is_valid = sp.valid[g] != 0;
+  if (in_range && sp.normals_z) is_valid = sp.normals_z[g] >= (T)0;     // dibr.py:195 `face_normals_z >= 0.`
+  uint2 rec = empty_range(), rec2 = empty_range();
   int b = 0, tx0 = 0, tx1 = -1, ty0 = 0, ty1 = -1;
-  bool has = false;
-  if (is_valid) {
+  int sx0 = 0, sx1 = -1, sy0 = 0, sy1 = -1;
+  bool has = false, has2 = false;
+  if (DUAL ? in_range : is_valid) {
     T xmin, ymin, xmax, ymax;
     if (sp.bbox_in) {
       const T* bb = sp.bbox_in + g * 4;
@@ -218,24 +252,29 @@ __global__ void __launch_bounds__(256) setup_count_kernel(SetupParams<T> sp, Fac
       xmax = max_nan(max_nan(p[0], p[2]), p[4]);
       ymin = min_nan(min_nan(p[1], p[3]), p[5]);
       ymax = max_nan(max_nan(p[1], p[3]), p[5]);
+    }
+    if (DUAL) {
+      if (is_valid) has = face_pixel_range<T>(xmin, ymin, xmax, ymax, sp.pix_mult, geo, rec, tx0, tx1, ty0, ty1);
       // dibr.py:36-38: points_min - boxlen*multiplier, points_max + boxlen*multiplier
-      xmin = RN<T>::sub(xmin, sp.margin); ymin = RN<T>::sub(ymin, sp.margin);
-      xmax = RN<T>::add(xmax, sp.margin); ymax = RN<T>::add(ymax, sp.margin);
+      has2 = face_pixel_range<T>(RN<T>::sub(xmin, soft_margin), RN<T>::sub(ymin, soft_margin),
+                                 RN<T>::add(xmax, soft_margin), RN<T>::add(ymax, soft_margin), sp.pix_mult, geo,
+                                 rec2, sx0, sx1, sy0, sy1);
+    } else {
+      if (!sp.bbox_in) {
+        xmin = RN<T>::sub(xmin, sp.margin); ymin = RN<T>::sub(ymin, sp.margin);
+        xmax = RN<T>::add(xmax, sp.margin); ymax = RN<T>::add(ymax, sp.margin);
+      }
+      has = face_pixel_range<T>(xmin, ymin, xmax, ymax, sp.pix_mult, geo, rec, tx0, tx1, ty0, ty1);
     }
-    const float sx = pix_scale(sp.pix_mult, geo.W), sy = pix_scale(sp.pix_mult, geo.H);
-    int ix0, ix1, ky0, ky1;
-    pass_range<T>(sx, geo.W, xmin, xmax, ix0, ix1);
-    pass_range<T>(sy, geo.H, ymin, ymax, ky0, ky1);      // k counts rows from the bottom
-    if (ix0 <= ix1 && ky0 <= ky1) {
-      const int jy0 = geo.H - 1 - ky1, jy1 = geo.H - 1 - ky0;
-      rec = pack_range(ix0, ix1, jy0, jy1);
-      b = fl.view_of(g);
-      tx0 = ix0 / TILE; tx1 = ix1 / TILE; ty0 = jy0 / TILE; ty1 = jy1 / TILE;
-      has = true;
-    }
+    if (has || has2) b = fl.view_of(g);
   }
-  bin_faces_warp<false>(has, b, has ? (int)(g - fl.base(b)) : 0, tx0, tx1, ty0, ty1, g, fl, geo, L);
-  if (in_range) L.ranges[g] = rec;
+  const int local = (has || has2) ? (int)(g - fl.base(b)) : 0;
+  bin_faces_warp<false>(has, b, local, tx0, tx1, ty0, ty1, g, fl, geo, L.l[0]);
+  if (in_range) L.l[0].ranges[g] = rec;
+  if (DUAL) {
+    bin_faces_warp<false>(has2, b, local, sx0, sx1, sy0, sy1, g, fl, geo, L.l[1]);
+    if (in_range) L.l[1].ranges[g] = rec2;
+  }
 }
 
 // scheduling weight of a tile: its own list + a share of the enclosing coarse cell's list (filtered by the consumer)
@@ -245,82 +284,82 @@ __device__ __forceinline__ int tile_weight_bucket(const int* cnt, const Geometry
   return w > 0 ? 32 - __clz(w) : 0;
 }
 
-// one CTA per view
-__global__ void __launch_bounds__(1024) scan_kernel(Geometry geo, BinLists L) {
+// grid (chunks of SCAN_CHUNK counters, views, list sets): see the file header (K1b)
+constexpr int SCAN_CHUNK = 1024;
+__global__ void __launch_bounds__(SCAN_CHUNK) scan_kernel(Geometry geo, BinLists2 LL) {
   __shared__ int warp_sums[32];
   __shared__ int s_base;
-  const int b = blockIdx.x;
+  __shared__ int hist[NBUCKET];
+  const BinLists& L = LL.l[blockIdx.z];
+  const int b = blockIdx.y;
   const int T = geo.slots_per_view;
   const int* cnt = L.tile_count + (int64_t)b * T;
-  int* off = L.tile_offset + (int64_t)b * T;
-  int* cur = L.tile_cursor + (int64_t)b * T;
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-  // pass 1: view total
-  int local = 0;
-  for (int t = threadIdx.x; t < T; t += blockDim.x) local += cnt[t];
+  const int t = blockIdx.x * SCAN_CHUNK + threadIdx.x;
+  if (threadIdx.x < NBUCKET) hist[threadIdx.x] = 0;
+  const int c = (t < T) ? cnt[t] : 0;
+  int incl = c;
 #pragma unroll
-  for (int o = 16; o > 0; o >>= 1) local += __shfl_xor_sync(0xffffffffu, local, o);
-  if (lane == 0) warp_sums[warp] = local;
+  for (int o = 1; o < 32; o <<= 1) {
+    const int n = __shfl_up_sync(0xffffffffu, incl, o);
+    if (lane >= o) incl += n;
+  }
+  if (lane == 31) warp_sums[warp] = incl;
   __syncthreads();
   if (warp == 0) {
-    int v = warp_sums[lane];
-#pragma unroll
-    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
-    if (lane == 0) s_base = atomicAdd(L.alloc_cursor, v);
-  }
-  __syncthreads();
-  int running = s_base;
-  // pass 2: exclusive scan in chunks of blockDim.x
-  for (int t0 = 0; t0 < T; t0 += blockDim.x) {
-    const int t = t0 + threadIdx.x;
-    const int c = (t < T) ? cnt[t] : 0;
-    int incl = c;
+    const int v = warp_sums[lane];
+    int wi = v;
 #pragma unroll
     for (int o = 1; o < 32; o <<= 1) {
-      const int n = __shfl_up_sync(0xffffffffu, incl, o);
-      if (lane >= o) incl += n;
+      const int n = __shfl_up_sync(0xffffffffu, wi, o);
+      if (lane >= o) wi += n;
     }
-    __syncthreads();                       // warp_sums reuse
-    if (lane == 31) warp_sums[warp] = incl;
-    __syncthreads();
-    int wprefix = 0, total = 0;
-    {
-      const int v = warp_sums[lane];
-      int wi = v;
-#pragma unroll
-      for (int o = 1; o < 32; o <<= 1) {
-        const int n = __shfl_up_sync(0xffffffffu, wi, o);
-        if (lane >= o) wi += n;
-      }
-      wprefix = __shfl_sync(0xffffffffu, wi - v, warp);
-      total = __shfl_sync(0xffffffffu, wi, 31);
-    }
-    if (t < T) {
-      const int o = running + wprefix + incl - c;
-      off[t] = o;
-      cur[t] = o;
-    }
-    running += total;
+    warp_sums[lane] = wi - v;                                     // exclusive prefix of the warp totals
+    if (lane == 31) s_base = wi > 0 ? atomicAdd(L.alloc_cursor, wi) : 0;    // this chunk's segment of `pairs`
   }
-  // pass 3: launch order of the view's tiles for the per-tile kernels — heaviest first (longest-processing-time
-  // scheduling: a few tiles hold hundreds of sliver faces and would otherwise finish long after the rest of the
-  // grid).  Buckets of floor(log2(weight)) + 1; the order inside a bucket is arbitrary (it only affects scheduling).
-  __shared__ int hist[33], bbase[33];
-  if (threadIdx.x < 33) hist[threadIdx.x] = 0;
+  // bucket counts of the chunk's fine tiles (heaviest-first launch order of the per-tile kernels: a few tiles hold
+  // hundreds of sliver faces and would otherwise finish long after the rest of the grid)
+  if (t < geo.tiles_per_view) atomicAdd(&hist[tile_weight_bucket(cnt, geo, t)], 1);
   __syncthreads();
-  int* order = L.tile_order + (int64_t)b * geo.tiles_per_view;
-  for (int t = threadIdx.x; t < geo.tiles_per_view; t += blockDim.x)
-    atomicAdd(&hist[tile_weight_bucket(cnt, geo, t)], 1);
-  __syncthreads();
-  if (threadIdx.x == 0) {
-    int run = 0;
-    for (int k = 32; k >= 0; --k) { bbase[k] = run; run += hist[k]; hist[k] = 0; }
+  if (t < T) {
+    const int o = s_base + warp_sums[warp] + incl - c;
+    L.tile_offset[(int64_t)b * T + t] = o;
+    L.tile_cursor[(int64_t)b * T + t] = o;
   }
-  __syncthreads();
-  for (int t = threadIdx.x; t < geo.tiles_per_view; t += blockDim.x) {
-    const int k = tile_weight_bucket(cnt, geo, t);
-    order[bbase[k] + atomicAdd(&hist[k], 1)] = (t % geo.tiles_x) | ((t / geo.tiles_x) << 16);   // tx | ty << 16
+  if (threadIdx.x < NBUCKET && hist[threadIdx.x] > 0)
+    atomicAdd(&L.bucket_hist[b * NBUCKET + threadIdx.x], hist[threadIdx.x]);
+}
+inline dim3 scan_grid(const Geometry& geo, int n_sets) {
+  return dim3((unsigned)((geo.slots_per_view + SCAN_CHUNK - 1) / SCAN_CHUNK), (unsigned)geo.B, (unsigned)n_sets);
+}
+
+// Ordering step of fill: thread = (view, tile).  Its bucket's first position = the number of tiles in heavier buckets
+// (33 cached loads); lanes of a warp that share (view, bucket) — 32 neighbouring tiles usually do — reserve their
+// positions with one atomic.  Entries are packed tile coordinates (tx | ty << 16); the order inside a bucket is
+// arbitrary (it only affects scheduling).
+__device__ __forceinline__ void place_tile_order(const Geometry& geo, const BinLists& L, const int64_t i) {
+  const int64_t n = (int64_t)geo.B * geo.tiles_per_view;
+  const bool act = i < n;
+  const int b = act ? (int)(i / geo.tiles_per_view) : 0;
+  const int t = act ? (int)(i - (int64_t)b * geo.tiles_per_view) : 0;
+  int key = -1 - (int)(threadIdx.x & 31);
+  int k = 0;
+  if (act) {
+    k = tile_weight_bucket(L.tile_count + (int64_t)b * geo.slots_per_view, geo, t);
+    key = b * NBUCKET + k;
   }
+  const unsigned peers = __match_any_sync(0xffffffffu, key);
+  if (!act) return;
+  const int lane = threadIdx.x & 31;
+  const int leader = __ffs(peers) - 1;
+  int pos = 0;
+  if (lane == leader) {
+    int base = 0;
+    for (int h = k + 1; h < NBUCKET; ++h) base += __ldg(L.bucket_hist + b * NBUCKET + h);
+    pos = base + atomicAdd(&L.bucket_cursor[key], __popc(peers));
+  }
+  pos = __shfl_sync(peers, pos, leader) + __popc(peers & ((1u << lane) - 1u));
+  L.tile_order[(int64_t)b * geo.tiles_per_view + pos] = (t % geo.tiles_x) | ((t / geo.tiles_x) << 16);
 }
 
 // Grid of the per-tile kernels: x = view, (y, z) = rank of the tile in its view's order — consecutive CTAs take the
@@ -341,21 +380,35 @@ __device__ __forceinline__ bool scheduled_tile(const BinLists& L, const Geometry
   return true;
 }
 
-__global__ void __launch_bounds__(256) fill_kernel(FaceLayout fl, Geometry geo, BinLists L) {
+// grid covers max(Ntot, B * tiles_per_view) threads: thread = face (scatter) and thread = (view, tile) (order)
+template <bool DUAL>
+__global__ void __launch_bounds__(256) fill_kernel(FaceLayout fl, Geometry geo, BinLists2 LL) {
   const int64_t g = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-  bool has = false;
-  int b = 0, local = 0, tx0 = 0, tx1 = -1, ty0 = 0, ty1 = -1;
-  if (g < fl.Ntot) {
-    const uint2 r = L.ranges[g];
-    if (!range_empty(r)) {
-      has = true;
-      tx0 = (int)(r.x & 0xffffu) / TILE; tx1 = (int)(r.x >> 16) / TILE;
-      ty0 = (int)(r.y & 0xffffu) / TILE; ty1 = (int)(r.y >> 16) / TILE;
-      b = fl.view_of(g);
-      local = (int)(g - fl.base(b));
+#pragma unroll
+  for (int set = 0; set < (DUAL ? 2 : 1); ++set) {
+    const BinLists& L = LL.l[set];
+    place_tile_order(geo, L, g);
+    if ((int64_t)blockIdx.x * blockDim.x >= fl.Ntot) continue;      // CTA-uniform: this CTA holds no faces
+    bool has = false;
+    int b = 0, local = 0, tx0 = 0, tx1 = -1, ty0 = 0, ty1 = -1;
+    if (g < fl.Ntot) {
+      const uint2 r = L.ranges[g];
+      if (!range_empty(r)) {
+        has = true;
+        tx0 = (int)(r.x & 0xffffu) / TILE; tx1 = (int)(r.x >> 16) / TILE;
+        ty0 = (int)(r.y & 0xffffu) / TILE; ty1 = (int)(r.y >> 16) / TILE;
+        b = fl.view_of(g);
+        local = (int)(g - fl.base(b));
+      }
     }
+    bin_faces_warp<true>(has, b, local, tx0, tx1, ty0, ty1, g, fl, geo, L);
   }
-  bin_faces_warp<true>(has, b, local, tx0, tx1, ty0, ty1, g, fl, geo, L);
+}
+inline unsigned binning_blocks(const FaceLayout& fl, const Geometry& geo, bool with_order) {
+  int64_t n = fl.Ntot;
+  const int64_t tiles = (int64_t)geo.B * geo.tiles_per_view;
+  if (with_order && tiles > n) n = tiles;
+  return (unsigned)((n + 255) / 256);
 }
 
 // The candidate sources of one 16x16 tile: the faces binned to the tile itself (all touch it), those binned to

@@ -10,6 +10,8 @@
 #include "dibr_losses.cuh"
 #include "dibr_deftet.cuh"
 
+#include <nvtx3/nvToolsExt.h>       // header-only NVTX v3: ranges cost a load + branch unless a tool (nsys, ncu) is attached
+
 #include <atomic>
 #include <cmath>
 #include <cstdio>
@@ -45,9 +47,16 @@ inline int cuda_fail(cudaError_t e, const char* where) {
 // Process-wide (forward runs on the Python thread, backward on the autograd thread); measurement only.
 std::atomic<int> g_prof_kernel{-1};
 std::atomic<cudaEvent_t> g_prof_start{nullptr}, g_prof_stop{nullptr};
+const char* const kKernelNames[DIBR_KERNEL_COUNT] = {
+    "dibr/setup_count", "dibr/scan", "dibr/fill", "dibr/raster_fwd", "dibr/raster_bwd", "dibr/soft_mask_fwd",
+    "dibr/soft_mask_bwd", "dibr/prepare_vertices_fwd", "dibr/prepare_vertices_bwd", "dibr/texture_mapping_fwd",
+    "dibr/texture_mapping_bwd", "dibr/mask_iou_fwd", "dibr/mask_iou_bwd", "dibr/deftet_fwd", "dibr/deftet_bwd"};
+// Every kernel launch site sits in one of these scopes: an NVTX range named after the kernel (so that an nsys / ncu
+// timeline of a training step reads "dibr/raster_fwd ..." instead of mangled template names) + the timing hook.
 struct ProfScope {
-  bool on; cudaStream_t s;
-  ProfScope(int id, cudaStream_t st) : on(false), s(st) {
+  bool on, nvtx; cudaStream_t s;
+  ProfScope(int id, cudaStream_t st) : on(false), nvtx(id >= 0 && id < DIBR_KERNEL_COUNT), s(st) {
+    if (nvtx) nvtxRangePushA(kKernelNames[id]);
     int expect = id;
     if (g_prof_kernel.load(std::memory_order_acquire) == id &&
         g_prof_kernel.compare_exchange_strong(expect, -2)) {          // claim it (one launch only)
@@ -55,7 +64,10 @@ struct ProfScope {
       cudaEventRecord(g_prof_start.load(), s);
     }
   }
-  ~ProfScope() { if (on) { cudaEventRecord(g_prof_stop.load(), s); g_prof_kernel.store(-1, std::memory_order_release); } }
+  ~ProfScope() {
+    if (on) { cudaEventRecord(g_prof_stop.load(), s); g_prof_kernel.store(-1, std::memory_order_release); }
+    if (nvtx) nvtxRangePop();
+  }
 };
 
 inline size_t align_up(size_t v, size_t a = 256) { return (v + a - 1) / a * a; }
@@ -67,21 +79,29 @@ inline const char* tuning_env(const char* name) {
   return on ? getenv(name) : nullptr;
 }
 
-// Workspace carving: two BinLists (index 0 = rasterizer, 1 = soft mask) — each entry point uses one.
+// Workspace carving.  One BinLists = a ZERO part (counters: one memset) and a REST part (offsets, order, ranges, lists).
+// Standalone calls use [zero | rest].  The dibr_rasterization call (and every soft-mask call, with an empty rasterizer
+// part) uses the FUSED layout [soft zero | raster zero | log zero | soft rest | raster rest | log rest]: all
+// counters of both list sets and of the pair log are contiguous and are cleared by ONE memset.
 struct WsLayout {
   size_t ranges, tile_count, tile_offset, tile_cursor, pairs, large_list, large_count, alloc_cursor, tile_order;
-  size_t zero_begin, zero_end;     // [tile_count | large_count | alloc_cursor] are contiguous => one memset
+  size_t bucket_hist, bucket_cursor;
+  size_t zero_begin, zero_end;     // [tile_count | large_count | alloc_cursor | bucket_hist | bucket_cursor]
   size_t total;
 };
-WsLayout ws_layout(int B, int64_t Ntot, const Geometry& geo) {
-  WsLayout w;
+size_t ws_zero_part(WsLayout& w, int B, const Geometry& geo, size_t o) {
   const size_t bt = (size_t)B * geo.slots_per_view;
-  size_t o = 0;
   w.zero_begin = o;
   w.tile_count = o;  o = align_up(o + bt * sizeof(int));
   w.large_count = o; o = align_up(o + (size_t)B * sizeof(int));
   w.alloc_cursor = o; o = align_up(o + sizeof(int));
+  w.bucket_hist = o; o = align_up(o + (size_t)B * NBUCKET * sizeof(int));
+  w.bucket_cursor = o; o = align_up(o + (size_t)B * NBUCKET * sizeof(int));
   w.zero_end = o;
+  return o;
+}
+size_t ws_rest_part(WsLayout& w, int B, int64_t Ntot, const Geometry& geo, size_t o) {
+  const size_t bt = (size_t)B * geo.slots_per_view;
   w.tile_offset = o; o = align_up(o + bt * sizeof(int));
   w.tile_cursor = o; o = align_up(o + bt * sizeof(int));
   w.tile_order = o;  o = align_up(o + (size_t)B * geo.tiles_per_view * sizeof(int));
@@ -89,6 +109,11 @@ WsLayout ws_layout(int B, int64_t Ntot, const Geometry& geo) {
   w.large_list = o;  o = align_up(o + (size_t)Ntot * sizeof(int));
   w.pairs = o;       o = align_up(o + (size_t)Ntot * PAIRS_PER_FACE * sizeof(int));
   w.total = o;
+  return o;
+}
+WsLayout ws_layout(int B, int64_t Ntot, const Geometry& geo) {
+  WsLayout w;
+  ws_rest_part(w, B, Ntot, geo, ws_zero_part(w, B, geo, 0));
   return w;
 }
 BinLists carve(void* ws, const WsLayout& w) {
@@ -103,6 +128,8 @@ BinLists carve(void* ws, const WsLayout& w) {
   L.large_count = reinterpret_cast<int*>(p + w.large_count);
   L.alloc_cursor = reinterpret_cast<int*>(p + w.alloc_cursor);
   L.tile_order = reinterpret_cast<int*>(p + w.tile_order);
+  L.bucket_hist = reinterpret_cast<int*>(p + w.bucket_hist);
+  L.bucket_cursor = reinterpret_cast<int*>(p + w.bucket_cursor);
   return L;
 }
 
@@ -115,7 +142,7 @@ int check_dims(int B, int64_t Ntot, int H, int W) {
   return DIBR_OK;
 }
 
-// K0 + K1: ranges, counts, scan, fill.  3 kernels + 1 memset.
+// K0 + K1 on one set of lists: ranges, counts, scan, fill (+ tile order).  3 kernels + 1 memset.
 template <typename T>
 int run_binning(const SetupParams<T>& sp, const FaceLayout& fl, const Geometry& geo, void* ws, size_t ws_bytes,
                 cudaStream_t s, BinLists& L) {
@@ -123,17 +150,16 @@ int run_binning(const SetupParams<T>& sp, const FaceLayout& fl, const Geometry& 
   if (!ws || ws_bytes < w.total) return DIBR_ERR_WORKSPACE;
   L = carve(ws, w);
   CUDA_TRY(cudaMemsetAsync(static_cast<unsigned char*>(ws) + w.zero_begin, 0, w.zero_end - w.zero_begin, s));
-  const unsigned nb = (unsigned)((fl.Ntot + 255) / 256);
+  BinLists2 LL; LL.l[0] = L; LL.l[1] = L;
+  const unsigned nb = binning_blocks(fl, geo, false);
   if (nb > 0) {
-    { ProfScope ps(DIBR_KERNEL_SETUP_COUNT, s); setup_count_kernel<T><<<nb, 256, 0, s>>>(sp, fl, geo, L); }
+    { ProfScope ps(DIBR_KERNEL_SETUP_COUNT, s); setup_count_kernel<T, false><<<nb, 256, 0, s>>>(sp, (T)0, fl, geo, LL); }
     LAUNCH_CHECK("setup_count_kernel");
   }
-  { ProfScope ps(DIBR_KERNEL_SCAN, s); scan_kernel<<<geo.B, 1024, 0, s>>>(geo, L); }
+  { ProfScope ps(DIBR_KERNEL_SCAN, s); scan_kernel<<<scan_grid(geo, 1), SCAN_CHUNK, 0, s>>>(geo, LL); }
   LAUNCH_CHECK("scan_kernel");
-  if (nb > 0) {
-    { ProfScope ps(DIBR_KERNEL_FILL, s); fill_kernel<<<nb, 256, 0, s>>>(fl, geo, L); }
-    LAUNCH_CHECK("fill_kernel");
-  }
+  { ProfScope ps(DIBR_KERNEL_FILL, s); fill_kernel<false><<<binning_blocks(fl, geo, true), 256, 0, s>>>(fl, geo, LL); }
+  LAUNCH_CHECK("fill_kernel");
   return DIBR_OK;
 }
 
@@ -166,7 +192,7 @@ int rasterize_fwd_impl(const T* z, const T* img, const T* bbox_in, const T* cons
   const Geometry geo = make_geometry(B, H, W);
   FaceLayout fl; fl.first_idx = first_idx; fl.F = F; fl.Ntot = Ntot; fl.B = B;
   SetupParams<T> sp;
-  sp.img = img; sp.bbox_in = bbox_in; sp.valid = valid; sp.coord_mult = coord_mult;
+  sp.img = img; sp.bbox_in = bbox_in; sp.valid = valid; sp.normals_z = nullptr; sp.coord_mult = coord_mult;
   sp.premultiplied = premultiplied; sp.margin = (T)0; sp.pix_mult = pix_mult;
   BinLists L;
   if (int e = run_binning<T>(sp, fl, geo, ws, ws_bytes, s, L)) return e;
@@ -184,7 +210,8 @@ int rasterize_fwd_impl(const T* z, const T* img, const T* bbox_in, const T* cons
 template <typename T>
 int rasterize_bwd_impl(const T* const* grad_outs, const int64_t* face_idx, const T* weights, const T* img,
                        const T* const* feats, const int* channels, int n_feat, int B, int F, int H, int W,
-                       double multiplier, float eps, T* grad_img, T* const* grad_feats, void* stream) {
+                       double multiplier, float eps, T* grad_img, T* const* grad_feats, void* stream,
+                       bool zero_grad_img = true) {
   if (int e = check_dims(B, (int64_t)B * F, H, W)) return e;
   if (F < 0) return DIBR_ERR_INVALID_ARGUMENT;
   if (!weights && !((float)multiplier > 0.0f)) return DIBR_ERR_INVALID_ARGUMENT;
@@ -199,7 +226,7 @@ int rasterize_bwd_impl(const T* const* grad_outs, const int64_t* face_idx, const
   }
   if (nf > 0) {
     if (!grad_img) return DIBR_ERR_INVALID_ARGUMENT;
-    CUDA_TRY(cudaMemsetAsync(grad_img, 0, nf * 6 * sizeof(T), s));
+    if (zero_grad_img) CUDA_TRY(cudaMemsetAsync(grad_img, 0, nf * 6 * sizeof(T), s));
     for (int t = 0; t < n_feat; ++t)
       if (channels[t] > 0) CUDA_TRY(cudaMemsetAsync(grad_feats[t], 0, nf * 3 * channels[t] * sizeof(T), s));
   }
@@ -209,10 +236,12 @@ int rasterize_bwd_impl(const T* const* grad_outs, const int64_t* face_idx, const
   RasterBwdParams<T> bp;
   bp.grad_out = gin; bp.face_idx = face_idx; bp.weights = weights; bp.img = img; bp.feat = fin;
   bp.coord_mult = (T)multiplier; bp.pix_mult = (float)multiplier; bp.eps = eps; bp.F = F;
+  bp.sx = (float)multiplier / (float)W; bp.sy = (float)multiplier / (float)H;      // = pix_scale(), IEEE fp32 division
   bp.grad_img = grad_img; bp.grad_feat = gout;
   {
     ProfScope ps(DIBR_KERNEL_RASTER_BWD, s);
-    raster_bwd_kernel<T><<<(unsigned)(B * geo.tiles_per_view), 256, 0, s>>>(bp, geo);
+    raster_bwd_kernel<T><<<dim3((unsigned)geo.tiles_x, (unsigned)geo.tiles_y, (unsigned)(B < 65535 ? B : 65535)), 256,
+                           0, s>>>(bp, geo);
   }
   LAUNCH_CHECK("raster_bwd_kernel");
   return DIBR_OK;
@@ -270,11 +299,22 @@ int launch_soft_overflow(const SoftParams<T>& p, const FaceLayout& fl, const Geo
   return DIBR_OK;
 }
 
-// Pair log of the soft-mask forward (dibr_soft_mask.cuh), placed behind the bins in the same workspace.
-struct LogLayout { size_t counts, flags, over, recs, total; unsigned cap_seg; bool ok; };
-LogLayout log_layout(const Geometry& geo, size_t bins_total, size_t elem) {
-  LogLayout l;
+// Pair log of the soft-mask forward (dibr_soft_mask.cuh) and the FUSED workspace layout every soft-mask call uses:
+//   [soft zero | raster zero (dibr_rasterization only) | log zero (always reserved) | soft rest | raster rest | log rest]
+// The offsets do not depend on whether the log is in use (only the tail does), so a forward that had to go without a
+// log is followed by a recompute backward on the same workspace.
+struct LogLayout { size_t counts, flags, over, recs; unsigned cap_seg; bool ok; };
+struct FusedLayout {
+  WsLayout soft, rast;
+  LogLayout log;
+  bool has_rast;
+  size_t zero_begin, zero_end, total_no_log, total;
+};
+FusedLayout fused_layout(int B, int64_t Ntot, bool with_raster, const Geometry& geo) {
+  FusedLayout f;
+  f.has_rast = with_raster;
   const int64_t P = (int64_t)geo.B * geo.H * geo.W;
+  LogLayout& l = f.log;
   l.ok = P > 0 && P < ((int64_t)1 << 32);                 // pixel indices are logged as u32
   int64_t cap = 2 * P + 65536;                            // measured: 0.5 - 1.3 pairs per pixel on configs 1-5
   static const long long forced = [] {                    // DIBR_SOFT_LOG_CAP=<entries>: tests of the overflow path
@@ -283,85 +323,50 @@ LogLayout log_layout(const Geometry& geo, size_t bins_total, size_t elem) {
   }();
   if (forced > 0) cap = forced;
   l.cap_seg = (unsigned)((cap + LOG_SEGMENTS - 1) / LOG_SEGMENTS);
-  const size_t n = (size_t)l.cap_seg * LOG_SEGMENTS;
-  size_t o = align_up(bins_total);
   const size_t nt = (size_t)geo.B * geo.tiles_per_view;
+  size_t o = 0;
+  f.zero_begin = o;
+  o = ws_zero_part(f.soft, B, geo, o);
+  if (with_raster) o = ws_zero_part(f.rast, B, geo, o);
   l.counts = o; o = align_up(o + (LOG_SEGMENTS + 1) * sizeof(unsigned));     // + the overflow counter
   l.flags = o;  o = align_up(o + nt * sizeof(unsigned));
+  f.zero_end = o;
+  o = ws_rest_part(f.soft, B, Ntot, geo, o);
+  if (with_raster) o = ws_rest_part(f.rast, B, Ntot, geo, o);
+  f.total_no_log = o;
   l.over = o;   o = align_up(o + nt * sizeof(unsigned));
-  (void)elem;                                              // 16-byte records for fp32 and fp64 alike
-  l.recs = o;   o = align_up(o + n * sizeof(uint4));
-  l.total = o;
-  return l;
+  l.recs = o;   o = align_up(o + (size_t)l.cap_seg * LOG_SEGMENTS * sizeof(uint4));   // 16-byte records, fp32 and fp64
+  f.total = o;
+  return f;
 }
 
+// The soft-mask kernels on prepared lists.  `use_log`: MODE_FWD appends its evaluated pairs to the log; MODE_BWD
+// consumes it (log kernel + the normally idle overflow kernel) instead of re-deriving the k-lists.
 template <typename T, int MODE>
-int soft_mask_impl(const T* img, const T* bbox_in, const int64_t* face_idx, int B, int F, int H, int W,
-                   float sigmainv, int knum, T coord_mult, int premultiplied, T margin, float pix_mult,
-                   T* soft, T* prob, int64_t* close_idx, uint8_t* dist_type, const T* grad_soft, const T* soft_in,
-                   T* grad_img, void* ws, size_t ws_bytes, void* stream, int bins_ready = 0, int keep_pairs = 0) {
-  if (int e = check_dims(B, (int64_t)B * F, H, W)) return e;
-  if (F < 0 || knum < 0 || !(pix_mult > 0.0f)) return DIBR_ERR_INVALID_ARGUMENT;
-  const bool side = prob || close_idx || dist_type;
-  if (side && !(prob && close_idx && dist_type)) return DIBR_ERR_INVALID_ARGUMENT;
-  cudaStream_t s = static_cast<cudaStream_t>(stream);
-  const size_t nf = (size_t)B * F;
-  if (MODE == MODE_BWD && nf > 0) {
-    if (!grad_img) return DIBR_ERR_INVALID_ARGUMENT;
-    CUDA_TRY(cudaMemsetAsync(grad_img, 0, nf * 6 * sizeof(T), s));
-  }
-  if (B == 0 || H == 0 || W == 0) return DIBR_OK;
-  if (!face_idx || (nf > 0 && !img)) return DIBR_ERR_INVALID_ARGUMENT;
-  if (MODE == MODE_FWD && !soft) return DIBR_ERR_INVALID_ARGUMENT;
-  if (MODE == MODE_BWD && (!grad_soft || !soft_in)) return DIBR_ERR_INVALID_ARGUMENT;
-  const Geometry geo = make_geometry(B, H, W);
-  FaceLayout fl; fl.first_idx = nullptr; fl.F = F; fl.Ntot = (int64_t)nf; fl.B = B;
-  SetupParams<T> sp;
-  sp.img = img; sp.bbox_in = bbox_in; sp.valid = nullptr; sp.coord_mult = coord_mult;
-  sp.premultiplied = premultiplied; sp.margin = margin; sp.pix_mult = pix_mult;
-  BinLists L;
-  if (bins_ready) {                      // the forward call's bins, still in `ws` (the consumers only read them)
-    const WsLayout w = ws_layout(geo.B, fl.Ntot, geo);
-    if (!ws || ws_bytes < w.total) return DIBR_ERR_WORKSPACE;
-    L = carve(ws, w);
-  } else if (int e = run_binning<T>(sp, fl, geo, ws, ws_bytes, s, L)) {
-    return e;
-  }
-  SoftParams<T> p;
-  p.img = img; p.coord_mult = coord_mult; p.premultiplied = premultiplied; p.pix_mult = pix_mult;
-  p.sigmainv = sigmainv; p.F = F; p.knum = knum; p.face_idx = face_idx; p.soft = soft; p.prob = prob;
-  p.close_idx = close_idx; p.dist_type = dist_type; p.grad_soft = grad_soft; p.soft_in = soft_in;
-  p.grad_img = grad_img;
+int soft_launch_on_lists(SoftParams<T> p, const FaceLayout& fl, const Geometry& geo, const BinLists& L, void* ws,
+                         const FusedLayout& fz, bool use_log, cudaStream_t s) {
   p.log_count = nullptr; p.over_count = nullptr; p.tile_flag = nullptr; p.over_list = nullptr; p.log = nullptr;
   p.log_cap = 0;
   {
     static const int sel = [] { const char* e = tuning_env("DIBR_SOFT_SEL"); return e ? atoi(e) : 0; }();
     p.sel_first = sel;                 // experiments: candidates taken by a tile's first pass (0 = default)
   }
-  // The pair log is used when it was asked for (forward: keep_pairs; backward: bins_ready == 2), the pixel
-  // indices fit 32 bits and the workspace holds it — the same test on both sides, so a forward that had to go
-  // without a log is followed by a recompute backward on the same workspace.
-  const LogLayout ll = log_layout(geo, ws_layout(geo.B, fl.Ntot, geo).total, sizeof(T));
-  const bool use_log = ((MODE == MODE_FWD) ? (keep_pairs != 0 && !side) : (bins_ready == 2)) && ll.ok && ws &&
-                       ws_bytes >= ll.total;
   // backward from the log = two launches (logged pairs, then the normally idle recompute kernel): one scope
   ProfScope both(use_log && MODE == MODE_BWD ? DIBR_KERNEL_SOFT_BWD : -100, s);
   if (use_log) {
     unsigned char* base = static_cast<unsigned char*>(ws);
-    p.log_count = reinterpret_cast<unsigned*>(base + ll.counts);
+    p.log_count = reinterpret_cast<unsigned*>(base + fz.log.counts);
     p.over_count = p.log_count + LOG_SEGMENTS;
-    p.tile_flag = reinterpret_cast<unsigned*>(base + ll.flags);
-    p.over_list = reinterpret_cast<unsigned*>(base + ll.over);
-    p.log = reinterpret_cast<uint4*>(base + ll.recs);
-    p.log_cap = ll.cap_seg;
-    if (MODE == MODE_FWD) {              // counts and flags are contiguous: one memset
-      CUDA_TRY(cudaMemsetAsync(base + ll.counts, 0, ll.over - ll.counts, s));
-    } else if (nf > 0) {                 // the logged pairs first, then the (normally idle) recompute kernel
+    p.tile_flag = reinterpret_cast<unsigned*>(base + fz.log.flags);
+    p.over_list = reinterpret_cast<unsigned*>(base + fz.log.over);
+    p.log = reinterpret_cast<uint4*>(base + fz.log.recs);
+    p.log_cap = fz.log.cap_seg;
+    if (MODE == MODE_BWD && fl.Ntot > 0) {     // the logged pairs first, then the (normally idle) recompute kernel
       soft_mask_bwd_log_kernel<T><<<dim3(LOG_CTAS_PER_SEGMENT, LOG_SEGMENTS), 256, 0, s>>>(p, fl, geo);
       g_launches.fetch_add(1, std::memory_order_relaxed);
     }
   }
-  const unsigned grid = (unsigned)(B * geo.tiles_per_view);
+  const unsigned grid = (unsigned)(geo.B * geo.tiles_per_view);
   const int kid = MODE == MODE_FWD ? DIBR_KERNEL_SOFT_FWD : DIBR_KERNEL_SOFT_BWD;
   // threads per CTA (one CTA per tile either way): fp32 uses small CTAs (more resident tiles per SM hide the
   // barrier-separated phases); DIBR_SOFT_NT=64|128|256 overrides for experiments.  fp64: 256.
@@ -377,6 +382,153 @@ int soft_mask_impl(const T* img, const T* bbox_in, const int64_t* face_idx, int 
     if (int e = launch_soft<T, MODE, 256>(p, fl, geo, L, kid, s)) return e;
   }
   LAUNCH_CHECK("soft_mask_kernel");
+  return DIBR_OK;
+}
+
+// bins_ready: 0 = bin here; 1 = the forward call's bins are in `ws`; 2 = bins and pair log are; +4 = `ws` was laid out
+// by the dibr_rasterization call (it also holds the rasterizer's lists).
+template <typename T, int MODE>
+int soft_mask_impl(const T* img, const T* bbox_in, const int64_t* face_idx, int B, int F, int H, int W,
+                   float sigmainv, int knum, T coord_mult, int premultiplied, T margin, float pix_mult,
+                   T* soft, T* prob, int64_t* close_idx, uint8_t* dist_type, const T* grad_soft, const T* soft_in,
+                   T* grad_img, void* ws, size_t ws_bytes, void* stream, int bins_ready = 0, int keep_pairs = 0,
+                   bool zero_grad = true) {
+  if (int e = check_dims(B, (int64_t)B * F, H, W)) return e;
+  if (F < 0 || knum < 0 || !(pix_mult > 0.0f)) return DIBR_ERR_INVALID_ARGUMENT;
+  const bool side = prob || close_idx || dist_type;
+  if (side && !(prob && close_idx && dist_type)) return DIBR_ERR_INVALID_ARGUMENT;
+  cudaStream_t s = static_cast<cudaStream_t>(stream);
+  const size_t nf = (size_t)B * F;
+  if (MODE == MODE_BWD && nf > 0) {
+    if (!grad_img) return DIBR_ERR_INVALID_ARGUMENT;
+    if (zero_grad) CUDA_TRY(cudaMemsetAsync(grad_img, 0, nf * 6 * sizeof(T), s));
+  }
+  if (B == 0 || H == 0 || W == 0) return DIBR_OK;
+  if (!face_idx || (nf > 0 && !img)) return DIBR_ERR_INVALID_ARGUMENT;
+  if (MODE == MODE_FWD && !soft) return DIBR_ERR_INVALID_ARGUMENT;
+  if (MODE == MODE_BWD && (!grad_soft || !soft_in)) return DIBR_ERR_INVALID_ARGUMENT;
+  const Geometry geo = make_geometry(B, H, W);
+  FaceLayout fl; fl.first_idx = nullptr; fl.F = F; fl.Ntot = (int64_t)nf; fl.B = B;
+  const FusedLayout fz = fused_layout(B, fl.Ntot, (bins_ready & 4) != 0, geo);
+  if (!ws || ws_bytes < fz.total_no_log) return DIBR_ERR_WORKSPACE;
+  // The pair log is used when it was asked for (forward: keep_pairs; backward: bins_ready & 2), the pixel indices
+  // fit 32 bits and the workspace holds it — the same test on both sides.
+  const bool use_log = ((MODE == MODE_FWD) ? (keep_pairs != 0 && !side) : ((bins_ready & 2) != 0)) && fz.log.ok &&
+                       ws_bytes >= fz.total;
+  BinLists L = carve(ws, fz.soft);
+  if (!(bins_ready & 3)) {                  // otherwise: the forward call's bins, still in `ws` (only read here)
+    CUDA_TRY(cudaMemsetAsync(static_cast<unsigned char*>(ws) + fz.zero_begin, 0, fz.zero_end - fz.zero_begin, s));
+    SetupParams<T> sp;
+    sp.img = img; sp.bbox_in = bbox_in; sp.valid = nullptr; sp.normals_z = nullptr; sp.coord_mult = coord_mult;
+    sp.premultiplied = premultiplied; sp.margin = margin; sp.pix_mult = pix_mult;
+    BinLists2 LL; LL.l[0] = L; LL.l[1] = L;
+    const unsigned nb = binning_blocks(fl, geo, false);
+    if (nb > 0) {
+      { ProfScope ps(DIBR_KERNEL_SETUP_COUNT, s); setup_count_kernel<T, false><<<nb, 256, 0, s>>>(sp, (T)0, fl, geo, LL); }
+      LAUNCH_CHECK("setup_count_kernel");
+    }
+    { ProfScope ps(DIBR_KERNEL_SCAN, s); scan_kernel<<<scan_grid(geo, 1), SCAN_CHUNK, 0, s>>>(geo, LL); }
+    LAUNCH_CHECK("scan_kernel");
+    { ProfScope ps(DIBR_KERNEL_FILL, s); fill_kernel<false><<<binning_blocks(fl, geo, true), 256, 0, s>>>(fl, geo, LL); }
+    LAUNCH_CHECK("fill_kernel");
+  }
+  SoftParams<T> p;
+  p.img = img; p.coord_mult = coord_mult; p.premultiplied = premultiplied; p.pix_mult = pix_mult;
+  p.sigmainv = sigmainv; p.F = F; p.knum = knum; p.face_idx = face_idx; p.soft = soft; p.prob = prob;
+  p.close_idx = close_idx; p.dist_type = dist_type; p.grad_soft = grad_soft; p.soft_in = soft_in;
+  p.grad_img = grad_img;
+  return soft_launch_on_lists<T, MODE>(p, fl, geo, L, ws, fz, use_log, s);
+}
+
+// dibr_rasterization (dibr.py:119-209) = rasterize(valid = face_normals_z >= 0) + dibr_soft_mask in ONE call: both
+// list sets from one read of the coordinates (setup / scan / fill once), then the two per-tile kernels.
+template <typename T>
+int dibr_rasterization_fwd_impl(const T* z, const T* img, const T* const* feats, const int* channels, int n_feat,
+                                const T* normals_z, const uint8_t* valid, int B, int F, int H, int W,
+                                double multiplier, float eps, float sigmainv, double boxlen, int knum,
+                                T* const* out_feats, int64_t* out_idx, T* soft, void* ws, size_t ws_bytes,
+                                int keep_pairs, void* stream) {
+  if (F < 0 || knum < 0) return DIBR_ERR_INVALID_ARGUMENT;
+  const int64_t Ntot = (int64_t)B * F;
+  if (int e = check_dims(B, Ntot, H, W)) return e;
+  const float pix_mult = (float)multiplier;
+  if (!(pix_mult > 0.0f)) return DIBR_ERR_INVALID_ARGUMENT;
+  if (B == 0 || H == 0 || W == 0) return DIBR_OK;
+  if ((Ntot > 0 && (!z || !img)) || !out_idx || !soft) return DIBR_ERR_INVALID_ARGUMENT;
+  FeatSet<const T> fin; FeatSet<T> fout;
+  if (int e = make_featsets<T>(feats, out_feats, channels, n_feat, Ntot > 0, fin, fout)) return e;
+  cudaStream_t s = static_cast<cudaStream_t>(stream);
+  const Geometry geo = make_geometry(B, H, W);
+  FaceLayout fl; fl.first_idx = nullptr; fl.F = F; fl.Ntot = Ntot; fl.B = B;
+  const FusedLayout fz = fused_layout(B, Ntot, true, geo);
+  if (!ws || ws_bytes < fz.total_no_log) return DIBR_ERR_WORKSPACE;
+  const bool use_log = keep_pairs != 0 && fz.log.ok && ws_bytes >= fz.total;
+  BinLists2 LL; LL.l[0] = carve(ws, fz.rast); LL.l[1] = carve(ws, fz.soft);
+  CUDA_TRY(cudaMemsetAsync(static_cast<unsigned char*>(ws) + fz.zero_begin, 0, fz.zero_end - fz.zero_begin, s));
+  SetupParams<T> sp;
+  sp.img = img; sp.bbox_in = nullptr; sp.valid = valid; sp.normals_z = normals_z; sp.coord_mult = (T)multiplier;
+  sp.premultiplied = 0; sp.margin = (T)0; sp.pix_mult = pix_mult;
+  const unsigned nb = binning_blocks(fl, geo, false);
+  if (nb > 0) {
+    { ProfScope ps(DIBR_KERNEL_SETUP_COUNT, s);
+      setup_count_kernel<T, true><<<nb, 256, 0, s>>>(sp, (T)(boxlen * multiplier), fl, geo, LL); }
+    LAUNCH_CHECK("setup_count_kernel");
+  }
+  { ProfScope ps(DIBR_KERNEL_SCAN, s); scan_kernel<<<scan_grid(geo, 2), SCAN_CHUNK, 0, s>>>(geo, LL); }
+  LAUNCH_CHECK("scan_kernel");
+  { ProfScope ps(DIBR_KERNEL_FILL, s); fill_kernel<true><<<binning_blocks(fl, geo, true), 256, 0, s>>>(fl, geo, LL); }
+  LAUNCH_CHECK("fill_kernel");
+  RasterFwdParams<T> rp;
+  rp.z = z; rp.img = img; rp.feat = fin; rp.coord_mult = (T)multiplier; rp.premultiplied = 0;
+  rp.pix_mult = pix_mult; rp.eps = eps; rp.out_feat = fout; rp.out_idx = out_idx; rp.out_w = nullptr;
+  {
+    ProfScope ps(DIBR_KERNEL_RASTER_FWD, s);
+    launch_raster_fwd(rp, fl, geo, LL.l[0], s);
+  }
+  LAUNCH_CHECK("raster_fwd_kernel");
+  SoftParams<T> p;
+  p.img = img; p.coord_mult = (T)multiplier; p.premultiplied = 0; p.pix_mult = pix_mult;
+  p.sigmainv = sigmainv; p.F = F; p.knum = knum; p.face_idx = out_idx; p.soft = soft; p.prob = nullptr;
+  p.close_idx = nullptr; p.dist_type = nullptr; p.grad_soft = nullptr; p.soft_in = nullptr; p.grad_img = nullptr;
+  return soft_launch_on_lists<T, MODE_FWD>(p, fl, geo, LL.l[1], ws, fz, use_log, s);
+}
+
+// Backward of both outputs of dibr_rasterization into ONE grad_img buffer (zero-filled once; the two kernels'
+// red.global.add accumulate into it) + the feature gradients.  Either upstream gradient may be absent.
+template <typename T>
+int dibr_rasterization_bwd_impl(const T* const* grad_outs, const T* grad_soft, const T* soft,
+                                const int64_t* face_idx, const T* img, const T* const* feats, const int* channels,
+                                int n_feat, int B, int F, int H, int W, double multiplier, float eps, float sigmainv,
+                                double boxlen, int knum, T* grad_img, T* const* grad_feats, void* ws, size_t ws_bytes,
+                                int bins_ready, void* stream) {
+  if (F < 0 || knum < 0) return DIBR_ERR_INVALID_ARGUMENT;
+  if (int e = check_dims(B, (int64_t)B * F, H, W)) return e;
+  cudaStream_t s = static_cast<cudaStream_t>(stream);
+  const size_t nf = (size_t)B * F;
+  if (nf > 0) {
+    if (!grad_img) return DIBR_ERR_INVALID_ARGUMENT;
+    CUDA_TRY(cudaMemsetAsync(grad_img, 0, nf * 6 * sizeof(T), s));
+  }
+  bool any_out = false;
+  for (int t = 0; t < n_feat; ++t) any_out = any_out || (grad_outs && grad_outs[t]);
+  if (any_out || n_feat > 0) {
+    // feature gradients are zero-filled by rasterize_bwd_impl; with no upstream feature gradient they stay zero
+    if (any_out) {
+      if (int e = rasterize_bwd_impl<T>(grad_outs, face_idx, nullptr, img, feats, channels, n_feat, B, F, H, W,
+                                        multiplier, eps, grad_img, grad_feats, stream, false))
+        return e;
+    } else if (nf > 0 && grad_feats) {
+      for (int t = 0; t < n_feat; ++t)
+        if (channels[t] > 0 && grad_feats[t]) CUDA_TRY(cudaMemsetAsync(grad_feats[t], 0, nf * 3 * channels[t] * sizeof(T), s));
+    }
+  }
+  if (grad_soft) {
+    if (int e = soft_mask_impl<T, MODE_BWD>(img, nullptr, face_idx, B, F, H, W, sigmainv, knum, (T)multiplier, 0,
+                                            (T)(boxlen * multiplier), (float)multiplier, nullptr, nullptr, nullptr,
+                                            nullptr, grad_soft, soft, grad_img, ws, ws_bytes, stream, bins_ready, 0,
+                                            false))
+      return e;
+  }
   return DIBR_OK;
 }
 
@@ -561,10 +713,11 @@ int deftet_fwd_impl(const T* z, const T* img, const T* bbox, const T* pix, const
     deftet_setup_count_kernel<T><<<nb, 256, 0, s>>>(img, bbox, fl, geo, L, G);
     LAUNCH_CHECK("deftet_setup_count_kernel");
   }
-  scan_kernel<<<B, 1024, 0, s>>>(geo, L);
+  BinLists2 LL; LL.l[0] = L; LL.l[1] = L;
+  scan_kernel<<<scan_grid(geo, 1), SCAN_CHUNK, 0, s>>>(geo, LL);
   LAUNCH_CHECK("scan_kernel");
   if (nb > 0) {
-    fill_kernel<<<nb, 256, 0, s>>>(fl, geo, L);
+    fill_kernel<false><<<binning_blocks(fl, geo, true), 256, 0, s>>>(fl, geo, LL);
     LAUNCH_CHECK("fill_kernel");
   }
   DeftetParams<T> dp;
@@ -665,11 +818,16 @@ DIBR_API size_t dibr_workspace_bytes(int batch_size, int64_t total_faces, int he
 DIBR_API size_t dibr_soft_mask_workspace_bytes(int batch_size, int64_t total_faces, int height, int width,
                                                int keep_pairs, int elem_size) {
   if (check_dims(batch_size, total_faces, height, width) != DIBR_OK) return 0;
-  const Geometry geo = make_geometry(batch_size, height, width);
-  const size_t bins = ws_layout(batch_size, total_faces, geo).total;
-  if (!keep_pairs) return bins;
-  const LogLayout ll = log_layout(geo, bins, (size_t)elem_size);
-  return ll.ok ? ll.total : bins;
+  (void)elem_size;
+  const FusedLayout fz = fused_layout(batch_size, total_faces, false, make_geometry(batch_size, height, width));
+  return (keep_pairs && fz.log.ok) ? fz.total : fz.total_no_log;
+}
+
+DIBR_API size_t dibr_rasterization_workspace_bytes(int batch_size, int64_t total_faces, int height, int width,
+                                                   int keep_pairs) {
+  if (check_dims(batch_size, total_faces, height, width) != DIBR_OK) return 0;
+  const FusedLayout fz = fused_layout(batch_size, total_faces, true, make_geometry(batch_size, height, width));
+  return (keep_pairs && fz.log.ok) ? fz.total : fz.total_no_log;
 }
 
 DIBR_API size_t dibr_deftet_workspace_bytes(int batch_size, int64_t total_faces) {
@@ -764,6 +922,24 @@ DIBR_API size_t dibr_mask_iou_workspace_bytes(int B, int64_t P, int elem_size) {
                                        nullptr, nullptr, grad_soft, soft, grad_img, ws, ws_bytes, stream,    \
                                        bins_ready);                                                           \
   }                                                                                                           \
+  DIBR_API int dibr_rasterization_fwd_fused_##SUF(                                                            \
+      const T* z, const T* img, const T* const* feats, const int* channels, int n_feat, const T* normals_z,   \
+      const uint8_t* valid, int B, int F, int H, int W, double multiplier, float eps, float sigmainv,         \
+      double boxlen, int knum, T* const* out_feats, int64_t* out_face_idx, T* soft, void* ws, size_t ws_bytes, \
+      int keep_pairs, void* stream) {                                                                          \
+    return dibr_rasterization_fwd_impl<T>(z, img, feats, channels, n_feat, normals_z, valid, B, F, H, W,       \
+                                          multiplier, eps, sigmainv, boxlen, knum, out_feats, out_face_idx,    \
+                                          soft, ws, ws_bytes, keep_pairs, stream);                              \
+  }                                                                                                            \
+  DIBR_API int dibr_rasterization_bwd_fused_##SUF(                                                            \
+      const T* const* grad_outs, const T* grad_soft, const T* soft, const int64_t* face_idx, const T* img,    \
+      const T* const* feats, const int* channels, int n_feat, int B, int F, int H, int W, double multiplier,  \
+      float eps, float sigmainv, double boxlen, int knum, T* grad_img, T* const* grad_feats, void* ws,        \
+      size_t ws_bytes, int bins_ready, void* stream) {                                                         \
+    return dibr_rasterization_bwd_impl<T>(grad_outs, grad_soft, soft, face_idx, img, feats, channels, n_feat, \
+                                          B, F, H, W, multiplier, eps, sigmainv, boxlen, knum, grad_img,       \
+                                          grad_feats, ws, ws_bytes, bins_ready, stream);                        \
+  }                                                                                                            \
   DIBR_API int dibr_prepare_vertices_fwd_##SUF(const T* vertices, const int64_t* faces, const T* camera_proj, \
                                                const T* rot, const T* trans, const T* transform, int B,      \
                                                int Bv, int V, int F, T* face_vertices_camera,                \

@@ -25,11 +25,22 @@ struct RasterBwdParams {
   FeatSet<const T> feat;   // n tensors (B,F,3,C_t)
   T coord_mult;
   float pix_mult;
+  float sx, sy;            // pix_scale(pix_mult, W / H): one IEEE division each, taken on the host (same fp32 result)
   float eps;
   int F;
   T* grad_img;             // (B,F,3,2)
   FeatSet<T> grad_feat;    // n tensors (B,F,3,C_t)
 };
+
+// img gradient of one (warp, face): three 8-byte vector reductions (red.global.add.v2.f32, sm_90+) instead of six
+// scalar ones — a face's (3,2) record is 24 bytes, so every vertex pair is 8-byte aligned
+__device__ __forceinline__ void red_add2(float* p, const float a, const float b) {
+  asm volatile("red.global.add.v2.f32 [%0], {%1, %2};" ::"l"(p), "f"(a), "f"(b) : "memory");
+}
+__device__ __forceinline__ void red_add2(double* p, const double a, const double b) {
+  atomicAdd(p, a);
+  atomicAdd(p + 1, b);
+}
 
 // Sum `v` over the lanes of `peers` (every lane of the warp must call this with its own peers mask);
 // the result is valid on the group's lowest lane.  `src[s]` = partner lane for step s (self if none): the member
@@ -129,18 +140,28 @@ __device__ __forceinline__ void raster_bwd_tail(const RasterBwdParams<T>& bp, co
   acc1 *= inv_k3sq; acc2 *= inv_k3sq;
   T* gi = bp.grad_img + tf * 6;
 #pragma unroll
-  for (int k = 0; k < 6; ++k) {
-    const T gk = covered ? acc1 * dw1[k] + acc2 * dw2[k] : (T)0;   // dw1 / dw2 are only defined on covered lanes
-    const T sk = group_sum_n<T, NS>(gk, src);
-    if (leader) atomicAdd(gi + k, sk);               // :391-398
+  for (int k = 0; k < 6; k += 2) {
+    const T g0 = covered ? acc1 * dw1[k] + acc2 * dw2[k] : (T)0;   // dw1 / dw2 are only defined on covered lanes
+    const T g1 = covered ? acc1 * dw1[k + 1] + acc2 * dw2[k + 1] : (T)0;
+    const T s0 = group_sum_n<T, NS>(g0, src);
+    const T s1 = group_sum_n<T, NS>(g1, src);
+    if (leader) red_add2(gi + k, s0, s1);            // :391-398
   }
 }
 
 template <typename T>
+__device__ __forceinline__ void raster_bwd_tile(const RasterBwdParams<T>& bp, const Geometry& geo, const int b,
+                                                const int tx, const int ty);
+
+// grid (tiles_x, tiles_y, min(B, 65535)): no integer division in the per-thread prologue
+template <typename T>
 __global__ void __launch_bounds__(256, DIBR_RASTER_BWD_CTAS) raster_bwd_kernel(RasterBwdParams<T> bp, Geometry geo) {
-  const int tile = blockIdx.x % geo.tiles_per_view;
-  const int b = blockIdx.x / geo.tiles_per_view;
-  const int tx = tile % geo.tiles_x, ty = tile / geo.tiles_x;
+  for (int b = blockIdx.z; b < geo.B; b += gridDim.z) raster_bwd_tile<T>(bp, geo, b, blockIdx.x, blockIdx.y);
+}
+
+template <typename T>
+__device__ __forceinline__ void raster_bwd_tile(const RasterBwdParams<T>& bp, const Geometry& geo, const int b,
+                                                const int tx, const int ty) {
   const int px = tx * TILE + (threadIdx.x & (TILE - 1));
   const int py = ty * TILE + (threadIdx.x / TILE);
   const bool in_image = px < geo.W && py < geo.H;
@@ -151,7 +172,7 @@ __global__ void __launch_bounds__(256, DIBR_RASTER_BWD_CTAS) raster_bwd_kernel(R
   if (f >= bp.F) f = -1;                             // never write out of bounds on a corrupt index
   const bool covered = f >= 0;
   const unsigned any = __ballot_sync(0xffffffffu, covered);
-  if (any == 0u) return;
+  if (any == 0u) return;                             // (warp-uniform)
 
   // group lanes by face (uncovered lanes form their own group and contribute zeros)
   const unsigned peers = __match_any_sync(0xffffffffu, (int)f);
@@ -174,8 +195,8 @@ __global__ void __launch_bounds__(256, DIBR_RASTER_BWD_CTAS) raster_bwd_kernel(R
       w0 = w[0]; w1 = w[1]; w2 = w[2];
     } else {
       typedef RN<T> R;
-      const T x0 = (T)pix_coord(pix_scale(bp.pix_mult, geo.W), geo.W, px);
-      const T y0 = (T)pix_coord(pix_scale(bp.pix_mult, geo.H), geo.H, geo.H - 1 - py);
+      const T x0 = (T)pix_coord(bp.sx, geo.W, px);
+      const T y0 = (T)pix_coord(bp.sy, geo.H, geo.H - 1 - py);
       bary_weights<T>(R::mul(ax, bp.coord_mult), R::mul(ay, bp.coord_mult), R::mul(bx, bp.coord_mult),
                       R::mul(by, bp.coord_mult), R::mul(cx, bp.coord_mult), R::mul(cy, bp.coord_mult),
                       x0, y0, bp.eps, w0, w1, w2);

@@ -54,7 +54,7 @@ struct StagedFace {        // SoA in shared memory, one slot per staged face
 // scan (:106-170) ends with the best face among the inside faces of index > n — largest z0, lowest index on ties,
 // the first of them accepted whatever its depth — or with n itself.  Walks the tile's (unordered) candidate lists.
 template <typename T>
-__device__ __noinline__ void resolve_after_nan(const RasterFwdParams<T>& rp, const BinLists& L, const TileLists& tl,
+__device__ __forceinline__ void resolve_after_nan(const RasterFwdParams<T>& rp, const BinLists& L, const TileLists& tl,
                                                const int64_t vbase, const int px, const int py, const T x0,
                                                const T y0, const int n, int& best_f, T& bw0, T& bw1, T& bw2) {
   T best_z = 0;

@@ -168,10 +168,12 @@ template <>
 __device__ __forceinline__ void soft_pair<float>(const float* p, const float x0, const float y0,
                                                  const float multiplier, const float sigmainv, const bool fused,
                                                  const float prob_scale, float& d, float& prob, int& edgeid) {
+  bool ambiguous = false;
   if (fused) {
-    d = soft_distance_f32(p, x0, y0, multiplier, edgeid);
+    d = soft_distance_f32(p, x0, y0, multiplier, edgeid, ambiguous);
     prob = soft_prob_f32(d, prob_scale);
-  } else {
+  }
+  if (!fused || ambiguous) {          // ties between the six distances: the reference's exact arithmetic decides
     d = soft_distance<float>(p, x0, y0, multiplier, edgeid);
     prob = soft_prob<float>(d, sigmainv, multiplier);
   }

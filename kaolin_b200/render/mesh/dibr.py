@@ -96,6 +96,105 @@ class DibrSoftMaskCuda(Function):
         return grad_face_vertices_image, None, None, None, None, None
 
 
+class DibrRasterizationCuda(Function):
+    """``dibr_rasterization`` with backend cuda as ONE native call each way (dibr.py:119-209 = RasterizeCuda with
+    ``valid_faces = face_normals_z >= 0`` followed by DibrSoftMaskCuda): both face-list sets come from a single read of
+    the coordinates, and backward accumulates the rasterizer's and the soft mask's image-plane gradients into one
+    tensor.  forward(ctx, height, width, z, img, normals_z, sigmainv, boxlen, knum, multiplier, eps, *face_features)
+    -> (*interpolated_features, soft_mask, face_idx); forward values are bit-identical to the two separate calls."""
+    @staticmethod
+    def forward(ctx, height, width, face_vertices_z, face_vertices_image, face_normals_z, sigmainv, boxlen, knum,
+                multiplier, eps, *face_features):
+        fn = "dibr_rasterization"
+        dev = _require_cuda(fn, face_vertices_z=face_vertices_z, face_vertices_image=face_vertices_image,
+                            face_normals_z=face_normals_z,
+                            **{f"face_features[{i}]": f for i, f in enumerate(face_features)})
+        b, f = face_vertices_z.shape[0], face_vertices_z.shape[1]
+        dtype = face_vertices_z.dtype
+        suf = _lib.suffix(dtype, fn)
+        feats = []
+        for t in face_features:
+            if t.dtype != dtype or t.dim() != 4 or tuple(t.shape[:3]) != (b, f, 3):
+                raise RuntimeError(f"{fn}: every face_features tensor must be (B,F,3,C) of dtype {dtype}")
+            feats.append(t.contiguous())
+        if face_vertices_image.dtype != dtype or tuple(face_vertices_z.shape) != (b, f, 3) or \
+                tuple(face_vertices_image.shape) != (b, f, 3, 2):
+            raise RuntimeError(f"{fn}: expected face_vertices_z (B,F,3), face_vertices_image (B,F,3,2)")
+        if tuple(face_normals_z.shape) != (b, f) or face_normals_z.dtype != dtype:
+            raise RuntimeError(f"{fn}: face_normals_z must be (B,F) of dtype {dtype}")
+        img = face_vertices_image.contiguous()
+        z = face_vertices_z.contiguous()
+        nz = face_normals_z.contiguous()
+        chans = [t.shape[-1] for t in feats]
+        outs = [torch.empty((b, height, width, c), dtype=dtype, device=dev) for c in chans]
+        face_idx = torch.empty((b, height, width), dtype=torch.long, device=dev)
+        soft = torch.empty((b, height, width), dtype=dtype, device=dev)
+        # pair log for backward: see DibrSoftMaskCuda.forward (about 32 bytes per pixel, held until backward)
+        keep = 1 if ctx.needs_input_grad[3] else 0
+        lib = _lib.load()
+        with torch.cuda.device(dev):
+            nbytes = lib.dibr_rasterization_workspace_bytes(b, b * f, int(height), int(width), keep)
+            try:
+                ws = torch.empty(max(int(nbytes), 256), dtype=torch.uint8, device=dev)
+            except torch.cuda.OutOfMemoryError:
+                if not keep:
+                    raise
+                keep = 0
+                nbytes = lib.dibr_rasterization_workspace_bytes(b, b * f, int(height), int(width), 0)
+                ws = torch.empty(max(int(nbytes), 256), dtype=torch.uint8, device=dev)
+            code = getattr(lib, "dibr_rasterization_fwd_fused_" + suf)(
+                _lib.ptr(z), _lib.ptr(img), _lib.ptr_array(feats), _lib.int_array(chans), len(feats), _lib.ptr(nz), 0,
+                b, f, int(height), int(width), float(multiplier), float(eps), float(sigmainv), float(boxlen), int(knum),
+                _lib.ptr_array(outs), _lib.ptr(face_idx), _lib.ptr(soft), _lib.ptr(ws), nbytes, keep,
+                _lib.current_stream(dev))
+        _lib.check(code, fn)
+        ctx.save_for_backward(face_idx, soft, img, *feats)
+        ctx.mark_non_differentiable(face_idx)
+        ctx.set_materialize_grads(False)
+        ctx.args = (float(multiplier), float(eps), float(sigmainv), float(boxlen), int(knum))
+        ctx.out_shapes = [tuple(o.shape) for o in outs]
+        ctx.bins = ws if keep else None
+        return (*outs, soft, face_idx)
+
+    @staticmethod
+    def backward(ctx, *grads):
+        fn = "dibr_rasterization_backward"
+        g_outs, g_soft = grads[:-2], grads[-2]
+        n_in = 10 + len(g_outs)
+        if g_soft is None and all(g is None for g in g_outs):
+            return (None,) * n_in
+        face_idx, soft, img = ctx.saved_tensors[:3]
+        feats = list(ctx.saved_tensors[3:])
+        dev, dtype = img.device, img.dtype
+        suf = _lib.suffix(dtype, fn)
+        multiplier, eps, sigmainv, boxlen, knum = ctx.args
+        b, f = img.shape[0], img.shape[1]
+        h, w = face_idx.shape[1], face_idx.shape[2]
+        any_out = any(g is not None for g in g_outs)
+        gouts = [torch.zeros(shp, dtype=dtype, device=dev) if g is None else g.contiguous()
+                 for g, shp in zip(g_outs, ctx.out_shapes)] if any_out else []
+        g_soft = None if g_soft is None else g_soft.contiguous()
+        gi = torch.empty_like(img)
+        # without an upstream feature gradient the feature tensors get None (as when RasterizeCuda.backward is not run)
+        gfs = [torch.empty_like(t) for t in feats] if any_out else []
+        chans = [t.shape[-1] for t in feats]
+        lib = _lib.load()
+        with torch.cuda.device(dev):
+            ws, ready = ctx.bins, 6
+            ctx.bins = None
+            if ws is None:
+                nbytes = lib.dibr_soft_mask_workspace_bytes(b, b * f, h, w, 0, img.element_size())
+                ws, ready = torch.empty(max(int(nbytes), 256), dtype=torch.uint8, device=dev), 0
+            code = getattr(lib, "dibr_rasterization_bwd_fused_" + suf)(
+                _lib.ptr_array(gouts) if any_out else None, _lib.ptr(g_soft), _lib.ptr(soft), _lib.ptr(face_idx),
+                _lib.ptr(img), _lib.ptr_array(feats), _lib.int_array(chans), len(feats), b, f, h, w, multiplier, eps,
+                sigmainv, boxlen, knum, _lib.ptr(gi), _lib.ptr_array(gfs) if any_out else None, _lib.ptr(ws),
+                ws.numel(), ready, _lib.current_stream(dev))
+        _lib.check(code, fn)
+        gfs = gfs if any_out else [None] * len(feats)
+        return (None, None, None, gi, None, None, None, None, None, None, *gfs)
+
+
 def dibr_soft_mask(face_vertices_image, selected_face_idx,
                    sigmainv=7000, boxlen=0.02, knum=30, multiplier=1000.):
     r"""Soft foreground mask of DIB-R (reference: kaolin/render/mesh/dibr.py:75-117).
@@ -124,6 +223,16 @@ def dibr_rasterization(height, width, face_vertices_z, face_vertices_image,
     Returns:
         (features (B,H,W,C) or tuple of tensors, soft_mask (B,H,W), face_idx (B,H,W) int64, -1 = none)
     """
+    is_list = isinstance(face_features, (list, tuple))
+    feats = list(face_features) if is_list else [face_features]
+    if rast_backend == 'cuda' and 0 < len(feats) <= 8 and face_vertices_z.is_cuda and \
+            torch.is_tensor(face_normals_z) and face_normals_z.dtype == face_vertices_z.dtype and \
+            tuple(face_normals_z.shape) == tuple(face_vertices_z.shape[:2]):
+        # one native call each way (same values as the composition below, bit for bit)
+        *outs, soft_mask, face_idx = DibrRasterizationCuda.apply(
+            height, width, face_vertices_z, face_vertices_image, face_normals_z, sigmainv, boxlen, knum,
+            1000 if multiplier is None else multiplier, 1e-8 if eps is None else eps, *feats)
+        return (tuple(outs) if is_list else outs[0]), soft_mask, face_idx
     interpolated_features, face_idx = rasterize(
         height, width,
         face_vertices_z,

@@ -160,7 +160,14 @@ def test_c4_two_views_through_prepare_vertices_vs_ref_C(kal, O, ref_C):
     r_fcam, r_fimg, r_nrm = O.prepare_vertices(rleaf.expand(2, -1, -1), faces, proj, rot, eye)
     norm_close(fcam, r_fcam, 1e-5, "face_vertices_camera")
     norm_close(fimg, r_fimg, 1e-5, "face_vertices_image")
-    norm_close(nrm, r_nrm, 1e-4, "face_normals")
+    # unit normals of the 800 zero-area faces at the poles of the lat/long grid are rounding noise (the reference's
+    # own fp32 and fp64 evaluations differ by 0.5 there): compared on the faces with a resolvable area
+    e0, e1 = (r_fcam[:, :, 1] - r_fcam[:, :, 0]).double(), (r_fcam[:, :, 2] - r_fcam[:, :, 0]).double()
+    area_ok = (torch.cross(e0, e1, dim=-1).norm(dim=-1) > 1e-6).unsqueeze(-1)
+    assert float(area_ok.float().mean()) > 0.95
+    # (and the first rings of slivers next to the poles are ill-conditioned: the reference's fp32 normals are 1.9e-4
+    # off its fp64 ones on this mesh, so two fp32 evaluations are held to 1e-3)
+    norm_close(torch.where(area_ok, nrm, 0), torch.where(area_ok, r_nrm, 0), 1e-3, "face_normals")
     # -- rasterization path on identical face tensors
     z_d, img_d, nz_d = fcam[..., 2].detach().contiguous(), fimg.detach().contiguous(), nrm[..., 2].detach().contiguous()
     r = reference_chain(O, ref_C, Hh, Ww, z_d, img_d, vcol, nz_d >= 0., g_feat, g_soft)
@@ -263,3 +270,51 @@ def test_fused_fp32_soft_mask_adversarial_vs_ref_C(kal, O, ref_C, kind, sigmainv
     assert float(r_soft.max()) > 0.5, "the scene must put pixels close to faces"
     elem_close(soft, r_soft, 1e-4, f"soft_mask ({kind}, sigmainv {sigmainv}, multiplier {multiplier})")
     norm_close(img.grad, r_gs, 1e-4, f"grad ({kind}, sigmainv {sigmainv}, multiplier {multiplier})")
+
+
+# ------------------------------------------------------------------------------------------------ fused entry point
+@pytest.mark.parametrize("dtype", [torch.float32, torch.float64])
+def test_fused_dibr_rasterization_equals_the_separate_calls(kal, dtype):
+    """dibr_rasterization runs ONE native call each way (both list sets from one read of the coordinates, one
+    gradient tensor accumulated by both backward kernels): forward values are bit-identical to rasterize +
+    dibr_soft_mask (test_dibr.py:527-529), gradients equal to rounding — single tensor and list features, either
+    output alone and both."""
+    from kaolin_b200 import synth
+    d = synth.make_inputs("c1")
+    Hh, Ww = 96, 80
+    z = d["face_vertices_z"].to("cuda", dtype).repeat(2, 1, 1)
+    img0 = d["face_vertices_image"].to("cuda", dtype).repeat(2, 1, 1, 1)
+    img0[1] = img0[1] * 0.7 + 0.1
+    f0 = d["face_features"][0].to("cuda", dtype).repeat(2, 1, 1, 1)
+    nz = d["face_normals_z"].to("cuda", dtype).repeat(2, 1)
+    g = torch.Generator().manual_seed(3)
+    for feats0 in ([f0], [f0[..., :1].contiguous(), f0[..., 1:].contiguous()]):
+        is_list = len(feats0) > 1
+        g_out = [torch.rand(2, Hh, Ww, f.shape[-1], generator=g, dtype=torch.float64).to("cuda", dtype) for f in feats0]
+        g_soft = torch.rand(2, Hh, Ww, generator=g, dtype=torch.float64).to("cuda", dtype)
+        for which in ("both", "soft", "features"):
+            res = []
+            for fused in (True, False):
+                img = img0.clone().requires_grad_(True)
+                feats = [f.clone().requires_grad_(True) for f in feats0]
+                arg = feats if is_list else feats[0]
+                if fused:
+                    out, soft, idx = kal.render.mesh.dibr_rasterization(Hh, Ww, z, img, arg, nz, 7000., 0.03, 20)
+                else:
+                    out, idx = kal.render.mesh.rasterize(Hh, Ww, z, img, arg, nz >= 0.)
+                    soft = kal.render.mesh.dibr_soft_mask(img, idx, 7000., 0.03, 20)
+                outs = list(out) if is_list else [out]
+                ts, gs = [], []
+                if which in ("both", "features"):
+                    ts, gs = ts + outs, gs + g_out
+                if which in ("both", "soft"):
+                    ts, gs = ts + [soft], gs + [g_soft]
+                torch.autograd.backward(ts, gs)
+                res.append((outs, soft, idx, img.grad, [f.grad for f in feats]))
+            (o_a, s_a, i_a, gi_a, gf_a), (o_b, s_b, i_b, gi_b, gf_b) = res
+            assert torch.equal(i_a, i_b) and torch.equal(s_a, s_b) and all(torch.equal(x, y) for x, y in zip(o_a, o_b))
+            norm_close(gi_a, gi_b, 1e-5 if dtype == torch.float32 else 1e-12, f"grad img ({which})")
+            for x, y in zip(gf_a, gf_b):
+                assert (x is None) == (y is None), which
+                if x is not None:
+                    norm_close(x, y, 1e-5 if dtype == torch.float32 else 1e-12, f"grad feats ({which})")

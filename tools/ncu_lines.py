@@ -39,7 +39,8 @@ def src_text(ln):
     import os
     f, n = ln
     if f not in _SRC:
-        path = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "kaolin_b200", "csrc", f)
+        root = os.environ.get("DIBR_SRC_ROOT") or os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+        path = os.path.join(root, "kaolin_b200", "csrc", f)      # DIBR_SRC_ROOT: the tree the profiled .so was built from
         _SRC[f] = open(path).read().split("\n") if os.path.exists(path) else []
     return _SRC[f][n - 1].strip()[:90] if 0 < n <= len(_SRC[f]) else ""
 
