@@ -812,7 +812,10 @@ DIBR_API int dibr_profile_next_launch(int kernel_id, void* start_event, void* st
 
 DIBR_API size_t dibr_workspace_bytes(int batch_size, int64_t total_faces, int height, int width) {
   if (batch_size < 0 || total_faces < 0 || height < 0 || width < 0) return 0;
-  return ws_layout(batch_size, total_faces, make_geometry(batch_size, height, width)).total;
+  const Geometry geo = make_geometry(batch_size, height, width);
+  const size_t a = ws_layout(batch_size, total_faces, geo).total;                      // rasterizer / deftet layout
+  const size_t b = fused_layout(batch_size, total_faces, false, geo).total_no_log;     // soft-mask entry points
+  return a > b ? a : b;
 }
 
 DIBR_API size_t dibr_soft_mask_workspace_bytes(int batch_size, int64_t total_faces, int height, int width,
