@@ -63,7 +63,8 @@ enum {
   DIBR_ERR_INVALID_ARGUMENT = 1, /* null pointer, negative size, unsupported value */
   DIBR_ERR_WORKSPACE = 2,        /* ws == NULL or ws_bytes too small */
   DIBR_ERR_CUDA = 3,             /* a CUDA runtime call / kernel launch failed (dibr_last_cuda_error) */
-  DIBR_ERR_TOO_LARGE = 4         /* a dimension exceeds what the kernels index (H, W <= 32768; B*F < 2^31) */
+  DIBR_ERR_TOO_LARGE = 4,        /* a dimension exceeds what the kernels index (H, W <= 32768; B*F < 2^31) */
+  DIBR_ERR_SCRATCH_LIMIT = 5     /* a _noalloc entry point needs more than DIBR_NOALLOC_SCRATCH_BYTES of scratch */
 };
 
 int dibr_abi_version(void);
@@ -338,6 +339,26 @@ int dibr_mask_iou_fwd_f32(const float* lhs, const float* rhs, int B, int64_t P, 
                           void* ws, size_t ws_bytes, void* stream);
 int dibr_mask_iou_fwd_f64(const double* lhs, const double* rhs, int B, int64_t P, double* loss, double* sums,
                           void* ws, size_t ws_bytes, void* stream);
+/* mask_iou forward WITHOUT a caller workspace and without any allocation.
+ *  No counterpart in the reference: added for callers that cannot call
+ *  cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid it).  Same inputs, outputs and
+ *  results as dibr_mask_iou_fwd_* (it runs the same two kernels); the scratch of the two-stage reduction lives in a
+ *  file-scope `static __device__` array of DIBR_NOALLOC_SCRATCH_BYTES inside the library, which every GPU that loads
+ *  the library holds until the process exits.  The call makes no cudaMalloc / cudaFree / allocating library call; the
+ *  first call per device takes the array's device address with cudaGetSymbolAddress (set-up), later calls only launch.
+ *  Limit: dibr_mask_iou_workspace_bytes(B, P, elem_size) <= dibr_noalloc_scratch_bytes(), i.e. B * ceil(P / 8192)
+ *  <= 131072 (fp32) / 65536 (fp64) — e.g. 128 views of 2048 x 2048 in fp32; beyond it the call returns
+ *  DIBR_ERR_SCRATCH_LIMIT before touching the GPU (use dibr_mask_iou_fwd_* with a workspace instead).
+ *  The array is shared by every call on the device and keeps the last call's contents; nothing in it must start at
+ *  zero (each call writes every slot it reads).  Calls that OVERLAP on the GPU — different streams without an
+ *  ordering between them — race on it: serialise them.  On one stream, back-to-back calls are safe.
+ */
+#define DIBR_NOALLOC_SCRATCH_BYTES (1u << 20)
+size_t dibr_noalloc_scratch_bytes(void);
+int dibr_mask_iou_fwd_noalloc_f32(const float* lhs, const float* rhs, int B, int64_t P, float* loss, float* sums,
+                                  void* stream);
+int dibr_mask_iou_fwd_noalloc_f64(const double* lhs, const double* rhs, int B, int64_t P, double* loss,
+                                  double* sums, void* stream);
 int dibr_mask_iou_bwd_f32(const float* grad_loss, const float* lhs, const float* rhs, const float* sums,
                           int B, int64_t P, float* grad_lhs, float* grad_rhs, void* stream);
 int dibr_mask_iou_bwd_f64(const double* grad_loss, const double* lhs, const double* rhs, const double* sums,

@@ -51,6 +51,7 @@ _TYPED = {
     "dibr_texture_mapping_fwd": [c_p, c_p, c_p, c_i, c_i64, c_i, c_i, c_i, c_i, c_i, c_p, c_p],
     "dibr_texture_mapping_bwd": [c_p, c_p, c_p, c_p, c_i, c_i64, c_i, c_i, c_i, c_i, c_i, c_p, c_p, c_p, c_p],
     "dibr_mask_iou_fwd": [c_p, c_p, c_i, c_i64, c_p, c_p, c_p, c_sz, c_p],
+    "dibr_mask_iou_fwd_noalloc": [c_p, c_p, c_i, c_i64, c_p, c_p, c_p],
     "dibr_mask_iou_bwd": [c_p, c_p, c_p, c_p, c_i, c_i64, c_p, c_p, c_p],
     "dibr_deftet_forward": [c_p, c_p, c_p, c_p, c_p, c_i, c_i, c_i, c_i, c_f, c_p, c_p, c_p, c_p, c_p, c_sz, c_p],
     "dibr_deftet_render_fused": [c_p, c_p, c_p, c_p, c_p, c_p, c_i, c_i, c_i, c_i, c_i, c_f, c_p, c_p, c_p, c_p,
@@ -59,7 +60,7 @@ _TYPED = {
 }
 EXPORTED_SYMBOLS = (["dibr_abi_version", "dibr_error_string", "dibr_last_cuda_error", "dibr_workspace_bytes",
                      "dibr_kernel_launch_count", "dibr_reset_kernel_launch_count", "dibr_profile_next_launch",
-                     "dibr_mask_iou_workspace_bytes", "dibr_deftet_workspace_bytes",
+                     "dibr_mask_iou_workspace_bytes", "dibr_noalloc_scratch_bytes", "dibr_deftet_workspace_bytes",
                      "dibr_soft_mask_workspace_bytes", "dibr_rasterization_workspace_bytes"] +
                     [f"{n}_{s}" for n in _TYPED for s in ("f32", "f64")])
 
@@ -111,6 +112,8 @@ def load():
         lib.dibr_mask_iou_workspace_bytes.argtypes = [c_i, c_i64, c_i]
         lib.dibr_soft_mask_workspace_bytes.restype = c_sz
         lib.dibr_soft_mask_workspace_bytes.argtypes = [c_i, c_i64, c_i, c_i, c_i, c_i]
+        lib.dibr_noalloc_scratch_bytes.restype = c_sz
+        lib.dibr_noalloc_scratch_bytes.argtypes = []
         lib.dibr_rasterization_workspace_bytes.restype = c_sz
         lib.dibr_rasterization_workspace_bytes.argtypes = [c_i, c_i64, c_i, c_i, c_i]
         lib.dibr_deftet_workspace_bytes.restype = c_sz

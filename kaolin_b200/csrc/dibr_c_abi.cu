@@ -672,6 +672,49 @@ int iou_bwd_impl(const T* g_loss, const T* lhs, const T* rhs, const T* sums, int
   return DIBR_OK;
 }
 
+// ---- allocation-free variant of mask_iou forward (no counterpart in the reference; added
+// for callers that cannot allocate: code under CUDA graph capture, tight serving loops, harnesses that
+// forbid cudaMalloc).  Its scratch — the per-chunk partial sums of the two-stage reduction — lives in this file-scope
+// device array instead of a caller-provided workspace.  Every GPU that loads the library holds these
+// DIBR_NOALLOC_SCRATCH_BYTES (1 MiB) until the process exits.
+//   * In HOST code `g_noalloc_scratch` is only a host-side stand-in for the symbol, NOT a device address: the address
+//     is taken once per device, with that device current, by cudaGetSymbolAddress below, and that pointer is what the
+//     kernels get.
+//   * All calls on a device share the array and it keeps the last call's contents.  Nothing in it has to start at
+//     zero: mask_iou_partial_kernel writes every (view, chunk) slot that mask_iou_finish_kernel reads, in the same
+//     call.  Calls that overlap on the GPU (different streams, no ordering between them) RACE on it.
+constexpr size_t NOALLOC_SCRATCH_BYTES = DIBR_NOALLOC_SCRATCH_BYTES;
+static __device__ __align__(256) unsigned char g_noalloc_scratch[NOALLOC_SCRATCH_BYTES];
+constexpr int NOALLOC_MAX_DEVICES = 64;
+std::atomic<void*> g_noalloc_ptr[NOALLOC_MAX_DEVICES];
+
+// device address of the scratch array on the CURRENT device (set-up: once per device; afterwards one atomic load)
+int noalloc_scratch_ptr(void** out) {
+  int dev = 0;
+  CUDA_TRY(cudaGetDevice(&dev));
+  if (dev < 0 || dev >= NOALLOC_MAX_DEVICES) return DIBR_ERR_INVALID_ARGUMENT;
+  void* p = g_noalloc_ptr[dev].load(std::memory_order_acquire);
+  if (!p) {
+    CUDA_TRY(cudaGetSymbolAddress(&p, g_noalloc_scratch));      // `dev` is current: its copy of the array
+    if (!p) return cuda_fail(cudaErrorInvalidSymbol, "cudaGetSymbolAddress(g_noalloc_scratch)");
+    g_noalloc_ptr[dev].store(p, std::memory_order_release);
+  }
+  *out = p;
+  return DIBR_OK;
+}
+
+template <typename T>
+int iou_fwd_noalloc_impl(const T* lhs, const T* rhs, int B, int64_t P, T* loss, T* sums, void* stream) {
+  if (B < 0 || P < 0 || !loss) return DIBR_ERR_INVALID_ARGUMENT;
+  if (B > 65535 || P >= (int64_t)1 << 40) return DIBR_ERR_TOO_LARGE;
+  const size_t need = iou_ws_bytes(B, P, (int)sizeof(T));
+  if (need > NOALLOC_SCRATCH_BYTES) return DIBR_ERR_SCRATCH_LIMIT;     // before any CUDA call
+  void* scratch = nullptr;
+  if (int e = noalloc_scratch_ptr(&scratch)) return e;
+  // the existing forward on the built-in scratch: two kernel launches on `stream`, no allocation of any kind
+  return iou_fwd_impl<T>(lhs, rhs, B, P, loss, sums, scratch, NOALLOC_SCRATCH_BYTES, stream);
+}
+
 // deftet_sparse_render (deftet.py:269-417).  Grid resolution: about 8 faces per cell, G in [1, 512].
 inline int deftet_grid(int F) {
   int g = (int)std::ceil(std::sqrt((double)(F > 0 ? F : 1) / 8.0));
@@ -796,6 +839,9 @@ DIBR_API const char* dibr_error_string(int code) {
     case DIBR_ERR_WORKSPACE: return "workspace missing or smaller than dibr_workspace_bytes()";
     case DIBR_ERR_CUDA: return "CUDA error (see dibr_last_cuda_error)";
     case DIBR_ERR_TOO_LARGE: return "dimension too large for the kernels' index types";
+    case DIBR_ERR_SCRATCH_LIMIT:
+      return "input needs more scratch than the built-in array of the _noalloc entry point holds "
+             "(dibr_noalloc_scratch_bytes(); use the variant that takes a caller workspace)";
     default: return "unknown error code";
   }
 }
@@ -843,6 +889,7 @@ DIBR_API size_t dibr_deftet_workspace_bytes(int batch_size, int64_t total_faces)
 DIBR_API size_t dibr_mask_iou_workspace_bytes(int B, int64_t P, int elem_size) {
   return iou_ws_bytes(B, P, elem_size);
 }
+DIBR_API size_t dibr_noalloc_scratch_bytes(void) { return NOALLOC_SCRATCH_BYTES; }
 
 #define DEFINE_ENTRY_POINTS(SUF, T)                                                                           \
   DIBR_API int dibr_rasterize_fwd_fused_##SUF(const T* z, const T* img, const T* feat, const uint8_t* valid, \
@@ -977,6 +1024,10 @@ DIBR_API size_t dibr_mask_iou_workspace_bytes(int B, int64_t P, int elem_size) {
   DIBR_API int dibr_mask_iou_fwd_##SUF(const T* lhs, const T* rhs, int B, int64_t P, T* loss, T* sums,       \
                                        void* ws, size_t ws_bytes, void* stream) {                            \
     return iou_fwd_impl<T>(lhs, rhs, B, P, loss, sums, ws, ws_bytes, stream);                                 \
+  }                                                                                                           \
+  DIBR_API int dibr_mask_iou_fwd_noalloc_##SUF(const T* lhs, const T* rhs, int B, int64_t P, T* loss,        \
+                                               T* sums, void* stream) {                                      \
+    return iou_fwd_noalloc_impl<T>(lhs, rhs, B, P, loss, sums, stream);                                       \
   }                                                                                                           \
   DIBR_API int dibr_mask_iou_bwd_##SUF(const T* grad_loss, const T* lhs, const T* rhs, const T* sums,        \
                                        int B, int64_t P, T* grad_lhs, T* grad_rhs, void* stream) {           \

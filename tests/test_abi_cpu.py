@@ -39,7 +39,7 @@ def test_header_symbols_exported(lib):
 def test_host_only_entry_points(lib):
     assert lib.dibr_abi_version() == 7
     assert lib.dibr_error_string(0) == b"ok"
-    for code in (1, 2, 3, 4, 99):
+    for code in (1, 2, 3, 4, 5, 99):
         assert len(lib.dibr_error_string(code)) > 0
     n = lib.dibr_workspace_bytes(16, 16 * 20000, 512, 512)
     assert n > 16 * 20000 * 8 and n % 256 == 0
