@@ -108,6 +108,20 @@ __device__ __forceinline__ void load_face_xy<float>(const float* img, int64_t g,
 // pixel range; (tx0..tx1, ty0..ty1) its tile rectangle; `local` its index in view `b`.
 // One level (fine tiles or coarse cells) of bin_faces_warp: lanes with `act` hold the cell rectangle (x0..x1, y0..y1)
 // of their face in a grid that is `stride` cells wide, whose counters start at `slot0` of the view's slots.
+// 32 x 32 bit transpose across the warp: lane i passes row i and gets column i (bit r of the result = bit i of
+// lane r's argument).  Five butterfly stages, one shuffle each.
+__device__ __forceinline__ unsigned warp_transpose32(unsigned a) {
+  const int lane = threadIdx.x & 31;
+#pragma unroll
+  for (int j = 16; j > 0; j >>= 1) {
+    const unsigned m = j == 16 ? 0x0000ffffu : j == 8 ? 0x00ff00ffu : j == 4 ? 0x0f0f0f0fu : j == 2 ? 0x33333333u
+                                                                                                    : 0x55555555u;
+    const unsigned o = __shfl_xor_sync(0xffffffffu, a, j);
+    a = (lane & j) ? ((a & ~m) | ((o & ~m) >> j)) : ((a & m) | ((o & m) << j));
+  }
+  return a;
+}
+
 template <bool FILL>
 __device__ __forceinline__ void bin_level_warp(const bool act, const int b, const int local, const int x0,
                                                const int x1, const int y0, const int y1, const int slot0,
@@ -124,39 +138,54 @@ __device__ __forceinline__ void bin_level_warp(const bool act, const int b, cons
   const int uy1 = __reduce_max_sync(0xffffffffu, act ? y1 : -1);
   const int uw = ux1 - ux0 + 1, ncell = uw * (uy1 - uy0 + 1);
   if (same && ncell <= 64) {
+    // The warp's (face, cell) incidences as a 32 x 64 bit matrix: lane = face holds the row-major mask of the union
+    // cells its rectangle covers (<= 16 bits); one bit-matrix transpose (two when the union has more than 32 cells)
+    // hands lane c the set of faces in union cells c and c + 32 — their popcounts are the cells' counts, and a face's
+    // position inside a cell is its rank in that set (face order inside the warp).  Lane c issues the ONE atomic of
+    // (warp, cell c); no walk over the union's cells (that walk — a ballot and four compares per cell — was 50 % of
+    // setup_count's and 85 % of fill's instructions: ncu, profiles/r02_a_c3_b8_ncu_summary.csv).
     int* ctr = ctr0 + (int64_t)b0 * geo.slots_per_view;
+    unsigned long long cells = 0ull;
+    if (act) {
+      const unsigned long long row = ((1ull << (x1 - x0 + 1)) - 1ull) << (x0 - ux0);
+      for (int y = y0; y <= y1; ++y) cells |= row << ((y - uy0) * uw);
+    }
+    const bool two = ncell > 32;                                      // warp-uniform
+    const unsigned t_lo = warp_transpose32((unsigned)cells);
+    const unsigned t_hi = two ? warp_transpose32((unsigned)(cells >> 32)) : 0u;
+    // row / column of union cells `lane` and `lane + 32`: exact for c < 64, uw <= 64 (the quotient's fraction is at
+    // least 1 / 128 away from an integer, the product's error below 1e-5)
+    const float inv_uw = __frcp_rn((float)uw);
+    const int r_lo = (int)(((float)lane + 0.5f) * inv_uw), r_hi = (int)(((float)(lane + 32) + 0.5f) * inv_uw);
+    int* const p_lo = ctr + (uy0 + r_lo) * stride + ux0 + (lane - r_lo * uw);
+    int* const p_hi = ctr + (uy0 + r_hi) * stride + ux0 + (lane + 32 - r_hi * uw);
     if (!FILL) {
-      for (int y = uy0; y <= uy1; ++y)
-        for (int x = ux0; x <= ux1; ++x) {
-          const unsigned m = __ballot_sync(0xffffffffu, act && x >= x0 && x <= x1 && y >= y0 && y <= y1);
-          if (m != 0u && lane == 0) atomicAdd(ctr + y * stride + x, __popc(m));     // no return value: a RED
-        }
+      if (t_lo != 0u) atomicAdd(p_lo, __popc(t_lo));                  // no return value: a RED
+      if (t_hi != 0u) atomicAdd(p_hi, __popc(t_hi));
       return;
     }
-    // FILL: the reservations return a position.  Lane j makes the reservation of union cells j and j + 32, so that
-    // all of the warp's atomics are in flight together (one round trip instead of one per cell: a small scene's
-    // fill_kernel is nothing but that chain); a second walk hands every face its position — the cell's base from
-    // the lane that reserved it + the face's popc rank.
-    unsigned m_lo = 0u, m_hi = 0u;
-    {
-      int x = ux0, y = uy0;
-      for (int c = 0; c < ncell; ++c) {
-        const unsigned m = __ballot_sync(0xffffffffu, act && x >= x0 && x <= x1 && y >= y0 && y <= y1);
-        if ((c & 31) == lane) { if (c < 32) m_lo = m; else m_hi = m; }
-        if (++x > ux1) { x = ux0; ++y; }
-      }
-    }
+    // FILL: all of the warp's reservations are in flight together (one round trip); then every face walks its OWN
+    // cells (<= 16) and takes the cell's base and member set from the lane that owns the cell.
     int base_lo = 0, base_hi = 0;
-    if (m_lo != 0u) base_lo = atomicAdd(ctr + (uy0 + lane / uw) * stride + ux0 + lane % uw, __popc(m_lo));
-    if (m_hi != 0u) base_hi = atomicAdd(ctr + (uy0 + (lane + 32) / uw) * stride + ux0 + (lane + 32) % uw, __popc(m_hi));
-    {
-      int x = ux0, y = uy0;
-      for (int c = 0; c < ncell; ++c) {
-        const bool hit = act && x >= x0 && x <= x1 && y >= y0 && y <= y1;
-        const unsigned m = __ballot_sync(0xffffffffu, hit);
-        const int base = __shfl_sync(0xffffffffu, c < 32 ? base_lo : base_hi, c & 31);
-        if (hit) L.pairs[base + __popc(m & ((1u << lane) - 1u))] = local;
-        if (++x > ux1) { x = ux0; ++y; }
+    if (t_lo != 0u) base_lo = atomicAdd(p_lo, __popc(t_lo));
+    if (t_hi != 0u) base_hi = atomicAdd(p_hi, __popc(t_hi));
+    const int n_own = act ? (x1 - x0 + 1) * (y1 - y0 + 1) : 0;
+    const int n_max = __reduce_max_sync(0xffffffffu, n_own);
+    const unsigned lt = (1u << lane) - 1u;
+    int cx = x0, cy = y0;
+    for (int k = 0; k < n_max; ++k) {                                 // warp-uniform trip count
+      const bool mine = k < n_own;
+      const int c = mine ? (cy - uy0) * uw + (cx - ux0) : 0;
+      unsigned t = __shfl_sync(0xffffffffu, t_lo, c & 31);
+      int base = __shfl_sync(0xffffffffu, base_lo, c & 31);
+      if (two) {
+        const unsigned t2 = __shfl_sync(0xffffffffu, t_hi, c & 31);
+        const int base2 = __shfl_sync(0xffffffffu, base_hi, c & 31);
+        if (c >= 32) { t = t2; base = base2; }
+      }
+      if (mine) {
+        L.pairs[base + __popc(t & lt)] = local;
+        if (++cx > x1) { cx = x0; ++cy; }
       }
     }
     return;

@@ -199,6 +199,7 @@ int rasterize_fwd_impl(const T* z, const T* img, const T* bbox_in, const T* cons
   RasterFwdParams<T> rp;
   rp.z = z; rp.img = img; rp.feat = fin; rp.coord_mult = coord_mult; rp.premultiplied = premultiplied;
   rp.pix_mult = pix_mult; rp.eps = eps; rp.out_feat = fout; rp.out_idx = out_idx; rp.out_w = out_w;
+  rp.soft_out = nullptr; rp.tile_unc = nullptr;
   {
     ProfScope ps(DIBR_KERNEL_RASTER_FWD, s);
     launch_raster_fwd(rp, fl, geo, L, s);
@@ -308,6 +309,7 @@ struct FusedLayout {
   WsLayout soft, rast;
   LogLayout log;
   bool has_rast;
+  size_t unc;                      // per-tile coverage maps handed from the rasterizer to the soft mask (has_rast only)
   size_t zero_begin, zero_end, total_no_log, total;
 };
 FusedLayout fused_layout(int B, int64_t Ntot, bool with_raster, const Geometry& geo) {
@@ -333,6 +335,8 @@ FusedLayout fused_layout(int B, int64_t Ntot, bool with_raster, const Geometry& 
   f.zero_end = o;
   o = ws_rest_part(f.soft, B, Ntot, geo, o);
   if (with_raster) o = ws_rest_part(f.rast, B, Ntot, geo, o);
+  f.unc = o;
+  if (with_raster) o = align_up(o + nt * (TILE_PIX / 32) * sizeof(unsigned));
   f.total_no_log = o;
   l.over = o;   o = align_up(o + nt * sizeof(unsigned));
   l.recs = o;   o = align_up(o + (size_t)l.cap_seg * LOG_SEGMENTS * sizeof(uint4));   // 16-byte records, fp32 and fp64
@@ -436,7 +440,7 @@ int soft_mask_impl(const T* img, const T* bbox_in, const int64_t* face_idx, int 
   p.img = img; p.coord_mult = coord_mult; p.premultiplied = premultiplied; p.pix_mult = pix_mult;
   p.sigmainv = sigmainv; p.F = F; p.knum = knum; p.face_idx = face_idx; p.soft = soft; p.prob = prob;
   p.close_idx = close_idx; p.dist_type = dist_type; p.grad_soft = grad_soft; p.soft_in = soft_in;
-  p.grad_img = grad_img;
+  p.grad_img = grad_img; p.tile_unc = nullptr;
   return soft_launch_on_lists<T, MODE>(p, fl, geo, L, ws, fz, use_log, s);
 }
 
@@ -481,6 +485,11 @@ int dibr_rasterization_fwd_impl(const T* z, const T* img, const T* const* feats,
   RasterFwdParams<T> rp;
   rp.z = z; rp.img = img; rp.feat = fin; rp.coord_mult = (T)multiplier; rp.premultiplied = 0;
   rp.pix_mult = pix_mult; rp.eps = eps; rp.out_feat = fout; rp.out_idx = out_idx; rp.out_w = nullptr;
+  // fp32: the rasterizer's epilogue hands every tile's coverage map (and the provisional soft values) to the
+  // soft-mask kernel; the fp64 gather kernel does not, and the soft-mask kernel then reads face_idx as usual
+  unsigned* const tile_unc = sizeof(T) == 4 ? reinterpret_cast<unsigned*>(static_cast<unsigned char*>(ws) + fz.unc)
+                                            : nullptr;
+  rp.soft_out = tile_unc ? soft : nullptr; rp.tile_unc = tile_unc;
   {
     ProfScope ps(DIBR_KERNEL_RASTER_FWD, s);
     launch_raster_fwd(rp, fl, geo, LL.l[0], s);
@@ -490,6 +499,7 @@ int dibr_rasterization_fwd_impl(const T* z, const T* img, const T* const* feats,
   p.img = img; p.coord_mult = (T)multiplier; p.premultiplied = 0; p.pix_mult = pix_mult;
   p.sigmainv = sigmainv; p.F = F; p.knum = knum; p.face_idx = out_idx; p.soft = soft; p.prob = nullptr;
   p.close_idx = nullptr; p.dist_type = nullptr; p.grad_soft = nullptr; p.soft_in = nullptr; p.grad_img = nullptr;
+  p.tile_unc = tile_unc;
   return soft_launch_on_lists<T, MODE_FWD>(p, fl, geo, LL.l[1], ws, fz, use_log, s);
 }
 

@@ -39,6 +39,12 @@ struct RasterFwdParams {
   FeatSet<T> out_feat;     // n tensors (B,H,W,C_t)
   int64_t* out_idx;        // (B,H,W)
   T* out_w;                // (B,H,W,3) or nullptr
+  // dibr_rasterization only (fp32 scatter kernel; nullptr otherwise): the epilogue also writes the soft mask's value of
+  // every pixel that the soft-mask kernel may not touch (1 = covered, dibr_soft_mask_cuda.cu:68-70; 0 = uncovered
+  // without candidates) and the tile's 256-bit map of uncovered pixels (8 words per tile, bit = t & 31 of word t >> 5,
+  // t = row * 16 + column), so that the soft-mask kernel neither re-reads face_idx nor visits finished tiles.
+  T* soft_out;             // (B,H,W) or nullptr
+  unsigned* tile_unc;      // [B * tiles_per_view * 8] or nullptr
 };
 
 template <typename T>
@@ -512,54 +518,63 @@ raster_fwd_scatter_kernel(RasterFwdParams<float> rp, FaceLayout fl, Geometry geo
   __syncthreads();
 
   const bool nan_seen = sh.nan_seen != 0;                             // CTA-uniform, rare
-  for (int t = threadIdx.x; t < TILE_PIX; t += NT) {
+  unsigned* const unc = rp.tile_unc
+      ? rp.tile_unc + ((size_t)b * geo.tiles_per_view + (size_t)(ty * geo.tiles_x + tx)) * (TILE_PIX / 32) : nullptr;
+  for (int t = threadIdx.x; t < TILE_PIX; t += NT) {                   // uniform trip count (TILE_PIX % NT == 0)
     const int px = rx0 + (t & (TILE - 1)), py = ry0 + (t / TILE);
-    if (px >= geo.W || py >= geo.H) continue;
-    const float x0 = sh.px[t & (TILE - 1)], y0 = sh.py[t / TILE];
+    const bool in_image = px < geo.W && py < geo.H;
     int best_f = -1;
-    float bw0 = 0, bw1 = 0, bw2 = 0;
-    if (nan_seen) {
-      scan_pixel_in_order_rule(rp, L, tl, vbase, px, py, x0, y0, best_f, bw0, bw1, bw2);
-    } else {
-      const unsigned long long key = sh.key[t];
-      if ((unsigned)(key >> 32) != ORD_NEG_INF) {
-        best_f = (int)(0xffffffffu - (unsigned)key);
-        float p[6];
-        load_face_xy<float>(rp.img, vbase + best_f, rp.coord_mult, rp.premultiplied, p);
-        bary_weights<float>(p[0], p[1], p[2], p[3], p[4], p[5], x0, y0, rp.eps, bw0, bw1, bw2);
+    if (in_image) {
+      const float x0 = sh.px[t & (TILE - 1)], y0 = sh.py[t / TILE];
+      float bw0 = 0, bw1 = 0, bw2 = 0;
+      if (nan_seen) {
+        scan_pixel_in_order_rule(rp, L, tl, vbase, px, py, x0, y0, best_f, bw0, bw1, bw2);
+      } else {
+        const unsigned long long key = sh.key[t];
+        if ((unsigned)(key >> 32) != ORD_NEG_INF) {
+          best_f = (int)(0xffffffffu - (unsigned)key);
+          float p[6];
+          load_face_xy<float>(rp.img, vbase + best_f, rp.coord_mult, rp.premultiplied, p);
+          bary_weights<float>(p[0], p[1], p[2], p[3], p[4], p[5], x0, y0, rp.eps, bw0, bw1, bw2);
+        }
       }
-    }
-    const int64_t pix = ((int64_t)b * geo.H + py) * geo.W + px;
-    rp.out_idx[pix] = (int64_t)best_f;
-    if (rp.out_w) {
-      float* w = rp.out_w + pix * 3;
-      w[0] = bw0; w[1] = bw1; w[2] = bw2;
-    }
-    // rasterization_cuda.cu:172-189 per feature tensor; small channel counts take fully unrolled loads / stores
-    for (int ft = 0; ft < rp.feat.n; ++ft) {
-      const int C = rp.feat.ch[ft];
-      const float* feat = rp.feat.ptr[ft];
-      float* out = rp.out_feat.ptr[ft];
-      switch (C) {
-        case 1: store_features<float, 1>(feat, out, vbase, pix, best_f, bw0, bw1, bw2); break;
-        case 2: store_features<float, 2>(feat, out, vbase, pix, best_f, bw0, bw1, bw2); break;
-        case 3: store_features<float, 3>(feat, out, vbase, pix, best_f, bw0, bw1, bw2); break;
-        case 4: store_features<float, 4>(feat, out, vbase, pix, best_f, bw0, bw1, bw2); break;
-        default: {
-          float* o = out + pix * C;
-          if (best_f >= 0) {
-            const float* f0 = feat + (vbase + best_f) * 3 * C;
-            const float* f1 = f0 + C;
-            const float* f2 = f1 + C;
-            int d = 0;
-            for (; d + 4 <= C; d += 4) interp_block<float, 4>(f0 + d, f1 + d, f2 + d, o + d, bw0, bw1, bw2);
-            if (d + 2 <= C) { interp_block<float, 2>(f0 + d, f1 + d, f2 + d, o + d, bw0, bw1, bw2); d += 2; }
-            if (d < C) interp_block<float, 1>(f0 + d, f1 + d, f2 + d, o + d, bw0, bw1, bw2);
-          } else {
-            for (int d = 0; d < C; ++d) o[d] = 0.0f;
+      const int64_t pix = ((int64_t)b * geo.H + py) * geo.W + px;
+      rp.out_idx[pix] = (int64_t)best_f;
+      if (rp.soft_out) rp.soft_out[pix] = best_f >= 0 ? 1.0f : 0.0f;    // final unless the soft-mask kernel finds hits
+      if (rp.out_w) {
+        float* w = rp.out_w + pix * 3;
+        w[0] = bw0; w[1] = bw1; w[2] = bw2;
+      }
+      // rasterization_cuda.cu:172-189 per feature tensor; small channel counts take fully unrolled loads / stores
+      for (int ft = 0; ft < rp.feat.n; ++ft) {
+        const int C = rp.feat.ch[ft];
+        const float* feat = rp.feat.ptr[ft];
+        float* out = rp.out_feat.ptr[ft];
+        switch (C) {
+          case 1: store_features<float, 1>(feat, out, vbase, pix, best_f, bw0, bw1, bw2); break;
+          case 2: store_features<float, 2>(feat, out, vbase, pix, best_f, bw0, bw1, bw2); break;
+          case 3: store_features<float, 3>(feat, out, vbase, pix, best_f, bw0, bw1, bw2); break;
+          case 4: store_features<float, 4>(feat, out, vbase, pix, best_f, bw0, bw1, bw2); break;
+          default: {
+            float* o = out + pix * C;
+            if (best_f >= 0) {
+              const float* f0 = feat + (vbase + best_f) * 3 * C;
+              const float* f1 = f0 + C;
+              const float* f2 = f1 + C;
+              int d = 0;
+              for (; d + 4 <= C; d += 4) interp_block<float, 4>(f0 + d, f1 + d, f2 + d, o + d, bw0, bw1, bw2);
+              if (d + 2 <= C) { interp_block<float, 2>(f0 + d, f1 + d, f2 + d, o + d, bw0, bw1, bw2); d += 2; }
+              if (d < C) interp_block<float, 1>(f0 + d, f1 + d, f2 + d, o + d, bw0, bw1, bw2);
+            } else {
+              for (int d = 0; d < C; ++d) o[d] = 0.0f;
+            }
           }
         }
       }
+    }
+    if (unc) {                                                         // (CTA-uniform)
+      const unsigned um = __ballot_sync(0xffffffffu, in_image && best_f < 0);
+      if (lane == 0) unc[t >> 5] = um;
     }
   }
 }

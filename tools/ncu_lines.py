@@ -68,7 +68,7 @@ def main():
             i = j
             if filt.replace(" ", "") not in name.replace("(int)", "").replace(" ", ""):
                 continue
-            norm = lambda t: t.replace("(int)", "").replace(" ", "").split("(dibr::")[0]
+            norm = lambda t: t.replace("(int)", "").replace("(bool)1", "true").replace("(bool)0", "false").replace(" ", "").split("(dibr::")[0]
             key = next((v for d, v in demangled.items() if norm(d) == norm(name)), None)
             lines = funcs.get(key, [])
             ci = hdr.index("Instructions Executed"); cs = hdr.index("# Samples")

@@ -22,7 +22,8 @@ KEYS = [("gpu__time_duration.sum", "duration"), ("dram__bytes_read.sum", "dram_r
         ("sm__warps_active.avg.pct_of_peak_sustained_active", "achieved_occupancy_pct"),
         ("launch__registers_per_thread", "registers"), ("sm__inst_executed.sum", "warp_instructions"),
         ("smsp__thread_inst_executed_per_inst_executed.ratio", "active_threads_per_warp")]
-NAMES = {"raster_fwd_scatter_kernel": "raster_fwd", "raster_fwd_kernel": "raster_fwd", "raster_bwd_kernel": "raster_bwd",
+NAMES = {"setup_count_kernel": "setup_count", "fill_kernel": "fill", "scan_kernel": "scan",
+         "raster_fwd_scatter_kernel": "raster_fwd", "raster_fwd_kernel": "raster_fwd", "raster_bwd_kernel": "raster_bwd",
          "soft_mask_kernel<float, 0": "soft_fwd", "soft_mask_kernel<float, 1": "soft_bwd_recompute",
          "soft_mask_bwd_log_kernel": "soft_bwd", "soft_mask_overflow_kernel": "soft_bwd_overflow",
          "soft_mask_kernel<double, 0": "soft_fwd_f64", "soft_mask_kernel<double, 1": "soft_bwd_f64"}
@@ -32,7 +33,11 @@ UNIT = {"byte": 1.0, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9, "ns": 1e-3, "us":
 
 def main():
     rep, out = sys.argv[1], sys.argv[2]
-    raw = subprocess.run(["ncu", "-i", rep, "--page", "raw", "--csv"], capture_output=True, text=True).stdout
+    if rep.endswith(".csv") or rep.endswith(".csv.gz"):      # a raw page exported on the GPU box (tools/prof_all.sh)
+        import gzip
+        raw = (gzip.open(rep, "rt") if rep.endswith(".gz") else open(rep)).read()
+    else:
+        raw = subprocess.run(["ncu", "-i", rep, "--page", "raw", "--csv"], capture_output=True, text=True).stdout
     rows = list(csv.reader(raw.splitlines()))
     hdr, units = rows[0], rows[1]
     idx = {h: i for i, h in enumerate(hdr)}

@@ -36,14 +36,21 @@ def main():
     g = torch.Generator().manual_seed(4242)
     g_feats = [torch.rand(B, H, W, f.shape[-1], generator=g).to(dev) for f in feats0]
     g_soft = torch.rand(B, H, W, generator=g).to(dev)
+    ones_nz = torch.ones(z.shape[0], z.shape[1], device=dev)
 
     def step():
         img = img0.detach().requires_grad_(True)
         feats = [f.detach().requires_grad_(True) for f in feats0]
         feats = feats if len(feats) > 1 else feats[0]
-        valid = None if nz is None else (nz >= 0.)
-        out, face_idx = kal.render.mesh.rasterize(H, W, z, img, feats, valid, d["multiplier"], d["eps"])
-        soft = kal.render.mesh.dibr_soft_mask(img, face_idx, d["sigmainv"], d["boxlen"], d["knum"], d["multiplier"])
+        if args.fused:          # the call bench.py times
+            out, soft, face_idx = kal.render.mesh.dibr_rasterization(
+                H, W, z, img, feats, ones_nz if nz is None else nz, d["sigmainv"], d["boxlen"], d["knum"],
+                d["multiplier"], d["eps"])
+        else:
+            valid = None if nz is None else (nz >= 0.)
+            out, face_idx = kal.render.mesh.rasterize(H, W, z, img, feats, valid, d["multiplier"], d["eps"])
+            soft = kal.render.mesh.dibr_soft_mask(img, face_idx, d["sigmainv"], d["boxlen"], d["knum"],
+                                                  d["multiplier"])
         outs = list(out) if isinstance(out, tuple) else [out]
         torch.autograd.backward(outs + [soft], g_feats + [g_soft])
 
