@@ -317,7 +317,7 @@ FusedLayout fused_layout(int B, int64_t Ntot, bool with_raster, const Geometry& 
   f.has_rast = with_raster;
   const int64_t P = (int64_t)geo.B * geo.H * geo.W;
   LogLayout& l = f.log;
-  l.ok = P > 0 && P < ((int64_t)1 << 32);                 // pixel indices are logged as u32
+  l.ok = P > 0 && P < ((int64_t)1 << 32) && Ntot < ((int64_t)1 << 29);   // pixel / face-view indices are logged as u32 / 29 bits
   int64_t cap = 2 * P + 65536;                            // measured: 0.5 - 1.3 pairs per pixel on configs 1-5
   static const long long forced = [] {                    // DIBR_SOFT_LOG_CAP=<entries>: tests of the overflow path
     const char* e = tuning_env("DIBR_SOFT_LOG_CAP");

@@ -6,12 +6,13 @@
 // contains the pixel (:80-171), so order is semantic: the tile's candidate faces (enlarged-bbox tile list +
 // filtered coarse / "large" faces) are taken in passes of increasing face-index ranges — a pass holds the ~2*NT
 // lowest remaining ids, chosen by one histogram sweep (select_hi) — gathered into shared memory, sorted by face
-// index (chunk_rank_sort) and turned into 32-bit coverage masks of the tile's columns and rows.
+// index (chunk_rank_sort) and turned into coverage masks of the tile's columns and rows, stored transposed per
+// chunk of 32 candidates (one word per column / row = the chunk's candidates covering it).
 //
-// Per pass: (A, once) compact the uncovered pixels; (B) every pixel gets the slots of its next hits, in face
-// order, until it has knum — per warp for its own pixels with lane = candidate and ballot / popc ranks when the
-// tile has few uncovered pixels, lane = pixel sweeps otherwise; (C) the (pixel, k) pairs of a warp's pixels are
-// flattened and evaluated one per lane; (D) one lane per pixel multiplies the probabilities in face order.
+// Per pass: (A, once) compact the uncovered pixels (from the rasterizer's coverage map when it left one); (B) every
+// pixel gets the slots of its next hits, in face order, until it has knum — lane = pixel, one AND of its column and
+// row words tests 32 candidates; (C) the (pixel, k) pairs of a warp's pixels are flattened and evaluated one per
+// lane; (D) one lane per pixel multiplies the probabilities in face order.
 //
 // MODE_FWD writes soft (+ optional k-list side buffers, API-visible through
 // _C.render.mesh.dibr_soft_mask_forward_cuda).  MODE_BWD re-derives the same k-list with the same
@@ -25,9 +26,6 @@ namespace dibr {
 
 #ifndef DIBR_SOFT_TPS
 #define DIBR_SOFT_TPS 1024       // resident threads per SM the fp32 register allocation aims at
-#endif
-#ifndef DIBR_SOFT_PWB
-#define DIBR_SOFT_PWB 16         // per-warp k-list building up to this many uncovered pixels per warp
 #endif
 #ifndef DIBR_SOFT_CELLS
 #define DIBR_SOFT_CELLS 32       // k-list cells per thread of the CTA
@@ -59,7 +57,7 @@ struct SoftParams {
   const T* soft_in;           // (B,H,W)
   T* grad_img;                // (B,F,3,2)
   // pair log (optional; written by the fused forward, consumed by soft_mask_bwd_log_kernel): every evaluated
-  // (pixel, face) pair as one 16-byte record {global pixel index, face << 3 | distance type, probability}, in LOG_SEGMENTS
+  // (pixel, face) pair as one 16-byte record {global pixel index, (view * F + face) << 3 | distance type, probability}, in LOG_SEGMENTS
   // independent segments (a tile appends to segment hash(tile), one atomicAdd per warp and super-batch).
   // A tile whose reservation does not fit its segment raises its flag and enters the overflow list: its logged
   // pairs are ignored and soft_mask_overflow_kernel recomputes that tile (MODE_BWD).
@@ -589,19 +587,26 @@ __device__ __forceinline__ void soft_tile(const SoftParams<T>& sp, const FaceLay
         }
       }
       // ---- tile-local coverage mask of every candidate: bit x (columns) and bit 16 + y (rows) of the pixels
-      //      inside its enlarged bbox — the exact pixel range of the reference's float test (:89-97)
-      for (int k = threadIdx.x; k < count; k += NT) {
-        const uint2 r = L.ranges[vbase + s_ids[k]];
-        const int lx0 = max((int)(r.x & 0xffffu), rx0) - rx0, lx1 = min((int)(r.x >> 16), rx1) - rx0;
-        const int ly0 = max((int)(r.y & 0xffffu), ry0) - ry0, ly1 = min((int)(r.y >> 16), ry1) - ry0;
-        s_mask[k] = (lx0 <= lx1 && ly0 <= ly1) ? (bit_span16(lx0, lx1) | (bit_span16(ly0, ly1) << 16)) : 0u;
+      //      inside its enlarged bbox — the exact pixel range of the reference's float test (:89-97) — stored
+      //      TRANSPOSED per chunk of 32 candidates: word 32 c + x = the candidates of chunk c that cover column x,
+      //      word 32 c + 16 + y = those that cover row y, so that phase B tests 32 candidates against a pixel with
+      //      one AND (a warp handles whole chunks: the loop index advances by NT, a multiple of 32)
+      const int count32 = (count + 31) & ~31;
+      for (int k = threadIdx.x; k < count32; k += NT) {
+        unsigned m = 0u;
+        if (k < count) {
+          const uint2 r = L.ranges[vbase + s_ids[k]];
+          const int lx0 = max((int)(r.x & 0xffffu), rx0) - rx0, lx1 = min((int)(r.x >> 16), rx1) - rx0;
+          const int ly0 = max((int)(r.y & 0xffffu), ry0) - ry0, ly1 = min((int)(r.y >> 16), ry1) - ry0;
+          if (lx0 <= lx1 && ly0 <= ly1) m = bit_span16(lx0, lx1) | (bit_span16(ly0, ly1) << 16);
+        }
+        s_mask[k] = warp_transpose32(m);
       }
-      for (int k = count + threadIdx.x; k < ((count + 31) & ~31); k += NT) s_mask[k] = 0u;   // pad to 32 (>= 4)
       __syncthreads();
 
       // ---- phases B-D over super-batches of NPB uncovered pixels (usually the whole tile at once):
-      //      B  lane = pixel, 32 pixels per warp pass: one sweep over the candidate masks (uint4 broadcast
-      //         reads) appends the slots of the pixel's next hits, in face order, to its cell row, until it
+      //      B  lane = one of the warp's pixels: column word AND row word of every chunk of 32 candidates = the
+      //         pixel's hits in that chunk; their slots are appended, in face order, to its cell row, until it
       //         has K in total
       //      C  each warp takes an equal slice of the super-batch's pixels; their new (pixel, k) pairs are
       //         flattened (prefix sum of the list lengths; owner by REDUX/ballot/popc) and evaluated one per
@@ -609,55 +614,32 @@ __device__ __forceinline__ void soft_tile(const SoftParams<T>& sp, const FaceLay
       //         gradients)
       //      D  forward, lane = one of the warp's pixels: multiplies the new probabilities, in face order, into the
       //         pixel's running product (:174-182)
-      const int n4 = (count + 3) >> 2;
       for (int sb0 = 0; sb0 < U; sb0 += NPB) {
         const int nsb = min(NPB, U - sb0);
         const int PW = (nsb + NW - 1) / NW;              // pixels per warp (<= 32) in phase C
         const int ubase = warp * PW;
-        // -- B
-        if (PW <= DIBR_SOFT_PWB) {
-          // few uncovered pixels (the usual case away from silhouettes): every warp builds the k-lists of its OWN
-          // phase-C pixels, lane = candidate — 32 coverage masks per step, hits ranked by ballot / popc — instead of
-          // one warp sweeping all candidates for all pixels while the others wait; no CTA barrier before phase C
+        // -- B  (lane = one of the warp's own phase-C pixels; no CTA barrier before phase C)
+        {
           const int npx = max(0, min(PW, nsb - ubase));
-          for (int i = 0; i < npx; ++i) {                // warp-uniform
-            const int u = ubase + i;
-            const int t = s_upix[sb0 + u];
-            const int room = min(K - s_ktot[sb0 + u], KROW);
-            const unsigned mybit = (1u << (t & 15)) | (0x10000u << (t >> 4));
-            cell_int* row = s_celli + u * KS;
-            int kid = 0;
-            for (int j0 = 0; j0 < count && kid < room; j0 += 32) {
-              const bool hit = (s_mask[j0 + lane] & mybit) == mybit;       // masks are zero-padded to 32
-              const unsigned hm = __ballot_sync(0xffffffffu, hit);
-              const int pos = kid + __popc(hm & lt_mask);
-              if (hit && pos < room) row[pos] = (cell_int)(j0 + lane);
-              kid = min(room, kid + __popc(hm));
+          const bool actb = lane < npx;
+          const int u = ubase + lane;
+          const int t = actb ? s_upix[sb0 + u] : 0;
+          const int room = actb ? min(K - s_ktot[sb0 + u], KROW) : 0;
+          cell_int* row = s_celli + u * KS;
+          const unsigned* cm = s_mask + (t & 15);          // + 32 c: the chunk's candidates covering the pixel's column
+          const unsigned* rm = s_mask + 16 + (t >> 4);     //         ... and its row
+          int kid = 0;
+          for (int c = 0; c < count32; c += 32) {          // candidates in face order: chunk by chunk, bit by bit
+            if (!__any_sync(0xffffffffu, kid < room)) break;        // every list of the warp is full
+            unsigned h = kid < room ? (cm[c] & rm[c]) : 0u;
+            while (h != 0u && kid < room) {
+              row[kid++] = (cell_int)(c + __ffs(h) - 1);
+              h &= h - 1u;
             }
-            if (lane == 0) s_knew[u] = kid;
           }
-          __syncwarp();
-        } else {
-          for (int u0 = warp * 32; u0 < nsb; u0 += NT) {   // lane = pixel, uint4 broadcast reads of the masks
-            const int u = u0 + lane;
-            const bool act = u < nsb;
-            const int t = act ? s_upix[sb0 + u] : 0;
-            const int room = act ? min(K - s_ktot[sb0 + u], KROW) : 0;
-            const unsigned mybit = (1u << (t & 15)) | (0x10000u << (t >> 4));
-            cell_int* row = s_celli + u * KS;
-            int kid = 0;
-            for (int j = 0; j < n4; ++j) {
-              const uint4 m = reinterpret_cast<const uint4*>(s_mask)[j];
-              if ((m.x & mybit) == mybit && kid < room) { row[kid] = (cell_int)(4 * j); ++kid; }
-              if ((m.y & mybit) == mybit && kid < room) { row[kid] = (cell_int)(4 * j + 1); ++kid; }
-              if ((m.z & mybit) == mybit && kid < room) { row[kid] = (cell_int)(4 * j + 2); ++kid; }
-              if ((m.w & mybit) == mybit && kid < room) { row[kid] = (cell_int)(4 * j + 3); ++kid; }
-              if ((j & 7) == 7 && __all_sync(0xffffffffu, kid >= room)) break;
-            }
-            if (act) s_knew[u] = kid;
-          }
-          __syncthreads();
+          if (actb) s_knew[u] = kid;
         }
+        __syncwarp();
         // -- C
         if (ubase < nsb) {
           const int npix = min(PW, nsb - ubase);
@@ -727,7 +709,7 @@ __device__ __forceinline__ void soft_tile(const SoftParams<T>& sp, const FaceLay
               if (logging && lbase + (unsigned)q < sp.log_cap) {
                 const size_t o = (size_t)seg * sp.log_cap + lbase + (unsigned)q;
                 sp.log[o] = log_pack((unsigned)(((int64_t)b * geo.H + ry0 + ly) * geo.W + rx0 + lx),
-                                     ((unsigned)f << 3) | (unsigned)edgeid, prob,
+                                     ((unsigned)(vbase + f) << 3) | (unsigned)edgeid, prob,
                                      (unsigned)(rx0 + lx) | ((unsigned)(ry0 + ly) << 16));
               }
               if (sp.prob) {
@@ -827,7 +809,7 @@ __device__ __forceinline__ void log_pixel_coords(const uint4& rec, const Geometr
 template <>
 __device__ __forceinline__ void log_pixel_coords<float>(const uint4& rec, const Geometry&, const unsigned hw,
                                                         unsigned& b, unsigned& px, unsigned& py) {
-  b = rec.x / hw;
+  b = 0u;                                   // only needed for the overflow flags: taken there
   px = rec.w & 0xffffu; py = rec.w >> 16;
 }
 // `any_over`: some tile overflowed the log (normally none: the per-pair flag gather is skipped)
@@ -838,14 +820,21 @@ __device__ __forceinline__ void log_fetch_pixel(const SoftParams<T>& sp, const G
   log_pixel_coords<T>(it.rec, geo, hw, it.b, it.px, it.py);
   it.g = sp.grad_soft[pix];
   it.soft = sp.soft_in[pix];
-  it.flag = any_over ? sp.tile_flag[it.b * geo.tiles_per_view + (it.py / TILE) * geo.tiles_x + it.px / TILE] : 0u;
+  it.flag = 0u;
+  if (any_over) {                           // rare: some tile overflowed the log
+    if (sizeof(T) == 4) it.b = pix / hw;
+    it.flag = sp.tile_flag[it.b * geo.tiles_per_view + (it.py / TILE) * geo.tiles_x + it.px / TILE];
+  }
 }
 template <typename T>
 __device__ __forceinline__ void log_fetch_face(const SoftParams<T>& sp, const FaceLayout& fl, LogItem<T>& it) {
-  it.gf = fl.base((int)it.b) + (int)(it.rec.y >> 3);
+  it.gf = (int64_t)(it.rec.y >> 3);         // records carry the face's index in the whole batch (view * F + face)
   load_face_xy<T>(sp.img, it.gf, sp.coord_mult, sp.premultiplied, it.p);
 }
 
+#ifndef DIBR_LOG_INFLIGHT
+#define DIBR_LOG_INFLIGHT 2       // logged pairs whose gathers are in flight together, per thread
+#endif
 template <typename T>
 __global__ void __launch_bounds__(256) soft_mask_bwd_log_kernel(SoftParams<T> sp, FaceLayout fl, Geometry geo) {
   const unsigned seg = blockIdx.y;
@@ -857,25 +846,26 @@ __global__ void __launch_bounds__(256) soft_mask_bwd_log_kernel(SoftParams<T> sp
   const unsigned stride = gridDim.x * blockDim.x;
   // (summing lanes that hold the same face with shuffles before the atomics was measured slower: c2 0.121 vs
   // 0.108 ms, c3 0.175 vs 0.154 ms — the kernel waits on its gathers, not on the atomics)
-  for (unsigned i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += 2 * stride) {
-    const unsigned j = i + stride;
-    const bool two = j < n;
-    LogItem<T> a, c;
-    a.rec = log[i];
-    c.rec = log[two ? j : i];
-    log_fetch_pixel<T>(sp, geo, hw, any_over, a);
-    log_fetch_pixel<T>(sp, geo, hw, any_over, c);
-    log_fetch_face<T>(sp, fl, a);
-    log_fetch_face<T>(sp, fl, c);
-    if (a.g != (T)0 && !a.flag) {
-      const T x0 = (T)pix_coord(sx, geo.W, (int)a.px), y0 = (T)pix_coord(sy, geo.H, geo.H - 1 - (int)a.py);
-      soft_backward_pair<T>(a.p, x0, y0, log_prob<T>(a.rec), (int)(a.rec.y & 7u), a.g, a.soft, sp.sigmainv,
-                            sp.pix_mult, sp.grad_img + a.gf * 6);
+  for (unsigned i0 = blockIdx.x * blockDim.x + threadIdx.x; i0 < n; i0 += DIBR_LOG_INFLIGHT * stride) {
+    LogItem<T> it[DIBR_LOG_INFLIGHT];
+    bool on[DIBR_LOG_INFLIGHT];
+#pragma unroll
+    for (int q = 0; q < DIBR_LOG_INFLIGHT; ++q) {
+      const unsigned j = i0 + (unsigned)q * stride;
+      on[q] = j < n;
+      it[q].rec = log[on[q] ? j : i0];
     }
-    if (two && c.g != (T)0 && !c.flag) {
-      const T x0 = (T)pix_coord(sx, geo.W, (int)c.px), y0 = (T)pix_coord(sy, geo.H, geo.H - 1 - (int)c.py);
-      soft_backward_pair<T>(c.p, x0, y0, log_prob<T>(c.rec), (int)(c.rec.y & 7u), c.g, c.soft, sp.sigmainv,
-                            sp.pix_mult, sp.grad_img + c.gf * 6);
+#pragma unroll
+    for (int q = 0; q < DIBR_LOG_INFLIGHT; ++q) log_fetch_pixel<T>(sp, geo, hw, any_over, it[q]);
+#pragma unroll
+    for (int q = 0; q < DIBR_LOG_INFLIGHT; ++q) log_fetch_face<T>(sp, fl, it[q]);
+#pragma unroll
+    for (int q = 0; q < DIBR_LOG_INFLIGHT; ++q) {
+      if (on[q] && it[q].g != (T)0 && !it[q].flag) {
+        const T x0 = (T)pix_coord(sx, geo.W, (int)it[q].px), y0 = (T)pix_coord(sy, geo.H, geo.H - 1 - (int)it[q].py);
+        soft_backward_pair<T>(it[q].p, x0, y0, log_prob<T>(it[q].rec), (int)(it[q].rec.y & 7u), it[q].g, it[q].soft,
+                              sp.sigmainv, sp.pix_mult, sp.grad_img + it[q].gf * 6);
+      }
     }
   }
 }
