@@ -265,6 +265,59 @@ int dibr_rasterization_bwd_fused_f64(const double* const* grad_outs, const doubl
                                      void* stream);
 
 /* ---------------------------------------------------------------------------------------------
+ * dibr_rasterization straight from the mesh — prepare_vertices folded into K0:
+ *     kaolin/render/mesh/utils.py:128-175 (prepare_vertices: rotate_translate_points / padded @ camera_transform,
+ *     perspective_camera, index_vertices_by_faces, face_normals) followed by kaolin/render/mesh/dibr.py:119-209
+ *     (dibr_rasterization with face_normals_z = face_normals[:, :, 2]).
+ *  The setup kernel gathers each face's vertices through `faces` (F,3) int64 from `vertices` (Bv,V,3) (Bv = 1: one
+ *  mesh seen by B cameras; Bv = B: one mesh per camera), applies the camera (rot (B,3,3) + trans (B,3), or transform
+ *  (B,4,3); exactly one form) and camera_proj (3), culls with the unit normal's z and bins — the camera-space
+ *  (B,F,3,3) tensor and the (B,F,3) normals are never materialised.  It WRITES face_vertices_image (B,F,3,2) and
+ *  face_vertices_z (B,F,3) (caller's buffers): the per-tile kernels and the backward read them, and they are
+ *  bit-identical to dibr_prepare_vertices_fwd's outputs, so every result equals the unfused chain's.
+ *  ws / keep_pairs / feats / out_feats: as dibr_rasterization_fwd_fused.
+ *  _bwd: the image-plane gradients of both outputs are accumulated in grad_image_scratch (B,F,3,2; caller's scratch,
+ *  contents unspecified afterwards) and folded by prepare_vertices' backward into grad_vertices (Bv,V,3) and, when
+ *  non-NULL, grad_proj (3) / grad_rot (B,3,3) / grad_trans (B,3) / grad_transform (B,4,3) — all zero-filled by the
+ *  library; at least one of them must be given.  face_vertices_z gets no gradient (rasterization_cuda.cu:238-402
+ *  has none either).  bins_ready as dibr_rasterization_bwd_fused.
+ */
+int dibr_rasterization_from_mesh_fwd_f32(const float* vertices, const int64_t* faces, const float* camera_proj,
+                                         const float* rot, const float* trans, const float* transform, int Bv, int V,
+                                         const float* const* feats, const int* channels, int n_feat, int B, int F,
+                                         int H, int W, double multiplier, float eps, float sigmainv, double boxlen,
+                                         int knum, float* face_vertices_image, float* face_vertices_z,
+                                         float* const* out_feats, int64_t* out_face_idx, float* soft, void* ws,
+                                         size_t ws_bytes, int keep_pairs, void* stream);
+int dibr_rasterization_from_mesh_fwd_f64(const double* vertices, const int64_t* faces, const double* camera_proj,
+                                         const double* rot, const double* trans, const double* transform, int Bv,
+                                         int V, const double* const* feats, const int* channels, int n_feat, int B,
+                                         int F, int H, int W, double multiplier, float eps, float sigmainv,
+                                         double boxlen, int knum, double* face_vertices_image,
+                                         double* face_vertices_z, double* const* out_feats, int64_t* out_face_idx,
+                                         double* soft, void* ws, size_t ws_bytes, int keep_pairs, void* stream);
+int dibr_rasterization_from_mesh_bwd_f32(const float* const* grad_outs, const float* grad_soft, const float* soft,
+                                         const int64_t* face_idx, const float* face_vertices_image,
+                                         const float* const* feats, const int* channels, int n_feat,
+                                         const float* vertices, const int64_t* faces, const float* camera_proj,
+                                         const float* rot, const float* trans, const float* transform, int Bv, int V,
+                                         int B, int F, int H, int W, double multiplier, float eps, float sigmainv,
+                                         double boxlen, int knum, float* grad_image_scratch,
+                                         float* const* grad_feats, float* grad_vertices, float* grad_proj,
+                                         float* grad_rot, float* grad_trans, float* grad_transform, void* ws,
+                                         size_t ws_bytes, int bins_ready, void* stream);
+int dibr_rasterization_from_mesh_bwd_f64(const double* const* grad_outs, const double* grad_soft, const double* soft,
+                                         const int64_t* face_idx, const double* face_vertices_image,
+                                         const double* const* feats, const int* channels, int n_feat,
+                                         const double* vertices, const int64_t* faces, const double* camera_proj,
+                                         const double* rot, const double* trans, const double* transform, int Bv,
+                                         int V, int B, int F, int H, int W, double multiplier, float eps,
+                                         float sigmainv, double boxlen, int knum, double* grad_image_scratch,
+                                         double* const* grad_feats, double* grad_vertices, double* grad_proj,
+                                         double* grad_rot, double* grad_trans, double* grad_transform, void* ws,
+                                         size_t ws_bytes, int bins_ready, void* stream);
+
+/* ---------------------------------------------------------------------------------------------
  * prepare_vertices — the producer of the path's inputs (first "next" row).
  *  Replaces the torch composition of kaolin/render/mesh/utils.py:128-175:
  *    camera transform      rotate_translate_points (kaolin/render/camera/legacy.py:22-37) when rot/trans are
@@ -325,6 +378,22 @@ int dibr_texture_mapping_bwd_f32(const float* grad_out, const float* uv, const f
 int dibr_texture_mapping_bwd_f64(const double* grad_out, const double* uv, const double* texture_maps,
                                  const double* mask, int B, int64_t N, int Bt, int C, int Ht, int Wt, int mode,
                                  double* grad_uv, double* grad_texture_maps, double* grad_mask, void* stream);
+
+/* ---------------------------------------------------------------------------------------------
+ * Image L1 loss of the fitting loop — examples/tutorial/ian_dibr.py:260  image_loss = torch.mean(torch.abs(image -
+ * gt_image)): loss (device scalar) = mean over the n elements of |a - b|, as a deterministic two-stage reduction (no
+ * float atomics); ws: dibr_image_l1_workspace_bytes(n, elem_size) bytes.  _bwd: grad_loss is a DEVICE scalar;
+ * grad_a = sign(a - b) * grad_loss / n, grad_b = -grad_a (either may be NULL).
+ */
+size_t dibr_image_l1_workspace_bytes(int64_t n, int elem_size);
+int dibr_image_l1_fwd_f32(const float* a, const float* b, int64_t n, float* loss, void* ws, size_t ws_bytes,
+                          void* stream);
+int dibr_image_l1_fwd_f64(const double* a, const double* b, int64_t n, double* loss, void* ws, size_t ws_bytes,
+                          void* stream);
+int dibr_image_l1_bwd_f32(const float* grad_loss, const float* a, const float* b, int64_t n, float* grad_a,
+                          float* grad_b, void* stream);
+int dibr_image_l1_bwd_f64(const double* grad_loss, const double* a, const double* b, int64_t n, double* grad_a,
+                          double* grad_b, void* stream);
 
 /* ---------------------------------------------------------------------------------------------
  * mask_iou — the consumer of soft_mask.
@@ -431,7 +500,9 @@ enum {
   DIBR_KERNEL_IOU_BWD = 12,
   DIBR_KERNEL_DEFTET_FWD = 13,
   DIBR_KERNEL_DEFTET_BWD = 14,
-  DIBR_KERNEL_COUNT = 15
+  DIBR_KERNEL_L1_FWD = 15,
+  DIBR_KERNEL_L1_BWD = 16,
+  DIBR_KERNEL_COUNT = 17
 };
 int dibr_profile_next_launch(int kernel_id, void* start_event, void* stop_event);
 

@@ -45,11 +45,18 @@ _TYPED = {
                                      c_p, c_p, c_p, c_sz, c_i, c_p],
     "dibr_rasterization_bwd_fused": [c_p, c_p, c_p, c_p, c_p, c_p, c_p, c_i, c_i, c_i, c_i, c_i, c_d, c_f, c_f, c_d,
                                      c_i, c_p, c_p, c_p, c_sz, c_i, c_p],
+    "dibr_rasterization_from_mesh_fwd": [c_p, c_p, c_p, c_p, c_p, c_p, c_i, c_i, c_p, c_p, c_i, c_i, c_i, c_i, c_i, c_d,
+                                         c_f, c_f, c_d, c_i, c_p, c_p, c_p, c_p, c_p, c_p, c_sz, c_i, c_p],
+    "dibr_rasterization_from_mesh_bwd": [c_p, c_p, c_p, c_p, c_p, c_p, c_p, c_i, c_p, c_p, c_p, c_p, c_p, c_p, c_i, c_i,
+                                         c_i, c_i, c_i, c_i, c_d, c_f, c_f, c_d, c_i, c_p, c_p, c_p, c_p, c_p, c_p, c_p,
+                                         c_p, c_sz, c_i, c_p],
     "dibr_prepare_vertices_fwd": [c_p, c_p, c_p, c_p, c_p, c_p, c_i, c_i, c_i, c_i, c_p, c_p, c_p, c_p],
     "dibr_prepare_vertices_bwd": [c_p, c_p, c_p, c_p, c_p, c_p, c_p, c_p, c_p, c_i, c_i, c_i, c_i, c_p, c_p, c_p, c_p,
                                   c_p, c_p],
     "dibr_texture_mapping_fwd": [c_p, c_p, c_p, c_i, c_i64, c_i, c_i, c_i, c_i, c_i, c_p, c_p],
     "dibr_texture_mapping_bwd": [c_p, c_p, c_p, c_p, c_i, c_i64, c_i, c_i, c_i, c_i, c_i, c_p, c_p, c_p, c_p],
+    "dibr_image_l1_fwd": [c_p, c_p, c_i64, c_p, c_p, c_sz, c_p],
+    "dibr_image_l1_bwd": [c_p, c_p, c_p, c_i64, c_p, c_p, c_p],
     "dibr_mask_iou_fwd": [c_p, c_p, c_i, c_i64, c_p, c_p, c_p, c_sz, c_p],
     "dibr_mask_iou_fwd_noalloc": [c_p, c_p, c_i, c_i64, c_p, c_p, c_p],
     "dibr_mask_iou_bwd": [c_p, c_p, c_p, c_p, c_i, c_i64, c_p, c_p, c_p],
@@ -60,7 +67,7 @@ _TYPED = {
 }
 EXPORTED_SYMBOLS = (["dibr_abi_version", "dibr_error_string", "dibr_last_cuda_error", "dibr_workspace_bytes",
                      "dibr_kernel_launch_count", "dibr_reset_kernel_launch_count", "dibr_profile_next_launch",
-                     "dibr_mask_iou_workspace_bytes", "dibr_noalloc_scratch_bytes", "dibr_deftet_workspace_bytes",
+                     "dibr_mask_iou_workspace_bytes", "dibr_image_l1_workspace_bytes", "dibr_noalloc_scratch_bytes", "dibr_deftet_workspace_bytes",
                      "dibr_soft_mask_workspace_bytes", "dibr_rasterization_workspace_bytes"] +
                     [f"{n}_{s}" for n in _TYPED for s in ("f32", "f64")])
 
@@ -110,6 +117,8 @@ def load():
         lib.dibr_reset_kernel_launch_count.restype = None
         lib.dibr_mask_iou_workspace_bytes.restype = c_sz
         lib.dibr_mask_iou_workspace_bytes.argtypes = [c_i, c_i64, c_i]
+        lib.dibr_image_l1_workspace_bytes.restype = c_sz
+        lib.dibr_image_l1_workspace_bytes.argtypes = [c_i64, c_i]
         lib.dibr_soft_mask_workspace_bytes.restype = c_sz
         lib.dibr_soft_mask_workspace_bytes.argtypes = [c_i, c_i64, c_i, c_i, c_i, c_i]
         lib.dibr_noalloc_scratch_bytes.restype = c_sz

@@ -24,6 +24,7 @@
 // face order (depth ties, soft-mask "first knum faces") use order-independent rules or sort in smem.
 #pragma once
 #include "dibr_common.cuh"
+#include "dibr_prepare.cuh"      // project_face: the mesh form of setup_count projects the faces itself
 
 namespace dibr {
 
@@ -257,21 +258,48 @@ __device__ __forceinline__ bool face_pixel_range(const T xmin, const T ymin, con
 // DUAL = false: one set of lists (L.l[0]) with sp.margin / sp.valid as given.  DUAL = true: L.l[0] = rasterizer lists
 // (margin 0, only faces with valid != 0 / normals_z >= 0), L.l[1] = soft-mask lists (margin soft_margin, ALL
 // faces: dibr.py:75-117 takes no valid mask), both from one read of the coordinates.
-template <typename T, bool DUAL>
+// MESH (with DUAL; dibr_rasterization_from_mesh): the thread projects its face itself from (vertices, faces, camera)
+// with prepare_vertices' arithmetic (project_face) — prepare_vertices (utils.py:128-175) folded into K0 — writes
+// face_vertices_image (B,F,3,2) and face_vertices_z (B,F,3) for the per-tile kernels and the backward, and culls with
+// the unit normal's z (dibr.py:195); neither the camera-space (B,F,3,3) tensor nor the normals are materialised.
+template <typename T>
+struct MeshOut {
+  T* img;      // (B,F,3,2)
+  T* z;        // (B,F,3)
+};
+template <typename T, bool DUAL, bool MESH>
 __global__ void __launch_bounds__(256) setup_count_kernel(SetupParams<T> sp, const T soft_margin, FaceLayout fl,
-                                                          Geometry geo, BinLists2 L) {
+                                                          Geometry geo, BinLists2 L, PrepareParams<T> mp,
+                                                          MeshOut<T> mo) {
   const int64_t g = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
   const bool in_range = g < fl.Ntot;                    // no early exit: the binning below is warp-collective
   bool is_valid = in_range;
-  if (in_range && sp.valid) is_valid = sp.valid[g] != 0;
-  if (in_range && sp.normals_z) is_valid = sp.normals_z[g] >= (T)0;     // dibr.py:195 `face_normals_z >= 0.`
+  if (!MESH) {
+    if (in_range && sp.valid) is_valid = sp.valid[g] != 0;
+    if (in_range && sp.normals_z) is_valid = sp.normals_z[g] >= (T)0;   // dibr.py:195 `face_normals_z >= 0.`
+  }
   uint2 rec = empty_range(), rec2 = empty_range();
   int b = 0, tx0 = 0, tx1 = -1, ty0 = 0, ty1 = -1;
   int sx0 = 0, sx1 = -1, sy0 = 0, sy1 = -1;
   bool has = false, has2 = false;
-  if (DUAL ? in_range : is_valid) {
+  if (MESH || DUAL ? in_range : is_valid) {
     T xmin, ymin, xmax, ymax;
-    if (sp.bbox_in) {
+    if (MESH) {
+      b = fl.view_of(g);
+      const ViewCamera<T> cam = load_camera<T>(mp, b);
+      T q[3][3], im[6], nrm[3], p[6];
+      project_face<T>(mp, cam, b, (int)(g - fl.base(b)), q, im, nrm);
+      is_valid = nrm[2] >= (T)0;
+      T* oi = mo.img + g * 6;
+      T* oz = mo.z + g * 3;
+#pragma unroll
+      for (int k = 0; k < 6; ++k) { oi[k] = im[k]; p[k] = RN<T>::mul(im[k], sp.coord_mult); }
+      oz[0] = q[0][2]; oz[1] = q[1][2]; oz[2] = q[2][2];
+      xmin = min_nan(min_nan(p[0], p[2]), p[4]);
+      xmax = max_nan(max_nan(p[0], p[2]), p[4]);
+      ymin = min_nan(min_nan(p[1], p[3]), p[5]);
+      ymax = max_nan(max_nan(p[1], p[3]), p[5]);
+    } else if (sp.bbox_in) {
       const T* bb = sp.bbox_in + g * 4;
       xmin = bb[0]; ymin = bb[1]; xmax = bb[2]; ymax = bb[3];
     } else {
@@ -295,7 +323,7 @@ __global__ void __launch_bounds__(256) setup_count_kernel(SetupParams<T> sp, con
       }
       has = face_pixel_range<T>(xmin, ymin, xmax, ymax, sp.pix_mult, geo, rec, tx0, tx1, ty0, ty1);
     }
-    if (has || has2) b = fl.view_of(g);
+    if (!MESH && (has || has2)) b = fl.view_of(g);
   }
   const int local = (has || has2) ? (int)(g - fl.base(b)) : 0;
   bin_faces_warp<false>(has, b, local, tx0, tx1, ty0, ty1, g, fl, geo, L.l[0]);

@@ -50,7 +50,8 @@ std::atomic<cudaEvent_t> g_prof_start{nullptr}, g_prof_stop{nullptr};
 const char* const kKernelNames[DIBR_KERNEL_COUNT] = {
     "dibr/setup_count", "dibr/scan", "dibr/fill", "dibr/raster_fwd", "dibr/raster_bwd", "dibr/soft_mask_fwd",
     "dibr/soft_mask_bwd", "dibr/prepare_vertices_fwd", "dibr/prepare_vertices_bwd", "dibr/texture_mapping_fwd",
-    "dibr/texture_mapping_bwd", "dibr/mask_iou_fwd", "dibr/mask_iou_bwd", "dibr/deftet_fwd", "dibr/deftet_bwd"};
+    "dibr/texture_mapping_bwd", "dibr/mask_iou_fwd", "dibr/mask_iou_bwd", "dibr/deftet_fwd", "dibr/deftet_bwd",
+    "dibr/image_l1_fwd", "dibr/image_l1_bwd"};
 // Every kernel launch site sits in one of these scopes: an NVTX range named after the kernel (so that an nsys / ncu
 // timeline of a training step reads "dibr/raster_fwd ..." instead of mangled template names) + the timing hook.
 struct ProfScope {
@@ -153,7 +154,7 @@ int run_binning(const SetupParams<T>& sp, const FaceLayout& fl, const Geometry& 
   BinLists2 LL; LL.l[0] = L; LL.l[1] = L;
   const unsigned nb = binning_blocks(fl, geo, false);
   if (nb > 0) {
-    { ProfScope ps(DIBR_KERNEL_SETUP_COUNT, s); setup_count_kernel<T, false><<<nb, 256, 0, s>>>(sp, (T)0, fl, geo, LL); }
+    { ProfScope ps(DIBR_KERNEL_SETUP_COUNT, s); setup_count_kernel<T, false, false><<<nb, 256, 0, s>>>(sp, (T)0, fl, geo, LL, PrepareParams<T>(), MeshOut<T>()); }
     LAUNCH_CHECK("setup_count_kernel");
   }
   { ProfScope ps(DIBR_KERNEL_SCAN, s); scan_kernel<<<scan_grid(geo, 1), SCAN_CHUNK, 0, s>>>(geo, LL); }
@@ -428,7 +429,7 @@ int soft_mask_impl(const T* img, const T* bbox_in, const int64_t* face_idx, int 
     BinLists2 LL; LL.l[0] = L; LL.l[1] = L;
     const unsigned nb = binning_blocks(fl, geo, false);
     if (nb > 0) {
-      { ProfScope ps(DIBR_KERNEL_SETUP_COUNT, s); setup_count_kernel<T, false><<<nb, 256, 0, s>>>(sp, (T)0, fl, geo, LL); }
+      { ProfScope ps(DIBR_KERNEL_SETUP_COUNT, s); setup_count_kernel<T, false, false><<<nb, 256, 0, s>>>(sp, (T)0, fl, geo, LL, PrepareParams<T>(), MeshOut<T>()); }
       LAUNCH_CHECK("setup_count_kernel");
     }
     { ProfScope ps(DIBR_KERNEL_SCAN, s); scan_kernel<<<scan_grid(geo, 1), SCAN_CHUNK, 0, s>>>(geo, LL); }
@@ -451,7 +452,7 @@ int dibr_rasterization_fwd_impl(const T* z, const T* img, const T* const* feats,
                                 const T* normals_z, const uint8_t* valid, int B, int F, int H, int W,
                                 double multiplier, float eps, float sigmainv, double boxlen, int knum,
                                 T* const* out_feats, int64_t* out_idx, T* soft, void* ws, size_t ws_bytes,
-                                int keep_pairs, void* stream) {
+                                int keep_pairs, void* stream, const PrepareParams<T>* mesh = nullptr) {
   if (F < 0 || knum < 0) return DIBR_ERR_INVALID_ARGUMENT;
   const int64_t Ntot = (int64_t)B * F;
   if (int e = check_dims(B, Ntot, H, W)) return e;
@@ -475,7 +476,14 @@ int dibr_rasterization_fwd_impl(const T* z, const T* img, const T* const* feats,
   const unsigned nb = binning_blocks(fl, geo, false);
   if (nb > 0) {
     { ProfScope ps(DIBR_KERNEL_SETUP_COUNT, s);
-      setup_count_kernel<T, true><<<nb, 256, 0, s>>>(sp, (T)(boxlen * multiplier), fl, geo, LL); }
+      if (mesh) {         // prepare_vertices folded into K0: `img` / `z` are OUTPUTS of this kernel (const cast: the
+        MeshOut<T> mo;    // caller's buffers, handed over as outputs by dibr_rasterization_from_mesh_fwd)
+        mo.img = const_cast<T*>(img); mo.z = const_cast<T*>(z);
+        setup_count_kernel<T, true, true><<<nb, 256, 0, s>>>(sp, (T)(boxlen * multiplier), fl, geo, LL, *mesh, mo);
+      } else {
+        setup_count_kernel<T, true, false><<<nb, 256, 0, s>>>(sp, (T)(boxlen * multiplier), fl, geo, LL,
+                                                              PrepareParams<T>(), MeshOut<T>());
+      } }
     LAUNCH_CHECK("setup_count_kernel");
   }
   { ProfScope ps(DIBR_KERNEL_SCAN, s); scan_kernel<<<scan_grid(geo, 2), SCAN_CHUNK, 0, s>>>(geo, LL); }
@@ -612,6 +620,57 @@ int prepare_impl(bool backward, const T* g_cam, const T* g_img, const T* g_nrm, 
   return DIBR_OK;
 }
 
+// Validation shared by the mesh entry points (same rules as prepare_impl).
+template <typename T>
+int mesh_params(const T* vertices, const int64_t* faces, const T* proj, const T* rot, const T* trans,
+                const T* transform, int B, int Bv, int V, int F, PrepareParams<T>& pp) {
+  if (B < 0 || V < 0 || F < 0 || (Bv != 1 && Bv != B)) return DIBR_ERR_INVALID_ARGUMENT;
+  if ((int64_t)Bv * V >= (int64_t)1 << 40) return DIBR_ERR_TOO_LARGE;
+  const bool by_matrix = transform != nullptr;
+  if (by_matrix == (rot != nullptr || trans != nullptr)) return DIBR_ERR_INVALID_ARGUMENT;   // exactly one camera form
+  if (!by_matrix && (!rot || !trans)) return DIBR_ERR_INVALID_ARGUMENT;
+  if ((int64_t)B * F > 0 && (!vertices || !faces || !proj)) return DIBR_ERR_INVALID_ARGUMENT;
+  pp = PrepareParams<T>();
+  pp.vertices = vertices; pp.faces = faces; pp.proj = proj; pp.rot = rot; pp.trans = trans;
+  pp.transform = transform; pp.B = B; pp.Bv = Bv; pp.V = V; pp.F = F;
+  return DIBR_OK;
+}
+
+// dibr_rasterization straight from the mesh: prepare_vertices (utils.py:128-175) + dibr_rasterization (dibr.py:119-209)
+// as 5 launches — K0 projects the faces itself (setup_count_kernel<T, true, true>) and writes face_vertices_image /
+// face_vertices_z for the per-tile kernels and the backward.
+template <typename T>
+int from_mesh_fwd_impl(const T* vertices, const int64_t* faces, const T* proj, const T* rot, const T* trans,
+                       const T* transform, int Bv, int V, const T* const* feats, const int* channels, int n_feat,
+                       int B, int F, int H, int W, double multiplier, float eps, float sigmainv, double boxlen,
+                       int knum, T* face_img, T* face_z, T* const* out_feats, int64_t* out_idx, T* soft, void* ws,
+                       size_t ws_bytes, int keep_pairs, void* stream) {
+  PrepareParams<T> pp;
+  if (int e = mesh_params<T>(vertices, faces, proj, rot, trans, transform, B, Bv, V, F, pp)) return e;
+  if ((int64_t)B * F > 0 && (!face_img || !face_z)) return DIBR_ERR_INVALID_ARGUMENT;
+  return dibr_rasterization_fwd_impl<T>(face_z, face_img, feats, channels, n_feat, nullptr, nullptr, B, F, H, W,
+                                        multiplier, eps, sigmainv, boxlen, knum, out_feats, out_idx, soft, ws, ws_bytes,
+                                        keep_pairs, stream, &pp);
+}
+
+// Backward of the mesh entry: image-plane gradients of both outputs into the caller's scratch (B,F,3,2), then
+// prepare_vertices' backward folds them into grad_vertices (+ optional camera gradients) — one call, the (B,F,3,2)
+// gradient never leaves the library's hands.
+template <typename T>
+int from_mesh_bwd_impl(const T* const* grad_outs, const T* grad_soft, const T* soft, const int64_t* face_idx,
+                       const T* face_img, const T* const* feats, const int* channels, int n_feat, const T* vertices,
+                       const int64_t* faces, const T* proj, const T* rot, const T* trans, const T* transform, int Bv,
+                       int V, int B, int F, int H, int W, double multiplier, float eps, float sigmainv, double boxlen,
+                       int knum, T* grad_img_scratch, T* const* grad_feats, T* g_vertices, T* g_proj, T* g_rot,
+                       T* g_trans, T* g_transform, void* ws, size_t ws_bytes, int bins_ready, void* stream) {
+  if (int e = dibr_rasterization_bwd_impl<T>(grad_outs, grad_soft, soft, face_idx, face_img, feats, channels, n_feat, B,
+                                             F, H, W, multiplier, eps, sigmainv, boxlen, knum, grad_img_scratch,
+                                             grad_feats, ws, ws_bytes, bins_ready, stream))
+    return e;
+  return prepare_impl<T>(true, nullptr, grad_img_scratch, nullptr, vertices, faces, proj, rot, trans, transform, B, Bv,
+                         V, F, nullptr, nullptr, nullptr, g_vertices, g_proj, g_rot, g_trans, g_transform, stream);
+}
+
 // texture_mapping (utils.py:23-76) [+ clamp(image * mask, 0, 1)]: one kernel each way.
 template <typename T>
 int texture_impl(bool backward, const T* g_out, const T* uv, const T* tex, const T* mask, int B, int64_t N, int Bt,
@@ -679,6 +738,38 @@ int iou_bwd_impl(const T* g_loss, const T* lhs, const T* rhs, const T* sums, int
     mask_iou_bwd_kernel<T><<<dim3((unsigned)iou_chunks(P), (unsigned)B), 256, 0, s>>>(lhs, rhs, sums, g_loss, P,
                                                                                        B, g_lhs, g_rhs); }
   LAUNCH_CHECK("mask_iou_bwd_kernel");
+  return DIBR_OK;
+}
+
+// image L1 loss (examples/tutorial/ian_dibr.py:260): mean |a - b| over n elements
+inline int l1_chunks(int64_t n) { return (int)((n + L1_CHUNK - 1) / L1_CHUNK); }
+template <typename T>
+int l1_fwd_impl(const T* a, const T* b, int64_t n, T* loss, void* ws, size_t ws_bytes, void* stream) {
+  if (n < 0 || !loss) return DIBR_ERR_INVALID_ARGUMENT;
+  if (n >= (int64_t)1 << 44) return DIBR_ERR_TOO_LARGE;
+  cudaStream_t s = static_cast<cudaStream_t>(stream);
+  const int chunks = l1_chunks(n);
+  if (n > 0) {
+    if (!a || !b) return DIBR_ERR_INVALID_ARGUMENT;
+    if (!ws || ws_bytes < align_up((size_t)chunks * sizeof(T))) return DIBR_ERR_WORKSPACE;
+    { ProfScope ps(DIBR_KERNEL_L1_FWD, s);
+      image_l1_partial_kernel<T><<<(unsigned)chunks, 256, 0, s>>>(a, b, n, static_cast<T*>(ws)); }
+    LAUNCH_CHECK("image_l1_partial_kernel");
+  }
+  image_l1_finish_kernel<T><<<1, 256, 0, s>>>(static_cast<const T*>(ws), chunks, n, loss);
+  LAUNCH_CHECK("image_l1_finish_kernel");
+  return DIBR_OK;
+}
+template <typename T>
+int l1_bwd_impl(const T* g_loss, const T* a, const T* b, int64_t n, T* g_a, T* g_b, void* stream) {
+  if (n < 0) return DIBR_ERR_INVALID_ARGUMENT;
+  if (n >= (int64_t)1 << 44) return DIBR_ERR_TOO_LARGE;
+  if (n == 0 || (!g_a && !g_b)) return DIBR_OK;
+  if (!g_loss || !a || !b) return DIBR_ERR_INVALID_ARGUMENT;
+  cudaStream_t s = static_cast<cudaStream_t>(stream);
+  { ProfScope ps(DIBR_KERNEL_L1_BWD, s);
+    image_l1_bwd_kernel<T><<<(unsigned)l1_chunks(n), 256, 0, s>>>(a, b, g_loss, n, g_a, g_b); }
+  LAUNCH_CHECK("image_l1_bwd_kernel");
   return DIBR_OK;
 }
 
@@ -896,6 +987,10 @@ DIBR_API size_t dibr_deftet_workspace_bytes(int batch_size, int64_t total_faces)
   return ws_layout(batch_size, total_faces, make_geometry(batch_size, G * TILE, G * TILE)).total;
 }
 
+DIBR_API size_t dibr_image_l1_workspace_bytes(int64_t n, int elem_size) {
+  if (n <= 0 || elem_size <= 0) return 256;
+  return align_up((size_t)l1_chunks(n) * (size_t)elem_size);
+}
 DIBR_API size_t dibr_mask_iou_workspace_bytes(int B, int64_t P, int elem_size) {
   return iou_ws_bytes(B, P, elem_size);
 }
@@ -1000,6 +1095,31 @@ DIBR_API size_t dibr_noalloc_scratch_bytes(void) { return NOALLOC_SCRATCH_BYTES;
                                           B, F, H, W, multiplier, eps, sigmainv, boxlen, knum, grad_img,       \
                                           grad_feats, ws, ws_bytes, bins_ready, stream);                        \
   }                                                                                                            \
+  DIBR_API int dibr_rasterization_from_mesh_fwd_##SUF(                                                        \
+      const T* vertices, const int64_t* faces, const T* camera_proj, const T* rot, const T* trans,            \
+      const T* transform, int Bv, int V, const T* const* feats, const int* channels, int n_feat, int B, int F, \
+      int H, int W, double multiplier, float eps, float sigmainv, double boxlen, int knum,                     \
+      T* face_vertices_image, T* face_vertices_z, T* const* out_feats, int64_t* out_face_idx, T* soft,         \
+      void* ws, size_t ws_bytes, int keep_pairs, void* stream) {                                               \
+    return from_mesh_fwd_impl<T>(vertices, faces, camera_proj, rot, trans, transform, Bv, V, feats, channels,  \
+                                 n_feat, B, F, H, W, multiplier, eps, sigmainv, boxlen, knum,                  \
+                                 face_vertices_image, face_vertices_z, out_feats, out_face_idx, soft, ws,      \
+                                 ws_bytes, keep_pairs, stream);                                                \
+  }                                                                                                            \
+  DIBR_API int dibr_rasterization_from_mesh_bwd_##SUF(                                                        \
+      const T* const* grad_outs, const T* grad_soft, const T* soft, const int64_t* face_idx,                   \
+      const T* face_vertices_image, const T* const* feats, const int* channels, int n_feat,                    \
+      const T* vertices, const int64_t* faces, const T* camera_proj, const T* rot, const T* trans,             \
+      const T* transform, int Bv, int V, int B, int F, int H, int W, double multiplier, float eps,             \
+      float sigmainv, double boxlen, int knum, T* grad_image_scratch, T* const* grad_feats,                    \
+      T* grad_vertices, T* grad_proj, T* grad_rot, T* grad_trans, T* grad_transform, void* ws,                 \
+      size_t ws_bytes, int bins_ready, void* stream) {                                                         \
+    return from_mesh_bwd_impl<T>(grad_outs, grad_soft, soft, face_idx, face_vertices_image, feats, channels,   \
+                                 n_feat, vertices, faces, camera_proj, rot, trans, transform, Bv, V, B, F, H,  \
+                                 W, multiplier, eps, sigmainv, boxlen, knum, grad_image_scratch, grad_feats,   \
+                                 grad_vertices, grad_proj, grad_rot, grad_trans, grad_transform, ws, ws_bytes, \
+                                 bins_ready, stream);                                                          \
+  }                                                                                                            \
   DIBR_API int dibr_prepare_vertices_fwd_##SUF(const T* vertices, const int64_t* faces, const T* camera_proj, \
                                                const T* rot, const T* trans, const T* transform, int B,      \
                                                int Bv, int V, int F, T* face_vertices_camera,                \
@@ -1030,6 +1150,14 @@ DIBR_API size_t dibr_noalloc_scratch_bytes(void) { return NOALLOC_SCRATCH_BYTES;
                                               T* grad_mask, void* stream) {                                  \
     return texture_impl<T>(true, grad_out, uv, texture_maps, mask, B, N, Bt, C, Ht, Wt, mode, nullptr,       \
                            grad_uv, grad_texture_maps, grad_mask, stream);                                    \
+  }                                                                                                           \
+  DIBR_API int dibr_image_l1_fwd_##SUF(const T* a, const T* b, int64_t n, T* loss, void* ws, size_t ws_bytes, \
+                                       void* stream) {                                                       \
+    return l1_fwd_impl<T>(a, b, n, loss, ws, ws_bytes, stream);                                               \
+  }                                                                                                           \
+  DIBR_API int dibr_image_l1_bwd_##SUF(const T* grad_loss, const T* a, const T* b, int64_t n, T* grad_a,      \
+                                       T* grad_b, void* stream) {                                            \
+    return l1_bwd_impl<T>(grad_loss, a, b, n, grad_a, grad_b, stream);                                        \
   }                                                                                                           \
   DIBR_API int dibr_mask_iou_fwd_##SUF(const T* lhs, const T* rhs, int B, int64_t P, T* loss, T* sums,       \
                                        void* ws, size_t ws_bytes, void* stream) {                            \

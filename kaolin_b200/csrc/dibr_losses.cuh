@@ -87,4 +87,48 @@ __global__ void __launch_bounds__(256) mask_iou_bwd_kernel(const T* __restrict__
   }
 }
 
+// ---------------------------------------------------------------- image L1 loss
+// torch.mean(torch.abs(image - gt_image)) of the fitting loop (examples/tutorial/ian_dibr.py:260): the reference runs
+// sub, abs and a mean reduction forward and sign / mul / div kernels backward, re-reading the images each time; here
+// one deterministic two-stage reduction (fixed chunk order, no float atomics) and one elementwise backward
+//   d loss / d a_i = sign(a_i - b_i) * grad_loss / n        (sign(0) = 0, as torch.abs' backward)
+constexpr int L1_CHUNK = 16384;        // elements per CTA (256 threads x 64)
+
+template <typename T>
+__global__ void __launch_bounds__(256) image_l1_partial_kernel(const T* __restrict__ a, const T* __restrict__ b,
+                                                               const int64_t n, T* partial) {
+  __shared__ T sh[8];
+  const int64_t lo = (int64_t)blockIdx.x * L1_CHUNK;
+  const int64_t hi = lo + L1_CHUNK < n ? lo + L1_CHUNK : n;
+  T acc = (T)0;
+  for (int64_t i = lo + threadIdx.x; i < hi; i += 256) {
+    const T d = a[i] - b[i];
+    acc += d < (T)0 ? -d : d;
+  }
+  acc = block_sum_256<T>(acc, sh);
+  if (threadIdx.x == 0) partial[blockIdx.x] = acc;
+}
+template <typename T>
+__global__ void __launch_bounds__(256) image_l1_finish_kernel(const T* partial, const int chunks, const int64_t n,
+                                                              T* loss) {
+  __shared__ T sh[8];
+  T acc = (T)0;
+  for (int c = threadIdx.x; c < chunks; c += 256) acc += partial[c];
+  acc = block_sum_256<T>(acc, sh);
+  if (threadIdx.x == 0) loss[0] = acc / (T)n;          // n == 0: 0 / 0 = NaN, torch.mean of an empty tensor
+}
+template <typename T>
+__global__ void __launch_bounds__(256) image_l1_bwd_kernel(const T* __restrict__ a, const T* __restrict__ b,
+                                                           const T* grad_loss, const int64_t n, T* g_a, T* g_b) {
+  const T k = grad_loss[0] / (T)n;
+  const int64_t lo = (int64_t)blockIdx.x * L1_CHUNK;
+  const int64_t hi = lo + L1_CHUNK < n ? lo + L1_CHUNK : n;
+  for (int64_t i = lo + threadIdx.x; i < hi; i += 256) {
+    const T d = a[i] - b[i];
+    const T g = d > (T)0 ? k : (d < (T)0 ? -k : (d == d ? (T)0 : d));   // NaN propagates
+    if (g_a) g_a[i] = g;
+    if (g_b) g_b[i] = -g;
+  }
+}
+
 }  // namespace dibr

@@ -75,16 +75,50 @@ __device__ __forceinline__ ViewCamera<T> load_camera(const PrepareParams<T>& pp,
   return c;
 }
 
+// Every operation of the forward is an explicit round-to-nearest intrinsic (never contracted or re-associated), so
+// that the two kernels that project faces — prepare_vertices_fwd_kernel and the mesh form of setup_count_kernel
+// (dibr_binning.cuh, dibr_rasterization_from_mesh) — produce the same bits: face_idx of the fused entry equals the
+// unfused chain's.
 template <typename T>
 __device__ __forceinline__ void to_camera(const ViewCamera<T>& c, const T* p, T* q) {
-  const T x = p[0] - c.t[0], y = p[1] - c.t[1], z = p[2] - c.t[2];
+  typedef RN<T> R;
+  const T x = R::sub(p[0], c.t[0]), y = R::sub(p[1], c.t[1]), z = R::sub(p[2], c.t[2]);
 #pragma unroll
-  for (int j = 0; j < 3; ++j) q[j] = x * c.m[j][0] + y * c.m[j][1] + z * c.m[j][2] + c.o[j];
+  for (int j = 0; j < 3; ++j)
+    q[j] = R::add(R::fma(z, c.m[j][2], R::fma(y, c.m[j][1], R::mul(x, c.m[j][0]))), c.o[j]);
 }
 
 template <typename T> __device__ __forceinline__ T sqrt_t(T v);
-template <> __device__ __forceinline__ float sqrt_t<float>(float v) { return sqrtf(v); }
-template <> __device__ __forceinline__ double sqrt_t<double>(double v) { return sqrt(v); }
+template <> __device__ __forceinline__ float sqrt_t<float>(float v) { return __fsqrt_rn(v); }
+template <> __device__ __forceinline__ double sqrt_t<double>(double v) { return __dsqrt_rn(v); }
+
+// One face of one view: camera-space vertices q, image coordinates img (legacy.py:136-137), unit normal
+// (trianglemesh.py:328-334).  An out-of-range vertex index gives NaNs (never a read outside the buffer).
+template <typename T>
+__device__ __forceinline__ void project_face(const PrepareParams<T>& pp, const ViewCamera<T>& cam, const int b,
+                                             const int f, T q[3][3], T img[6], T nrm[3]) {
+  typedef RN<T> R;
+  const T* vb = pp.vertices + (pp.Bv == 1 ? (int64_t)0 : (int64_t)b * pp.V * 3);
+  const T p0 = pp.proj[0], p1 = pp.proj[1], p2 = pp.proj[2];
+#pragma unroll
+  for (int k = 0; k < 3; ++k) {
+    const int64_t vi = pp.faces[(int64_t)f * 3 + k];
+    if ((uint64_t)vi >= (uint64_t)pp.V) {
+      q[k][0] = q[k][1] = q[k][2] = (T)NAN;
+    } else {
+      to_camera<T>(cam, vb + vi * 3, q[k]);
+    }
+    const T pz = R::mul(q[k][2], p2);
+    img[k * 2 + 0] = R::div(R::mul(q[k][0], p0), pz);
+    img[k * 2 + 1] = R::div(R::mul(q[k][1], p1), pz);
+  }
+  const T e0x = R::sub(q[1][0], q[0][0]), e0y = R::sub(q[1][1], q[0][1]), e0z = R::sub(q[1][2], q[0][2]);
+  const T e1x = R::sub(q[2][0], q[0][0]), e1y = R::sub(q[2][1], q[0][1]), e1z = R::sub(q[2][2], q[0][2]);
+  const T nx = R::fma(e0y, e1z, -R::mul(e0z, e1y)), ny = R::fma(e0z, e1x, -R::mul(e0x, e1z));
+  const T nz = R::fma(e0x, e1y, -R::mul(e0y, e1x));
+  const T len = R::add(sqrt_t<T>(R::fma(nz, nz, R::fma(ny, ny, R::mul(nx, nx)))), (T)1e-10);
+  nrm[0] = R::div(nx, len); nrm[1] = R::div(ny, len); nrm[2] = R::div(nz, len);
+}
 
 template <typename T>
 __global__ void __launch_bounds__(256) prepare_vertices_fwd_kernel(PrepareParams<T> pp) {
@@ -92,34 +126,17 @@ __global__ void __launch_bounds__(256) prepare_vertices_fwd_kernel(PrepareParams
   if (g >= (int64_t)pp.B * pp.F) return;
   const int b = (int)(g / pp.F), f = (int)(g % pp.F);
   const ViewCamera<T> cam = load_camera<T>(pp, b);
-  const T* vb = pp.vertices + (pp.Bv == 1 ? (int64_t)0 : (int64_t)b * pp.V * 3);
-  const T p0 = pp.proj[0], p1 = pp.proj[1], p2 = pp.proj[2];
-  T q[3][3];
-#pragma unroll
-  for (int k = 0; k < 3; ++k) {
-    const int64_t vi = pp.faces[(int64_t)f * 3 + k];
-    if ((uint64_t)vi >= (uint64_t)pp.V) {              // out-of-range index: never read outside the buffer
-      q[k][0] = q[k][1] = q[k][2] = (T)NAN;
-      continue;
-    }
-    to_camera<T>(cam, vb + vi * 3, q[k]);
-  }
+  T q[3][3], img[6], nrm[3];
+  project_face<T>(pp, cam, b, f, q, img, nrm);
   T* oc = pp.face_cam + g * 9;
   T* oi = pp.face_img + g * 6;
 #pragma unroll
   for (int k = 0; k < 3; ++k) {
     oc[k * 3 + 0] = q[k][0]; oc[k * 3 + 1] = q[k][1]; oc[k * 3 + 2] = q[k][2];
-    const T pz = q[k][2] * p2;                                   // legacy.py:136-137
-    oi[k * 2 + 0] = (q[k][0] * p0) / pz;
-    oi[k * 2 + 1] = (q[k][1] * p1) / pz;
+    oi[k * 2 + 0] = img[k * 2]; oi[k * 2 + 1] = img[k * 2 + 1];
   }
-  // trianglemesh.py:328-334
-  const T e0x = q[1][0] - q[0][0], e0y = q[1][1] - q[0][1], e0z = q[1][2] - q[0][2];
-  const T e1x = q[2][0] - q[0][0], e1y = q[2][1] - q[0][1], e1z = q[2][2] - q[0][2];
-  const T nx = e0y * e1z - e0z * e1y, ny = e0z * e1x - e0x * e1z, nz = e0x * e1y - e0y * e1x;
-  const T len = sqrt_t<T>(nx * nx + ny * ny + nz * nz) + (T)1e-10;
   T* on = pp.face_nrm + g * 3;
-  on[0] = nx / len; on[1] = ny / len; on[2] = nz / len;
+  on[0] = nrm[0]; on[1] = nrm[1]; on[2] = nrm[2];
 }
 
 template <typename T, bool CAMGRAD>

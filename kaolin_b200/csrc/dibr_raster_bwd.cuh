@@ -17,6 +17,10 @@ namespace dibr {
                                    // = 48 registers spilled 56 bytes per thread and measured 4 % slower at c2)
 #endif
 
+#ifndef DIBR_BWD_MAXSTEPS
+#define DIBR_BWD_MAXSTEPS 5        // shuffle steps of the per-face reduction inside a warp (see raster_bwd_tile)
+#endif
+
 template <typename T>
 struct RasterBwdParams {
   FeatSet<const T> grad_out;   // n tensors (B,H,W,C_t)
@@ -183,7 +187,13 @@ __device__ __forceinline__ void raster_bwd_tile(const RasterBwdParams<T>& bp, co
 #pragma unroll
   for (int s = 0; s < 5; ++s)
     if (__any_sync(0xffffffffu, covered && src[s] != (int)(threadIdx.x & 31))) steps |= 1u << s;
-  const bool leader = covered && ((peers & ((1u << (threadIdx.x & 31)) - 1u)) == 0u);
+  // A group is reduced in sub-groups of 2^DIBR_BWD_MAXSTEPS consecutive ranks, each with its own leader (the member
+  // whose rank is a multiple of that size): 5 = one leader per (warp, face).
+  const int my_rank = __popc(peers & ((1u << (threadIdx.x & 31)) - 1u));
+  const bool leader = covered && (my_rank & ((1 << DIBR_BWD_MAXSTEPS) - 1)) == 0;
+  steps &= (1u << DIBR_BWD_MAXSTEPS) - 1u;
+#pragma unroll
+  for (int s = DIBR_BWD_MAXSTEPS; s < 5; ++s) src[s] = (int)(threadIdx.x & 31);     // steps beyond the sub-group: none
 
   T w0 = 0, w1 = 0, w2 = 0;
   const int64_t tf = (int64_t)b * bp.F + (covered ? f : 0);
@@ -221,7 +231,8 @@ __device__ __forceinline__ void raster_bwd_tile(const RasterBwdParams<T>& bp, co
   }
   // the reduction depth of the warp's largest group, dispatched once: no per-step branches in the channel loops
   const int ns = 32 - __clz(steps);
-  if (ns <= 3) raster_bwd_tail<T, 3>(bp, pix, tf, covered, leader, w0, w1, w2, src, k3, dw1, dw2);
+  if (DIBR_BWD_MAXSTEPS <= 2 || ns <= 2) raster_bwd_tail<T, (DIBR_BWD_MAXSTEPS < 2 ? DIBR_BWD_MAXSTEPS : 2)>(bp, pix, tf, covered, leader, w0, w1, w2, src, k3, dw1, dw2);
+  else if (ns <= 3) raster_bwd_tail<T, 3>(bp, pix, tf, covered, leader, w0, w1, w2, src, k3, dw1, dw2);
   else if (ns == 4) raster_bwd_tail<T, 4>(bp, pix, tf, covered, leader, w0, w1, w2, src, k3, dw1, dw2);
   else raster_bwd_tail<T, 5>(bp, pix, tf, covered, leader, w0, w1, w2, src, k3, dw1, dw2);
 }

@@ -70,3 +70,59 @@ def mask_iou(lhs_mask, rhs_mask):
         rhs_mask = rhs_mask.to(lhs_mask.dtype)
     return MaskIouCuda.apply(lhs_mask.reshape(batch_size, -1).contiguous(),
                              rhs_mask.reshape(batch_size, -1).contiguous())
+
+
+class ImageL1Cuda(Function):
+    """forward(ctx, a, b) -> mean |a - b| (scalar); backward -> (grad_a, grad_b)."""
+    @staticmethod
+    def forward(ctx, a, b):
+        fn = "image_l1"
+        dev = a.device
+        suf = _lib.suffix(a.dtype, fn)
+        n = a.numel()
+        loss = torch.empty((), dtype=a.dtype, device=dev)
+        lib = _lib.load()
+        with torch.cuda.device(dev):
+            nbytes = lib.dibr_image_l1_workspace_bytes(n, a.element_size())
+            ws = torch.empty(nbytes, dtype=torch.uint8, device=dev)
+            code = getattr(lib, "dibr_image_l1_fwd_" + suf)(_lib.ptr(a), _lib.ptr(b), n, _lib.ptr(loss), _lib.ptr(ws),
+                                                            nbytes, _lib.current_stream(dev))
+        _lib.check(code, fn)
+        ctx.save_for_backward(a, b)
+        return loss
+
+    @staticmethod
+    def backward(ctx, grad_loss):
+        fn = "image_l1_backward"
+        a, b = ctx.saved_tensors
+        dev = a.device
+        suf = _lib.suffix(a.dtype, fn)
+        g_a = torch.empty_like(a) if ctx.needs_input_grad[0] else None
+        g_b = torch.empty_like(b) if ctx.needs_input_grad[1] else None
+        with torch.cuda.device(dev):
+            code = getattr(_lib.load(), "dibr_image_l1_bwd_" + suf)(
+                _lib.ptr(grad_loss.contiguous()), _lib.ptr(a), _lib.ptr(b), a.numel(), _lib.ptr(g_a), _lib.ptr(g_b),
+                _lib.current_stream(dev))
+        _lib.check(code, fn)
+        return g_a, g_b
+
+
+def image_l1(image, gt_image):
+    r"""``torch.mean(torch.abs(image - gt_image))`` — the image loss of the DIB-R fitting loop
+    (examples/tutorial/ian_dibr.py:260; not a function of the reference's ``kaolin.metrics.render``, which composes it
+    from torch ops) as one deterministic reduction forward and one elementwise kernel backward.
+
+    Args:
+        image (torch.FloatTensor): rendered image, any shape.
+        gt_image (torch.FloatTensor): target of the same shape.
+
+    Returns:
+        (torch.FloatTensor): the mean absolute difference, as a torch scalar.
+    """
+    assert gt_image.shape == image.shape
+    if not image.is_cuda or gt_image.device != image.device:
+        raise RuntimeError("image_l1: both images must be CUDA tensors on the same device "
+                           "(libdibr_b200.so has no CPU path)")
+    if gt_image.dtype != image.dtype:
+        gt_image = gt_image.to(image.dtype)
+    return ImageL1Cuda.apply(image.contiguous(), gt_image.contiguous())

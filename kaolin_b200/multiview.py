@@ -76,9 +76,10 @@ def look_at(eye, at, up):
 
 class MultiViewOptimizer:
     """Multi-view DIB-R shape optimisation (BASELINE.json config 4).  Each rank owns a contiguous shard of the
-    cameras; the mesh (vertices leaf, faces, per-vertex features) is replicated.  One step = prepare_vertices (fused CUDA kernel)
-    -> dibr_rasterization -> mask IoU + L1 feature loss -> backward -> ONE all-reduce of ``vertices.grad`` ->
-    Adam.  Losses are sums over the local views divided by the GLOBAL view count, so the all-reduced gradient
+    cameras; the mesh (vertices leaf, faces, per-vertex features) is replicated.  One step =
+    dibr_rasterization_from_mesh (prepare_vertices folded into the setup kernel) -> mask IoU + image L1 loss (fused
+    kernels) -> backward -> ONE all-reduce of ``vertices.grad`` -> Adam (fused), replayed from one CUDA graph after
+    ``capture()``.  Losses are sums over the local views divided by the GLOBAL view count, so the all-reduced gradient
     equals the single-process gradient over all cameras."""
 
     def __init__(self, vertices, faces, vertex_features, rot, trans, target_mask, target_feat, height, width,
@@ -97,11 +98,16 @@ class MultiViewOptimizer:
                                  dtype=vertices.dtype, device=vertices.device)
         # the per-face features do not depend on the vertices being optimised: gathered once
         self.face_features = vertex_features[faces].unsqueeze(0).expand(rot.shape[0], -1, -1, -1).contiguous()
-        self.opt = torch.optim.Adam([self.vertices], lr=lr)
+        # one fused, capturable Adam kernel on the GPU (the default foreach path: 4-5 single-CTA launches per step)
+        on_gpu = self.vertices.is_cuda
+        self.opt = torch.optim.Adam([self.vertices], lr=lr, fused=on_gpu, capturable=on_gpu) if on_gpu else \
+            torch.optim.Adam([self.vertices], lr=lr)
         self.last_grad = None               # the all-reduced vertices.grad of the last step
-        self.launch_mode = "eager launches (optimizer step + NCCL all-reduce are not captured)"
+        self.launch_mode = "eager launches"
         self.time_all_reduce = False        # measurement: CUDA events around the collective on the compute stream
         self._ar_events = []
+        self._graph = None                  # CUDA graph of one whole step (capture())
+        self._graph_loss = None
 
     def all_reduce_ms(self):
         """Durations of the all-reduce calls made while ``time_all_reduce`` was set (synchronises)."""
@@ -111,23 +117,66 @@ class MultiViewOptimizer:
         return ms or [0.0]
 
     def loss(self):
-        from .render.mesh import dibr_rasterization, prepare_vertices
+        from .render.mesh import dibr_rasterization_from_mesh
         from .metrics.render import mask_iou as fused_mask_iou
         verts = self.vertices if self.vertices.dim() == 3 else self.vertices.unsqueeze(0)
-        fcam, fimg, nrm = prepare_vertices(verts, self.faces, self.proj, camera_rot=self.rot,
-                                           camera_trans=self.trans)
-        b = fimg.shape[0]
-        img, soft, face_idx = dibr_rasterization(self.height, self.width, fcam[..., 2], fimg,
-                                                 self.face_features, nrm[..., 2],
-                                                 sigmainv=self.sigmainv, boxlen=self.boxlen, knum=self.knum)
+        b = self.rot.shape[0]
+        # prepare_vertices + dibr_rasterization (ian_dibr.py:246-252) in one native call each way
+        img, soft, face_idx = dibr_rasterization_from_mesh(self.height, self.width, verts, self.faces,
+                                                           self.face_features, self.proj, camera_rot=self.rot,
+                                                           camera_trans=self.trans, sigmainv=self.sigmainv,
+                                                           boxlen=self.boxlen, knum=self.knum)
         # per-view IoU and L1 terms, normalised by the global number of views:
         # sum_local(1 - iou_b) / n_total = mask_iou(local) * b / n_total   (fused reduction + analytic backward)
+        # (every view has the same number of pixels: the sum of the per-view L1 means is b times the shard's mean)
+        from .metrics.render import image_l1
         l_mask = fused_mask_iou(soft, self.target_mask) * (b / self.n_views_total)
-        l_feat = torch.sum(torch.abs(img - self.target_feat).mean(dim=(1, 2, 3))) / self.n_views_total
+        l_feat = image_l1(img, self.target_feat) * (b / self.n_views_total)
         return l_mask + l_feat, soft, face_idx
 
+    def capture(self, warmup=3):
+        """Capture one whole step — prepare + render + losses + backward + the NCCL all-reduce + Adam — into a CUDA
+        graph; ``step()`` then replays it (one launch per step: the step is ~35 launches of 3-150 us each, so eager
+        dispatch costs as much as the kernels).  The library only enqueues work on the current stream, NCCL
+        collectives and the fused capturable Adam are capturable.  Camera tensors, targets and ``vertices`` are the
+        static inputs (update them in place).  Falls back to eager launches, with the reason in ``launch_mode``."""
+        if not self.vertices.is_cuda:
+            return False
+        dev = self.vertices.device
+        try:
+            side = torch.cuda.Stream(dev)
+            side.wait_stream(torch.cuda.current_stream(dev))
+            with torch.cuda.stream(side):
+                for _ in range(warmup):
+                    self._eager_step()
+            torch.cuda.current_stream(dev).wait_stream(side)
+            torch.cuda.synchronize(dev)
+            self.opt.zero_grad(set_to_none=True)       # grads are allocated from the graph's pool during capture
+            graph = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(graph):
+                self._graph_loss = self._eager_step(zero=False)
+            self._graph = graph
+            self.launch_mode = "CUDA graph replay of the whole step (render, losses, backward, all-reduce, Adam)"
+            return True
+        except Exception as e:                          # noqa: BLE001 - any capture failure means: stay eager
+            self._graph = None
+            torch.cuda.synchronize(dev)
+            self.launch_mode = f"eager launches (graph capture failed: {type(e).__name__}: {str(e)[:120]})"
+            self.opt.zero_grad(set_to_none=True)
+            return False
+
     def step(self):
-        self.opt.zero_grad(set_to_none=True)
+        if self._graph is not None and not self.time_all_reduce:
+            self._graph.replay()
+            self.last_grad = self.vertices.grad
+            return self._graph_loss
+        return self._eager_step()
+
+    def _eager_step(self, zero=True):
+        if zero:
+            # after capture() the graph owns vertices.grad: keep that tensor (zero it in place) so that replays and
+            # eager measurement steps can be mixed
+            self.opt.zero_grad(set_to_none=self._graph is None)
         loss, _, _ = self.loss()
         loss.backward()
         if self.time_all_reduce and self.vertices.is_cuda:

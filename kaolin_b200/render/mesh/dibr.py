@@ -16,7 +16,7 @@ from .rasterization import rasterize, _legacy_to_opengl, nvdiff, _get_nvdiff_glc
 __all__ = [
     "dibr_soft_mask",
     "dibr_rasterization",
-]
+]   # = the reference's (dibr.py:21-24); dibr_rasterization_from_mesh (an addition) is exported by the package
 
 
 class DibrSoftMaskCuda(Function):
@@ -195,6 +195,117 @@ class DibrRasterizationCuda(Function):
         return (None, None, None, gi, None, None, None, None, None, None, *gfs)
 
 
+class DibrRasterizationFromMeshCuda(Function):
+    """``prepare_vertices`` + ``dibr_rasterization`` as ONE native call each way (the projection
+    is folded into the setup kernel, its backward runs behind the two gradient kernels inside the same call).
+    forward(ctx, height, width, vertices, faces, proj, rot, trans, transform, batch, sigmainv, boxlen, knum,
+    multiplier, eps, *face_features) -> (*interpolated_features, soft_mask, face_idx); gradients flow to ``vertices``,
+    the camera tensors that require grad, and the face features."""
+    @staticmethod
+    def forward(ctx, height, width, vertices, faces, proj, rot, trans, transform, batch, sigmainv, boxlen, knum,
+                multiplier, eps, *face_features):
+        fn = "dibr_rasterization_from_mesh"
+        dev = _require_cuda(fn, vertices=vertices, faces=faces,
+                            **{f"face_features[{i}]": f for i, f in enumerate(face_features)})
+        dtype = vertices.dtype
+        suf = _lib.suffix(dtype, fn)
+        b, f = int(batch), faces.shape[0]
+        feats = []
+        for t in face_features:
+            if t.dtype != dtype or t.dim() != 4 or tuple(t.shape[:3]) != (b, f, 3):
+                raise RuntimeError(f"{fn}: every face_features tensor must be (B,F,3,C) of dtype {dtype}")
+            feats.append(t.contiguous())
+        chans = [t.shape[-1] for t in feats]
+        outs = [torch.empty((b, height, width, c), dtype=dtype, device=dev) for c in chans]
+        face_idx = torch.empty((b, height, width), dtype=torch.long, device=dev)
+        soft = torch.empty((b, height, width), dtype=dtype, device=dev)
+        img = torch.empty((b, f, 3, 2), dtype=dtype, device=dev)       # written by the setup kernel
+        z = torch.empty((b, f, 3), dtype=dtype, device=dev)
+        need_geo = any(ctx.needs_input_grad[i] for i in (2, 4, 5, 6, 7))
+        keep = 1 if need_geo else 0
+        lib = _lib.load()
+        with torch.cuda.device(dev):
+            nbytes = lib.dibr_rasterization_workspace_bytes(b, b * f, int(height), int(width), keep)
+            try:
+                ws = torch.empty(max(int(nbytes), 256), dtype=torch.uint8, device=dev)
+            except torch.cuda.OutOfMemoryError:
+                if not keep:
+                    raise
+                keep = 0
+                nbytes = lib.dibr_rasterization_workspace_bytes(b, b * f, int(height), int(width), 0)
+                ws = torch.empty(max(int(nbytes), 256), dtype=torch.uint8, device=dev)
+            code = getattr(lib, "dibr_rasterization_from_mesh_fwd_" + suf)(
+                _lib.ptr(vertices), _lib.ptr(faces), _lib.ptr(proj), _lib.ptr(rot), _lib.ptr(trans),
+                _lib.ptr(transform), vertices.shape[0], vertices.shape[1], _lib.ptr_array(feats),
+                _lib.int_array(chans), len(feats), b, f, int(height), int(width), float(multiplier), float(eps),
+                float(sigmainv), float(boxlen), int(knum), _lib.ptr(img), _lib.ptr(z), _lib.ptr_array(outs),
+                _lib.ptr(face_idx), _lib.ptr(soft), _lib.ptr(ws), nbytes, keep, _lib.current_stream(dev))
+        _lib.check(code, fn)
+        ctx.save_for_backward(face_idx, soft, img, vertices, faces, proj, rot, trans, transform, *feats)
+        ctx.mark_non_differentiable(face_idx)
+        ctx.set_materialize_grads(False)
+        ctx.args = (float(multiplier), float(eps), float(sigmainv), float(boxlen), int(knum))
+        ctx.out_shapes = [tuple(o.shape) for o in outs]
+        ctx.bins = ws if keep else None
+        ctx.batch = b
+        return (*outs, soft, face_idx)
+
+    @staticmethod
+    def backward(ctx, *grads):
+        fn = "dibr_rasterization_from_mesh_backward"
+        g_outs, g_soft = grads[:-2], grads[-2]
+        n_in = 14 + len(g_outs)
+        if g_soft is None and all(g is None for g in g_outs):
+            return (None,) * n_in
+        face_idx, soft, img, vertices, faces, proj, rot, trans, transform = ctx.saved_tensors[:9]
+        feats = list(ctx.saved_tensors[9:])
+        dev, dtype = img.device, img.dtype
+        suf = _lib.suffix(dtype, fn)
+        multiplier, eps, sigmainv, boxlen, knum = ctx.args
+        b, f = img.shape[0], img.shape[1]
+        h, w = face_idx.shape[1], face_idx.shape[2]
+        need = ctx.needs_input_grad
+        any_out = any(g is not None for g in g_outs)
+        gouts = [torch.zeros(shp, dtype=dtype, device=dev) if g is None else g.contiguous()
+                 for g, shp in zip(g_outs, ctx.out_shapes)] if any_out else []
+        g_soft = None if g_soft is None else g_soft.contiguous()
+        gi = torch.empty_like(img)                                    # scratch of the native call
+        gfs = [torch.empty_like(t) for t in feats] if any_out else []
+        chans = [t.shape[-1] for t in feats]
+        g_vert = torch.empty_like(vertices) if need[2] else None
+        g_proj = torch.empty_like(proj) if need[4] else None
+        g_rot = torch.empty_like(rot) if rot is not None and need[5] else None
+        g_trans = torch.empty_like(trans) if trans is not None and need[6] else None
+        g_transform = torch.empty_like(transform) if transform is not None and need[7] else None
+        geo = any(t is not None for t in (g_vert, g_proj, g_rot, g_trans, g_transform))
+        lib = _lib.load()
+        with torch.cuda.device(dev):
+            ws, ready = ctx.bins, 6
+            ctx.bins = None
+            if ws is None:
+                nbytes = lib.dibr_soft_mask_workspace_bytes(b, b * f, h, w, 0, img.element_size())
+                ws, ready = torch.empty(max(int(nbytes), 256), dtype=torch.uint8, device=dev), 0
+            if geo:
+                code = getattr(lib, "dibr_rasterization_from_mesh_bwd_" + suf)(
+                    _lib.ptr_array(gouts) if any_out else None, _lib.ptr(g_soft), _lib.ptr(soft), _lib.ptr(face_idx),
+                    _lib.ptr(img), _lib.ptr_array(feats), _lib.int_array(chans), len(feats), _lib.ptr(vertices),
+                    _lib.ptr(faces), _lib.ptr(proj), _lib.ptr(rot), _lib.ptr(trans), _lib.ptr(transform),
+                    vertices.shape[0], vertices.shape[1], b, f, h, w, multiplier, eps, sigmainv, boxlen, knum,
+                    _lib.ptr(gi), _lib.ptr_array(gfs) if any_out else None, _lib.ptr(g_vert), _lib.ptr(g_proj),
+                    _lib.ptr(g_rot), _lib.ptr(g_trans), _lib.ptr(g_transform), _lib.ptr(ws), ws.numel(), ready,
+                    _lib.current_stream(dev))
+            else:                                                     # only the face features require grad
+                code = getattr(lib, "dibr_rasterization_bwd_fused_" + suf)(
+                    _lib.ptr_array(gouts) if any_out else None, _lib.ptr(g_soft), _lib.ptr(soft), _lib.ptr(face_idx),
+                    _lib.ptr(img), _lib.ptr_array(feats), _lib.int_array(chans), len(feats), b, f, h, w, multiplier,
+                    eps, sigmainv, boxlen, knum, _lib.ptr(gi), _lib.ptr_array(gfs) if any_out else None,
+                    _lib.ptr(ws), ws.numel(), ready, _lib.current_stream(dev))
+        _lib.check(code, fn)
+        gfs = gfs if any_out else [None] * len(feats)
+        return (None, None, g_vert, None, g_proj, g_rot, g_trans, g_transform, None, None, None, None, None, None,
+                *gfs)
+
+
 def dibr_soft_mask(face_vertices_image, selected_face_idx,
                    sigmainv=7000, boxlen=0.02, knum=30, multiplier=1000.):
     r"""Soft foreground mask of DIB-R (reference: kaolin/render/mesh/dibr.py:75-117).
@@ -253,3 +364,35 @@ def dibr_rasterization(height, width, face_vertices_z, face_vertices_image,
         _multiplier
     )
     return interpolated_features, soft_mask, face_idx
+
+
+def dibr_rasterization_from_mesh(height, width, vertices, faces, face_features, camera_proj, camera_rot=None,
+                                 camera_trans=None, camera_transform=None, sigmainv=7000, boxlen=0.02, knum=30,
+                                 multiplier=None, eps=None):
+    r"""``prepare_vertices`` followed by ``dibr_rasterization`` in one native call each way — the composition
+
+    .. code-block:: python
+
+        cam, img, nrm = prepare_vertices(vertices, faces, camera_proj, camera_rot, camera_trans, camera_transform)
+        dibr_rasterization(height, width, cam[..., 2], img, face_features, nrm[..., 2], sigmainv, boxlen, knum,
+                           multiplier, eps)
+
+    of the reference (kaolin/render/mesh/utils.py:128-175, dibr.py:119-209; the training step of
+    examples/tutorial/ian_dibr.py:246-252), with identical results: the setup kernel projects the faces itself, the
+    camera-space (B,F,3,3) tensor and the normals are never written, and backward returns ``vertices.grad`` (and the
+    camera gradients) directly.  Arguments as in the two reference functions; ``face_features`` is (B,F,3,C) or a list.
+
+    Returns:
+        (features (B,H,W,C) or tuple of tensors, soft_mask (B,H,W), face_idx (B,H,W) int64, -1 = none)
+    """
+    from .utils import _mesh_and_cameras
+    is_list = isinstance(face_features, (list, tuple))
+    feats = list(face_features) if is_list else [face_features]
+    if not 0 < len(feats) <= 8:
+        raise ValueError("dibr_rasterization_from_mesh: between 1 and 8 face feature tensors are supported")
+    v, f, proj, rot, trans, transform, batch = _mesh_and_cameras(vertices, faces, camera_proj, camera_rot,
+                                                                 camera_trans, camera_transform)
+    *outs, soft_mask, face_idx = DibrRasterizationFromMeshCuda.apply(
+        height, width, v, f, proj, rot, trans, transform, batch, sigmainv, boxlen, knum,
+        1000 if multiplier is None else multiplier, 1e-8 if eps is None else eps, *feats)
+    return (tuple(outs) if is_list else outs[0]), soft_mask, face_idx

@@ -103,6 +103,13 @@ def prepare_vertices(vertices, faces, camera_proj, camera_rot=None, camera_trans
         (torch.Tensor, torch.Tensor, torch.Tensor): face_vertices_camera :math:`(B, F, 3, 3)`,
         face_vertices_image :math:`(B, F, 3, 2)`, face_normals :math:`(B, F, 3)`.
     """
+    return PrepareVerticesCuda.apply(*_mesh_and_cameras(vertices, faces, camera_proj, camera_rot, camera_trans,
+                                                        camera_transform))
+
+
+def _mesh_and_cameras(vertices, faces, camera_proj, camera_rot=None, camera_trans=None, camera_transform=None):
+    """Argument checks and broadcasting of prepare_vertices (utils.py:128-175); returns the contiguous tensors
+    (vertices, faces, proj (3), rot | None, trans | None, transform | None, batch) the native calls take."""
     if camera_transform is None:
         assert camera_trans is not None and camera_rot is not None, \
             "camera_transform or camera_trans and camera_rot must be defined"
@@ -146,7 +153,7 @@ def prepare_vertices(vertices, faces, camera_proj, camera_rot=None, camera_trans
             transform = transform.expand(batch, 4, 3).contiguous()
     if bv != 1 and bv != batch:
         raise RuntimeError(f"prepare_vertices: vertices batch ({bv}) and camera batch ({batch}) do not broadcast")
-    return PrepareVerticesCuda.apply(vertices.contiguous(), faces.contiguous(), proj, rot, trans, transform, batch)
+    return vertices.contiguous(), faces.contiguous(), proj, rot, trans, transform, batch
 
 
 # ----------------------------------------------------------------------------------------------------------
