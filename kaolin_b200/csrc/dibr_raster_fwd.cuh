@@ -45,12 +45,6 @@ struct RasterFwdParams {
   // t = row * 16 + column), so that the soft-mask kernel neither re-reads face_idx nor visits finished tiles.
   T* soft_out;             // (B,H,W) or nullptr
   unsigned* tile_unc;      // [B * tiles_per_view * 8] or nullptr
-  // ... and the soft-mask kernel's WORK LIST: the tiles that have both uncovered pixels and soft-mask candidates
-  // (the only ones that kernel has anything to do for — a few percent of all tiles), appended as they finish here.
-  const int* soft_tile_count;   // the soft-mask lists' tile_count [B * slots_per_view] (fine tiles, then coarse cells)
-  const int* soft_large_count;  // ... and large_count [B]
-  unsigned* soft_work;          // [B * tiles_per_view] tile_global entries
-  unsigned* soft_work_count;    // [1], zeroed with the binning counters
 };
 
 template <typename T>
@@ -275,7 +269,6 @@ struct ScatterShared {
   unsigned short hit[NW][HIT_CAP];// per-warp stack of candidates: owner lane << 8 | row << 4 | column
   float pitch;                    // x distance of neighbouring pixel centres (2 * multiplier / W)
   int nan_seen;
-  int n_unc;                      // uncovered pixels of the tile (epilogue)
 };
 
 struct FaceRegs {                 // one face per lane (multiplied coordinates), read by shuffle from its owner lane
@@ -489,7 +482,6 @@ raster_fwd_scatter_kernel(RasterFwdParams<float> rp, FaceLayout fl, Geometry geo
   }
   if (threadIdx.x == 0) {
     sh.nan_seen = 0;
-    sh.n_unc = 0;
     sh.pitch = __fmul_rn(2.0f, pix_scale(rp.pix_mult, geo.W));
   }
   __syncthreads();
@@ -582,22 +574,7 @@ raster_fwd_scatter_kernel(RasterFwdParams<float> rp, FaceLayout fl, Geometry geo
     }
     if (unc) {                                                         // (CTA-uniform)
       const unsigned um = __ballot_sync(0xffffffffu, in_image && best_f < 0);
-      if (lane == 0) {
-        unc[t >> 5] = um;
-        if (um != 0u) atomicAdd(&sh.n_unc, __popc(um));
-      }
-    }
-  }
-  if (rp.soft_work) {                                                  // (CTA-uniform)
-    __syncthreads();
-    if (threadIdx.x == 0 && sh.n_unc > 0) {
-      const int64_t s0 = (int64_t)b * geo.slots_per_view;
-      const int n_cand = rp.soft_tile_count[s0 + ty * geo.tiles_x + tx] +
-                         rp.soft_tile_count[s0 + geo.tiles_per_view + (ty / COARSE) * geo.coarse_x + (tx / COARSE)] +
-                         rp.soft_large_count[b];
-      if (n_cand > 0)
-        rp.soft_work[atomicAdd(rp.soft_work_count, 1u)] =
-            (unsigned)b * (unsigned)geo.tiles_per_view + (unsigned)(ty * geo.tiles_x + tx);
+      if (lane == 0) unc[t >> 5] = um;
     }
   }
 }

@@ -774,29 +774,6 @@ soft_mask_kernel(SoftParams<T> sp, FaceLayout fl, Geometry geo, BinLists L) {
   soft_tile<T, MODE, NT>(sp, fl, geo, L, b, tx, ty);
 }
 
-// dibr_rasterization (fp32): the tiles with work — uncovered pixels AND candidates — were listed by the rasterizer's
-// epilogue (RasterFwdParams::soft_work); a persistent grid takes them off the list with an atomic cursor.  Every other
-// tile already holds its final values, and no CTA is launched for it (one CTA per tile spent a sixth of the kernel's
-// time on ~90 % of the tiles just to find out: two dependent loads and an exit each).
-template <typename T, int NT>
-__global__ void __launch_bounds__(NT, (sizeof(T) == 4 ? DIBR_SOFT_TPS / NT : 512 / NT))
-soft_mask_worklist_kernel(SoftParams<T> sp, FaceLayout fl, Geometry geo, BinLists L, const unsigned* work,
-                          const unsigned* work_count, unsigned* cursor) {
-  __shared__ unsigned s_next;
-  const unsigned n = *work_count;
-  while (true) {
-    __syncthreads();                                   // the previous tile is done with the shared memory
-    if (threadIdx.x == 0) s_next = atomicAdd(cursor, 1u);
-    __syncthreads();
-    const unsigned i = s_next;
-    if (i >= n) break;
-    const unsigned tg = work[i];
-    const unsigned b = tg / (unsigned)geo.tiles_per_view, tile = tg - b * (unsigned)geo.tiles_per_view;
-    const unsigned ty = tile / (unsigned)geo.tiles_x;
-    soft_tile<T, MODE_FWD, NT>(sp, fl, geo, L, (int)b, (int)(tile - ty * (unsigned)geo.tiles_x), (int)ty);
-  }
-}
-
 // Backward of the tiles whose pairs did not fit the log: a small persistent grid walks the overflow list
 // (normally empty: the CTAs read one word and exit).
 template <typename T, int NT>
