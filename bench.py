@@ -610,7 +610,20 @@ def gpu_run(args):
             line["cpu_baseline"] = cpu_reference_run(args.workload, 1, 0, wl.total, emit=False)
         print(json.dumps(line), flush=True)
     if world > 1:
-        dist.destroy_process_group()
+        # Teardown: a CUDA graph that captured an NCCL collective keeps the communicator busy, and destroying the
+        # process group under it deadlocks (measured: the 2-GPU run printed its line and then hung).  Release the
+        # graphs first, make sure every rank is done, and leave without running NCCL's destructors.
+        if c4 is not None:
+            wl4.opt._graph = None
+        del wl
+        import gc
+        gc.collect()
+        torch.cuda.synchronize()
+        dist.barrier()
+        torch.cuda.synchronize()
+        sys.stdout.flush()
+        sys.stderr.flush()
+        os._exit(0)
 
 
 def main():
