@@ -17,6 +17,9 @@ namespace dibr {
                                    // = 48 registers spilled 56 bytes per thread and measured 4 % slower at c2)
 #endif
 
+#ifndef DIBR_BWD_PREFETCH
+#define DIBR_BWD_PREFETCH 0
+#endif
 #ifndef DIBR_BWD_MAXSTEPS
 #define DIBR_BWD_MAXSTEPS 5        // shuffle steps of the per-face reduction inside a warp (see raster_bwd_tile)
 #endif
@@ -174,6 +177,14 @@ __device__ __forceinline__ void raster_bwd_tile(const RasterBwdParams<T>& bp, co
 
   long long f = -1;
   if (in_image) f = bp.face_idx[pix];
+#if DIBR_BWD_PREFETCH
+  // the upstream gradient's address depends on the pixel only: start its fetch together with face_idx, two dependent
+  // gathers (face_idx -> coordinates / features) before it is used (ncu: the kernel waits on long-scoreboard)
+  if (in_image) {
+    for (int ft = 0; ft < bp.feat.n; ++ft)
+      asm volatile("prefetch.global.L1 [%0];" ::"l"(bp.grad_out.ptr[ft] + pix * bp.feat.ch[ft]));
+  }
+#endif
   if (f >= bp.F) f = -1;                             // never write out of bounds on a corrupt index
   const bool covered = f >= 0;
   const unsigned any = __ballot_sync(0xffffffffu, covered);

@@ -194,12 +194,24 @@ __device__ __forceinline__ void store_features(const T* __restrict__ feat, T* __
                                                const int64_t pix, const int best_f, const T w0, const T w1,
                                                const T w2) {
   T* o = out + pix * CC;
+  T v[CC];
   if (best_f >= 0) {
     const T* f0 = feat + (vbase + best_f) * 3 * CC;
-    interp_block<T, CC>(f0, f0 + CC, f0 + 2 * CC, o, w0, w1, w2);
+    interp_block<T, CC>(f0, f0 + CC, f0 + 2 * CC, v, w0, w1, w2);
   } else {
 #pragma unroll
-    for (int d = 0; d < CC; ++d) o[d] = (T)0;
+    for (int d = 0; d < CC; ++d) v[d] = (T)0;
+  }
+  // a pixel's channels are contiguous: 2 / 4 fp32 channels go out as one 8 / 16-byte store (STG.E.64 / STG.E.128) when
+  // the tensor's base is that aligned (torch allocations are); a warp then writes 2 x 16 pixels = two contiguous
+  // 128 / 256-byte row segments with one instruction
+  if (sizeof(T) == 4 && CC == 2 && (reinterpret_cast<uintptr_t>(out) & 7u) == 0) {
+    *reinterpret_cast<float2*>(o) = make_float2((float)v[0], (float)v[1]);
+  } else if (sizeof(T) == 4 && CC == 4 && (reinterpret_cast<uintptr_t>(out) & 15u) == 0) {
+    *reinterpret_cast<float4*>(o) = make_float4((float)v[0], (float)v[1], (float)v[CC > 2 ? 2 : 0], (float)v[CC > 3 ? 3 : 0]);
+  } else {
+#pragma unroll
+    for (int d = 0; d < CC; ++d) o[d] = v[d];
   }
 }
 

@@ -135,11 +135,13 @@ __device__ __forceinline__ void soft_backward_pair<float>(const float* p, const 
   const float dLdz = -sigmainv * dLdp * (1.0f - allprob) * __fdividef(prob, (1.0f - prob) + 1e-7f);
   if (dLdz == 0.0f) return;
   const float s = dLdz * __fdividef(1.0f, multiplier);
+  // a vertex's (x, y) gradient goes out as ONE 8-byte vector reduction (red.global.add.v2.f32: the (3,2) record of a
+  // face is 24 bytes, every vertex 8-byte aligned) — half the atomic requests of a kernel that ncu shows throttled on
+  // its load / store queue (lg_throttle)
   if (edgeid >= 3) {
     const int v = edgeid - 3;
     const float x1 = v == 0 ? p[0] : (v == 1 ? p[2] : p[4]), y1 = v == 0 ? p[1] : (v == 1 ? p[3] : p[5]);
-    atomicAdd(gi + 2 * v, s * 2 * (x1 - x0));
-    atomicAdd(gi + 2 * v + 1, s * 2 * (y1 - y0));
+    red_add2(gi + 2 * v, s * 2 * (x1 - x0), s * 2 * (y1 - y0));
   } else {
     const int e = edgeid, e2 = edgeid == 2 ? 0 : edgeid + 1;
     const float x1 = e == 0 ? p[0] : (e == 1 ? p[2] : p[4]), y1 = e == 0 ? p[1] : (e == 1 ? p[3] : p[5]);
@@ -151,10 +153,8 @@ __device__ __forceinline__ void soft_backward_pair<float>(const float* p, const 
     const float dzdA = 2 * (x0 * up - dissquare * A) * rden;
     const float dzdB = 2 * (y0 * up - dissquare * Bc) * rden;
     const float dzdC = 2 * up * rden;
-    atomicAdd(gi + 2 * e, s * (dzdB - y2 * dzdC));
-    atomicAdd(gi + 2 * e + 1, s * (x2 * dzdC - dzdA));
-    atomicAdd(gi + 2 * e2, s * (y1 * dzdC - dzdB));
-    atomicAdd(gi + 2 * e2 + 1, s * (dzdA - x1 * dzdC));
+    red_add2(gi + 2 * e, s * (dzdB - y2 * dzdC), s * (x2 * dzdC - dzdA));
+    red_add2(gi + 2 * e2, s * (y1 * dzdC - dzdB), s * (dzdA - x1 * dzdC));
   }
 }
 
