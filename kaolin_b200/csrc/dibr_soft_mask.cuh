@@ -384,6 +384,64 @@ __device__ __forceinline__ void chunk_rank_sort(int* s_ids, const int count) {
   __syncthreads();
 }
 
+// Sort of `count` unique ids in shared memory by distribution: 256 buckets over [min, max] of the ids (histogram with
+// shared-memory atomics, one warp scans it, the ids are scattered to their buckets in `s_tmp`), then every id is
+// ranked inside its bucket only.  A tile's candidates are a few runs of consecutive face ids, so a bucket holds a
+// handful to a few tens of them: ~100 instructions per id instead of the ~400 of chunk_rank_sort (which ranks every
+// id against every 32-chunk: 6 binary-search steps per chunk) at 256-512 candidates, and no bitonic network beyond
+// 4 * NT.  `s_tmp`: count words; `s_hist`: 256 words; `scratch`: 2 words.  Worst case (all ids in one bucket): the
+// all-pairs ranking of count^2 / NT compares per thread.
+#ifndef DIBR_SOFT_BUCKET_SORT
+#define DIBR_SOFT_BUCKET_SORT 64   // candidates per pass from which the distribution sort is used (0 = never)
+#endif
+template <int NT>
+__device__ __forceinline__ void bucket_sort(int* s_ids, int* s_tmp, int* s_hist, int* scratch, const int count) {
+  int mn = 0x7fffffff, mx = -1;
+  for (int k = threadIdx.x; k < count; k += NT) { const int v = s_ids[k]; mn = min(mn, v); mx = max(mx, v); }
+  mn = __reduce_min_sync(0xffffffffu, mn);
+  mx = __reduce_max_sync(0xffffffffu, mx);
+  for (int k = threadIdx.x; k < 256; k += NT) s_hist[k] = 0;
+  if (threadIdx.x == 0) { scratch[0] = 0x7fffffff; scratch[1] = -1; }
+  __syncthreads();
+  if ((threadIdx.x & 31) == 0) { atomicMin(&scratch[0], mn); atomicMax(&scratch[1], mx); }
+  __syncthreads();
+  mn = scratch[0]; mx = scratch[1];
+  int shift = 0;
+  while (((mx - mn) >> shift) > 255) ++shift;
+  for (int k = threadIdx.x; k < count; k += NT) atomicAdd(&s_hist[(s_ids[k] - mn) >> shift], 1);
+  __syncthreads();
+  if (threadIdx.x < 32) {                                 // warp 0: exclusive prefix of the 256 counts, in place
+    const int lane = threadIdx.x;
+    int c[8], sum = 0;
+#pragma unroll
+    for (int q = 0; q < 8; ++q) { c[q] = s_hist[lane * 8 + q]; sum += c[q]; }
+    int incl = sum;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+      const int v = __shfl_up_sync(0xffffffffu, incl, o);
+      if (lane >= o) incl += v;
+    }
+    int run = incl - sum;
+#pragma unroll
+    for (int q = 0; q < 8; ++q) { s_hist[lane * 8 + q] = run; run += c[q]; }
+  }
+  __syncthreads();
+  for (int k = threadIdx.x; k < count; k += NT) {         // scatter: the bucket's cursor ends at the bucket's end
+    const int v = s_ids[k];
+    s_tmp[atomicAdd(&s_hist[(v - mn) >> shift], 1)] = v;
+  }
+  __syncthreads();
+  for (int k = threadIdx.x; k < count; k += NT) {         // rank inside the bucket (ids are unique)
+    const int x = s_tmp[k];
+    const int b = (x - mn) >> shift;
+    const int s = b > 0 ? s_hist[b - 1] : 0, e = s_hist[b];
+    int r = 0;
+    for (int j = s; j < e; ++j) r += (s_tmp[j] < x) ? 1 : 0;
+    s_ids[s + r] = x;
+  }
+  __syncthreads();
+}
+
 // bits lo..hi (inclusive, 0 <= lo <= hi <= 15)
 __device__ __forceinline__ unsigned bit_span16(int lo, int hi) { return ((2u << hi) - 1u) & ~((1u << lo) - 1u); }
 
@@ -566,7 +624,10 @@ __device__ __forceinline__ void soft_tile(const SoftParams<T>& sp, const FaceLay
     if (count > 0) {
       // ---- sort by face index; order is semantic (first knum faces in face order)
       __syncthreads();
-      if (count <= 4 * NT) {
+      if (DIBR_SOFT_BUCKET_SORT > 0 && count > DIBR_SOFT_BUCKET_SORT) {
+        // (s_mask is free until the masks are built below, s_knew between super-batches)
+        bucket_sort<NT>(s_ids, reinterpret_cast<int*>(s_mask), s_knew, scratch, count);
+      } else if (count <= 4 * NT) {
         chunk_rank_sort<NT>(s_ids, count);
       } else {
         int n2 = 1;
