@@ -13,8 +13,12 @@
 namespace dibr {
 
 #ifndef DIBR_RASTER_BWD_CTAS
-#define DIBR_RASTER_BWD_CTAS 4     // resident 256-thread CTAs per SM the register allocation aims at (64 registers: 5 CTAs
-                                   // = 48 registers spilled 56 bytes per thread and measured 4 % slower at c2)
+#define DIBR_RASTER_BWD_CTAS 6     // resident 256-thread CTAs per SM the register allocation aims at.  The kernel waits
+                                   // on its dependent gathers (face_idx -> coordinates -> features; ncu: long-scoreboard),
+                                   // so occupancy beats registers — measured after the derivative terms moved behind the
+                                   // channel loop (c3-64 / c5 / c2): 4 CTAs, 64 registers, no spills 1.275 / 0.667 /
+                                   // 0.209 ms; 6 CTAs, 40 registers, 40 B of spills **1.093 / 0.588 / 0.209**; 8 CTAs, 32
+                                   // registers, 88 B 1.121 / 0.618 / 0.227
 #endif
 
 #ifndef DIBR_BWD_PREFETCH
@@ -122,12 +126,14 @@ __device__ __forceinline__ void raster_bwd_block(const T* __restrict__ g, const 
   }
 }
 
-// Everything after the per-pixel derivatives, for a warp whose largest group needs NS reduction steps.
+// Everything after the weights, for a warp whose largest group needs NS reduction steps: the feature gradients
+// (channel loop), then the coordinate gradient.  The derivative terms dw1 / dw2 (rasterization_cuda.cu:302-374) are
+// formed AFTER the channel loop from the face's coordinates, re-read from L1: held across the loop they pushed the
+// kernel into a local-memory frame (40 LDL / 10 STL in the round-1 SASS even at 64 registers).
 template <typename T, int NS>
 __device__ __forceinline__ void raster_bwd_tail(const RasterBwdParams<T>& bp, const int64_t pix, const int64_t tf,
                                                 const bool covered, const bool leader, const T w0, const T w1,
-                                                const T w2, const int* src, const T k3, const T* dw1,
-                                                const T* dw2) {
+                                                const T w2, const int* src) {
   T acc1 = 0, acc2 = 0;
   for (int ft = 0; ft < bp.feat.n; ++ft) {
     const int C = bp.feat.ch[ft];                      // warp-uniform
@@ -143,13 +149,36 @@ __device__ __forceinline__ void raster_bwd_tail(const RasterBwdParams<T>& bp, co
     }
     if (d < C) raster_bwd_block<T, NS, 1>(g + d, ff + d, gf + d, C, covered, leader, w0, w1, w2, src, acc1, acc2);
   }
-  const T inv_k3sq = (T)1 / (k3 * k3);               // one reciprocal instead of a division per channel (:389;
+  T dw1[6], dw2[6];
+#pragma unroll
+  for (int k = 0; k < 6; ++k) { dw1[k] = 0; dw2[k] = 0; }
+  if (covered) {
+    const T* ps = bp.img + tf * 6;
+    const T ax = ps[0], ay = ps[1], bx = ps[2], by = ps[3], cx = ps[4], cy = ps[5];
+    // rasterization_cuda.cu:302-374
+    const T x0r = w0 * ax + w1 * bx + w2 * cx;
+    const T y0r = w0 * ay + w1 * by + w2 * cy;
+    const T m = bx - ax, p = by - ay, n = cx - ax, q = cy - ay, s = x0r - ax, t = y0r - ay;
+    const T k1 = s * q - n * t;
+    const T k2 = m * t - s * p;
+    T k3 = m * q - n * p;
+    k3 = RN<T>::add_eps(k3, bp.eps);
+    const T inv_k3sq = (T)1 / (k3 * k3);             // one reciprocal instead of a division per channel (:389;
                                                      // gradients are judged at 1e-4 relative)
-  acc1 *= inv_k3sq; acc2 *= inv_k3sq;
+    acc1 *= inv_k3sq; acc2 *= inv_k3sq;
+    const T dw1dm = -q * k1, dw1dn = -t * k3 + p * k1, dw1dp = n * k1, dw1dq = s * k3 - m * k1;
+    const T dw1ds = q * k3, dw1dt = -n * k3;
+    const T dw2dm = t * k3 - q * k2, dw2dn = p * k2, dw2dp = -s * k3 + n * k2, dw2dq = -m * k2;
+    const T dw2ds = -p * k3, dw2dt = m * k3;
+    dw1[0] = -(dw1dm + dw1dn + dw1ds); dw1[1] = -(dw1dp + dw1dq + dw1dt);
+    dw1[2] = dw1dm; dw1[3] = dw1dp; dw1[4] = dw1dn; dw1[5] = dw1dq;
+    dw2[0] = -(dw2dm + dw2dn + dw2ds); dw2[1] = -(dw2dp + dw2dq + dw2dt);
+    dw2[2] = dw2dm; dw2[3] = dw2dp; dw2[4] = dw2dn; dw2[5] = dw2dq;
+  }
   T* gi = bp.grad_img + tf * 6;
 #pragma unroll
   for (int k = 0; k < 6; k += 2) {
-    const T g0 = covered ? acc1 * dw1[k] + acc2 * dw2[k] : (T)0;   // dw1 / dw2 are only defined on covered lanes
+    const T g0 = covered ? acc1 * dw1[k] + acc2 * dw2[k] : (T)0;
     const T g1 = covered ? acc1 * dw1[k + 1] + acc2 * dw2[k + 1] : (T)0;
     const T s0 = group_sum_n<T, NS>(g0, src);
     const T s1 = group_sum_n<T, NS>(g1, src);
@@ -208,44 +237,27 @@ __device__ __forceinline__ void raster_bwd_tile(const RasterBwdParams<T>& bp, co
 
   T w0 = 0, w1 = 0, w2 = 0;
   const int64_t tf = (int64_t)b * bp.F + (covered ? f : 0);
-  T k3 = 1, dw1[6], dw2[6];
   if (covered) {
-    const T* ps = bp.img + tf * 6;
-    const T ax = ps[0], ay = ps[1], bx = ps[2], by = ps[3], cx = ps[4], cy = ps[5];
     if (bp.weights) {
       const T* w = bp.weights + pix * 3;
       w0 = w[0]; w1 = w[1]; w2 = w[2];
     } else {
       typedef RN<T> R;
+      const T* ps = bp.img + tf * 6;
+      const T ax = ps[0], ay = ps[1], bx = ps[2], by = ps[3], cx = ps[4], cy = ps[5];
       const T x0 = (T)pix_coord(bp.sx, geo.W, px);
       const T y0 = (T)pix_coord(bp.sy, geo.H, geo.H - 1 - py);
       bary_weights<T>(R::mul(ax, bp.coord_mult), R::mul(ay, bp.coord_mult), R::mul(bx, bp.coord_mult),
                       R::mul(by, bp.coord_mult), R::mul(cx, bp.coord_mult), R::mul(cy, bp.coord_mult),
                       x0, y0, bp.eps, w0, w1, w2);
     }
-    // rasterization_cuda.cu:302-374
-    const T x0r = w0 * ax + w1 * bx + w2 * cx;
-    const T y0r = w0 * ay + w1 * by + w2 * cy;
-    const T m = bx - ax, p = by - ay, n = cx - ax, q = cy - ay, s = x0r - ax, t = y0r - ay;
-    const T k1 = s * q - n * t;
-    const T k2 = m * t - s * p;
-    k3 = m * q - n * p;
-    k3 = RN<T>::add_eps(k3, bp.eps);
-    const T dw1dm = -q * k1, dw1dn = -t * k3 + p * k1, dw1dp = n * k1, dw1dq = s * k3 - m * k1;
-    const T dw1ds = q * k3, dw1dt = -n * k3;
-    const T dw2dm = t * k3 - q * k2, dw2dn = p * k2, dw2dp = -s * k3 + n * k2, dw2dq = -m * k2;
-    const T dw2ds = -p * k3, dw2dt = m * k3;
-    dw1[0] = -(dw1dm + dw1dn + dw1ds); dw1[1] = -(dw1dp + dw1dq + dw1dt);
-    dw1[2] = dw1dm; dw1[3] = dw1dp; dw1[4] = dw1dn; dw1[5] = dw1dq;
-    dw2[0] = -(dw2dm + dw2dn + dw2ds); dw2[1] = -(dw2dp + dw2dq + dw2dt);
-    dw2[2] = dw2dm; dw2[3] = dw2dp; dw2[4] = dw2dn; dw2[5] = dw2dq;
   }
   // the reduction depth of the warp's largest group, dispatched once: no per-step branches in the channel loops
   const int ns = 32 - __clz(steps);
-  if (DIBR_BWD_MAXSTEPS <= 2 || ns <= 2) raster_bwd_tail<T, (DIBR_BWD_MAXSTEPS < 2 ? DIBR_BWD_MAXSTEPS : 2)>(bp, pix, tf, covered, leader, w0, w1, w2, src, k3, dw1, dw2);
-  else if (ns <= 3) raster_bwd_tail<T, 3>(bp, pix, tf, covered, leader, w0, w1, w2, src, k3, dw1, dw2);
-  else if (ns == 4) raster_bwd_tail<T, 4>(bp, pix, tf, covered, leader, w0, w1, w2, src, k3, dw1, dw2);
-  else raster_bwd_tail<T, 5>(bp, pix, tf, covered, leader, w0, w1, w2, src, k3, dw1, dw2);
+  if (DIBR_BWD_MAXSTEPS <= 2 || ns <= 2) raster_bwd_tail<T, (DIBR_BWD_MAXSTEPS < 2 ? DIBR_BWD_MAXSTEPS : 2)>(bp, pix, tf, covered, leader, w0, w1, w2, src);
+  else if (ns <= 3) raster_bwd_tail<T, 3>(bp, pix, tf, covered, leader, w0, w1, w2, src);
+  else if (ns == 4) raster_bwd_tail<T, 4>(bp, pix, tf, covered, leader, w0, w1, w2, src);
+  else raster_bwd_tail<T, 5>(bp, pix, tf, covered, leader, w0, w1, w2, src);
 }
 
 }  // namespace dibr

@@ -14,6 +14,7 @@ import os
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 LIB = os.path.join(ROOT, "kaolin_b200", "libdibr_b200.so")
 HOT = ["setup_count_kernelIf", "scan_kernel", "fill_kernel", "raster_fwd_scatter_kernel", "raster_bwd_kernelIf",
+       "soft_mask_bwd_log_kernelIf", "prepare_vertices_bwd_kernelIf",
        "soft_mask_kernelIfLi0", "soft_mask_kernelIfLi1"]
 
 
