@@ -896,8 +896,11 @@ __device__ __forceinline__ void log_fetch_face(const SoftParams<T>& sp, const Fa
 #ifndef DIBR_LOG_INFLIGHT
 #define DIBR_LOG_INFLIGHT 2       // logged pairs whose gathers are in flight together, per thread
 #endif
+#ifndef DIBR_LOG_CTAS
+#define DIBR_LOG_CTAS 6           // resident 256-thread CTAs per SM the log backward's register allocation aims at
+#endif
 template <typename T>
-__global__ void __launch_bounds__(256) soft_mask_bwd_log_kernel(SoftParams<T> sp, FaceLayout fl, Geometry geo) {
+__global__ void __launch_bounds__(256, (sizeof(T) == 4 ? DIBR_LOG_CTAS : 2)) soft_mask_bwd_log_kernel(SoftParams<T> sp, FaceLayout fl, Geometry geo) {
   const unsigned seg = blockIdx.y;
   const unsigned n = min(sp.log_count[seg], sp.log_cap);
   const unsigned hw = (unsigned)geo.H * (unsigned)geo.W;
