@@ -355,9 +355,11 @@ __device__ __forceinline__ void scatter_faces(const RasterFwdParams<float>& rp, 
         ms = copysignf(fmaf(dd, 1.9073486328125e-6f /* 2^-19 */, 3.637978807091713e-12f), nc);
         const float sp = copysignf(sh.pitch, nc);                    // s * pitch
         const float a0 = (p[3] - p[5]) * sp, a1 = (p[5] - p[1]) * sp, a2 = (p[1] - p[3]) * sp;
-        rn0 = a0 != 0.0f ? -1.0f / a0 : 0.0f;
-        rn1 = a1 != 0.0f ? -1.0f / a1 : 0.0f;
-        rn2 = a2 != 0.0f ? -1.0f / a2 : 0.0f;
+        // approximate reciprocals (<= 2 ulp): the bounds they scale are clamped to [-2, 32] columns and carry a
+        // 1/64-pixel margin, 2.4e-7 relative is 8e-6 of a column at most (three IEEE divisions per staged face before)
+        rn0 = a0 != 0.0f ? __fdividef(-1.0f, a0) : 0.0f;
+        rn1 = a1 != 0.0f ? __fdividef(-1.0f, a1) : 0.0f;
+        rn2 = a2 != 0.0f ? __fdividef(-1.0f, a2) : 0.0f;
       }
     }
   }
