@@ -380,6 +380,22 @@ int dibr_texture_mapping_bwd_f64(const double* grad_out, const double* uv, const
                                  double* grad_uv, double* grad_texture_maps, double* grad_mask, void* stream);
 
 /* ---------------------------------------------------------------------------------------------
+ * Adam step of the fitting loop — torch.optim.Adam(params, lr, betas, eps) without weight decay / amsgrad
+ * (examples/tutorial/ian_dibr.py:116-123, `vertices_optim.step()` at :287) for ONE parameter tensor of n elements,
+ * one thread per element (torch hands a tensor to one CTA per 65 536 elements: a 20 k-vertex mesh is a single CTA).
+ * In place on param / exp_avg / exp_avg_sq.  `step` (1 float) is the DEVICE step counter, read and then incremented
+ * by the kernel (graph-capturable: nothing on the host changes between steps); `arrivals` (1 unsigned) is scratch that
+ * the caller zero-initialises once.  Same update as torch: m = b1 m + (1 - b1) g; v = b2 v + (1 - b2) g^2;
+ * param -= lr / (1 - b1^t) * m / (sqrt(v) / sqrt(1 - b2^t) + eps), t = step + 1, arithmetic in double.
+ */
+int dibr_adam_step_f32(float* param, const float* grad, float* exp_avg, float* exp_avg_sq, float* step,
+                       unsigned* arrivals, int64_t n, double lr, double beta1, double beta2, double eps,
+                       void* stream);
+int dibr_adam_step_f64(double* param, const double* grad, double* exp_avg, double* exp_avg_sq, float* step,
+                       unsigned* arrivals, int64_t n, double lr, double beta1, double beta2, double eps,
+                       void* stream);
+
+/* ---------------------------------------------------------------------------------------------
  * Image L1 loss of the fitting loop — examples/tutorial/ian_dibr.py:260  image_loss = torch.mean(torch.abs(image -
  * gt_image)): loss (device scalar) = mean over the n elements of |a - b|, as a deterministic two-stage reduction (no
  * float atomics); ws: dibr_image_l1_workspace_bytes(n, elem_size) bytes.  _bwd: grad_loss is a DEVICE scalar;

@@ -55,6 +55,7 @@ _TYPED = {
                                   c_p, c_p],
     "dibr_texture_mapping_fwd": [c_p, c_p, c_p, c_i, c_i64, c_i, c_i, c_i, c_i, c_i, c_p, c_p],
     "dibr_texture_mapping_bwd": [c_p, c_p, c_p, c_p, c_i, c_i64, c_i, c_i, c_i, c_i, c_i, c_p, c_p, c_p, c_p],
+    "dibr_adam_step": [c_p, c_p, c_p, c_p, c_p, c_p, c_i64, c_d, c_d, c_d, c_d, c_p],
     "dibr_image_l1_fwd": [c_p, c_p, c_i64, c_p, c_p, c_sz, c_p],
     "dibr_image_l1_bwd": [c_p, c_p, c_p, c_i64, c_p, c_p, c_p],
     "dibr_mask_iou_fwd": [c_p, c_p, c_i, c_i64, c_p, c_p, c_p, c_sz, c_p],

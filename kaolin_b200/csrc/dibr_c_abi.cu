@@ -773,6 +773,22 @@ int l1_bwd_impl(const T* g_loss, const T* a, const T* b, int64_t n, T* g_a, T* g
   return DIBR_OK;
 }
 
+// Adam step for one parameter tensor (the fitting loop's optimiser; see dibr_losses.cuh).  state: step (1 float) and
+// arrivals (1 unsigned, zero-initialised by the caller once) live on the device.
+template <typename T>
+int adam_impl(T* param, const T* grad, T* exp_avg, T* exp_avg_sq, float* step, unsigned* arrivals, int64_t n, double lr,
+              double beta1, double beta2, double eps, void* stream) {
+  if (n < 0) return DIBR_ERR_INVALID_ARGUMENT;
+  if (n >= (int64_t)1 << 38) return DIBR_ERR_TOO_LARGE;
+  if (!step || !arrivals || (n > 0 && (!param || !grad || !exp_avg || !exp_avg_sq))) return DIBR_ERR_INVALID_ARGUMENT;
+  cudaStream_t s = static_cast<cudaStream_t>(stream);
+  const unsigned nb = (unsigned)((n + 255) / 256);
+  adam_step_kernel<T><<<nb > 0 ? nb : 1, 256, 0, s>>>(param, grad, exp_avg, exp_avg_sq, step, arrivals, n, lr, beta1,
+                                                      beta2, eps);
+  LAUNCH_CHECK("adam_step_kernel");
+  return DIBR_OK;
+}
+
 // ---- allocation-free variant of mask_iou forward (no counterpart in the reference; added
 // for callers that cannot allocate: code under CUDA graph capture, tight serving loops, harnesses that
 // forbid cudaMalloc).  Its scratch — the per-chunk partial sums of the two-stage reduction — lives in this file-scope
@@ -1150,6 +1166,12 @@ DIBR_API size_t dibr_noalloc_scratch_bytes(void) { return NOALLOC_SCRATCH_BYTES;
                                               T* grad_mask, void* stream) {                                  \
     return texture_impl<T>(true, grad_out, uv, texture_maps, mask, B, N, Bt, C, Ht, Wt, mode, nullptr,       \
                            grad_uv, grad_texture_maps, grad_mask, stream);                                    \
+  }                                                                                                           \
+  DIBR_API int dibr_adam_step_##SUF(T* param, const T* grad, T* exp_avg, T* exp_avg_sq, float* step,           \
+                                    unsigned* arrivals, int64_t n, double lr, double beta1, double beta2,      \
+                                    double eps,                                                                \
+                                    void* stream) {                                                            \
+    return adam_impl<T>(param, grad, exp_avg, exp_avg_sq, step, arrivals, n, lr, beta1, beta2, eps, stream);   \
   }                                                                                                           \
   DIBR_API int dibr_image_l1_fwd_##SUF(const T* a, const T* b, int64_t n, T* loss, void* ws, size_t ws_bytes, \
                                        void* stream) {                                                       \

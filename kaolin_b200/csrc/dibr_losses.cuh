@@ -131,4 +131,37 @@ __global__ void __launch_bounds__(256) image_l1_bwd_kernel(const T* __restrict__
   }
 }
 
+// ---------------------------------------------------------------- Adam step of the fitting loop
+// torch.optim.Adam (no weight decay, no amsgrad; examples/tutorial/ian_dibr.py:116-123 `vertices_optim`) for ONE
+// parameter tensor, thread = element.  torch's fused / foreach implementations hand a tensor to `multi_tensor_apply`
+// in chunks of 65 536 elements per CTA: the 60 k coordinates of a 20 k-vertex mesh are one CTA, 49 us of a 600 us
+// step (profiles/r02_c4_b16_launches.csv).  `step` is a DEVICE counter (float, as torch's capturable Adam keeps it),
+// incremented by the kernel's first thread after every thread has read it — no host value changes between replays
+// of a captured step.
+template <typename T>
+__global__ void __launch_bounds__(256) adam_step_kernel(T* __restrict__ param, const T* __restrict__ grad,
+                                                        T* __restrict__ exp_avg, T* __restrict__ exp_avg_sq,
+                                                        float* step, unsigned* arrivals, const int64_t n,
+                                                        const double lr, const double b1, const double b2,
+                                                        const double eps) {
+  const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  const float t = step[0] + 1.0f;
+  if (i < n) {
+    const double g = (double)grad[i];
+    const double m = b1 * (double)exp_avg[i] + (1.0 - b1) * g;
+    const double v = b2 * (double)exp_avg_sq[i] + (1.0 - b2) * g * g;
+    exp_avg[i] = (T)m;
+    exp_avg_sq[i] = (T)v;
+    const double bias1 = 1.0 - pow(b1, (double)t), bias2 = 1.0 - pow(b2, (double)t);
+    const double denom = sqrt(v) / sqrt(bias2) + eps;
+    param[i] = (T)((double)param[i] - (lr / bias1) * (m / denom));
+  }
+  // the last CTA to finish advances the counter (every CTA has read it by then)
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    __threadfence();
+    if (atomicAdd(arrivals, 1u) == gridDim.x - 1) { step[0] = t; arrivals[0] = 0u; }
+  }
+}
+
 }  // namespace dibr

@@ -67,7 +67,7 @@ def test_captured_step_equals_eager_steps():
     # capture() ran warm-up steps: restart both from the same state (vertices and Adam moments)
     with torch.no_grad():
         graphed.vertices.copy_(v0)
-    for st in graphed.opt.state.values():
+    for st in graphed.opt.state.values():          # exp_avg, exp_avg_sq, step, arrivals: all start from zero
         for k, t in st.items():
             if torch.is_tensor(t):
                 t.zero_()
@@ -99,3 +99,22 @@ def test_step_loss_matches_unfused_composition():
     ref.backward()
     assert abs(float(ref) - float(loss)) <= 1e-6 * max(1.0, abs(float(ref)))
     norm_close(g_fused, leaf.grad, 1e-4, "vertices.grad")
+
+
+@pytest.mark.parametrize("dname", ["f32", "f64"])
+def test_per_element_adam_matches_torch(dname):
+    from kaolin_b200.multiview import PerElementAdam
+    dtype = torch.float32 if dname == "f32" else torch.float64
+    g = torch.Generator().manual_seed(9)
+    p0 = torch.rand(1, 7001, 3, generator=g, dtype=torch.float64).to(dtype).cuda()
+    a, b = p0.clone().requires_grad_(True), p0.clone().requires_grad_(True)
+    oa = torch.optim.Adam([a], lr=3e-3, betas=(0.9, 0.99), eps=1e-8)
+    ob = PerElementAdam([b], lr=3e-3, betas=(0.9, 0.99), eps=1e-8)
+    for it in range(6):
+        grad = (torch.rand(p0.shape, generator=g, dtype=torch.float64) - 0.5).to(dtype).cuda() * (10.0 ** (it - 3))
+        a.grad, b.grad = grad.clone(), grad.clone()
+        oa.step()
+        ob.step()
+        tol = 2e-6 if dname == "f32" else 1e-12
+        assert torch.allclose(b, a, rtol=tol, atol=tol), (it, float((a - b).abs().max()))
+    assert float(ob.state[b]["step"]) == 6.0
