@@ -56,7 +56,7 @@
 extern "C" {
 #endif
 
-#define DIBR_ABI_VERSION 7
+#define DIBR_ABI_VERSION 8
 
 enum {
   DIBR_OK = 0,

@@ -135,7 +135,7 @@ def load():
                 fn = getattr(lib, f"{name}_{suf}")
                 fn.restype = c_i
                 fn.argtypes = argtypes
-        if lib.dibr_abi_version() != 7:
+        if lib.dibr_abi_version() != 8:
             raise RuntimeError("kaolin_b200: libdibr_b200.so ABI version mismatch")
         _lib = lib
     return _lib

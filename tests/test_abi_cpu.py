@@ -37,7 +37,7 @@ def test_header_symbols_exported(lib):
 
 
 def test_host_only_entry_points(lib):
-    assert lib.dibr_abi_version() == 7
+    assert lib.dibr_abi_version() == 8
     assert lib.dibr_error_string(0) == b"ok"
     for code in (1, 2, 3, 4, 5, 99):
         assert len(lib.dibr_error_string(code)) > 0
