@@ -249,13 +249,20 @@ int rasterize_bwd_impl(const T* const* grad_outs, const int64_t* face_idx, const
   return DIBR_OK;
 }
 
-inline int soft_threads_default() {
-  static const int nt = [] {
+// Threads per tile CTA of the fp32 soft-mask kernels: 128 (more independent tiles per SM hide the barrier-separated
+// phases), except for DENSE scenes — many faces per tile, i.e. silhouette tiles with thousands of candidates — where
+// 256 threads (2048 candidates per pass instead of 1024, twice the lanes per heavy tile) win by far: measured on B200,
+// soft forward with 128 / 256 threads: c5 (61 faces per tile) 2.39 / 1.11 ms, c3 (24) 1.64 / 2.08 ms.
+// DIBR_SOFT_NT (with DIBR_B200_TUNING=1) overrides the choice.
+constexpr int SOFT_DENSE_FACES_PER_TILE = 48;
+inline int soft_threads_default(int64_t faces_per_view, int tiles_per_view) {
+  static const int forced = [] {
     const char* e = tuning_env("DIBR_SOFT_NT");
     const int v = e ? atoi(e) : 0;
-    return (v == 64 || v == 128 || v == 256) ? v : 128;
+    return (v == 64 || v == 128 || v == 256) ? v : 0;
   }();
-  return nt;
+  if (forced) return forced;
+  return faces_per_view >= (int64_t)SOFT_DENSE_FACES_PER_TILE * tiles_per_view ? 256 : 128;
 }
 
 template <typename T, int MODE, int NT>
@@ -375,7 +382,7 @@ int soft_launch_on_lists(SoftParams<T> p, const FaceLayout& fl, const Geometry& 
   const int kid = MODE == MODE_FWD ? DIBR_KERNEL_SOFT_FWD : DIBR_KERNEL_SOFT_BWD;
   // threads per CTA (one CTA per tile either way): fp32 uses small CTAs (more resident tiles per SM hide the
   // barrier-separated phases); DIBR_SOFT_NT=64|128|256 overrides for experiments.  fp64: 256.
-  int nt = sizeof(T) == 4 ? soft_threads_default() : 256;
+  int nt = sizeof(T) == 4 ? soft_threads_default(geo.B > 0 ? fl.Ntot / geo.B : 0, geo.tiles_per_view) : 256;
   if (MODE == MODE_BWD && use_log) {
     if (sizeof(T) == 4) { if (int e = launch_soft_overflow<T, 128>(p, fl, geo, L, grid, s)) return e; }
     else { if (int e = launch_soft_overflow<T, 256>(p, fl, geo, L, grid, s)) return e; }
