@@ -41,7 +41,8 @@
  * test_kernel_variants_give_identical_results).  They are read from the environment ONCE per process and ONLY
  * when DIBR_B200_TUNING=1 is set — without that single switch the library never looks at its environment:
  *     DIBR_RASTER_NT    = 64 | 128 | 256   threads per 16x16 tile of the rasterizer forward kernel (default 64)
- *     DIBR_SOFT_NT      = 64 | 128 | 256   threads per tile of the soft-mask kernels (default 128)
+ *     DIBR_SOFT_NT      = 64 | 128 | 256   threads per tile of the soft-mask kernels (default 128; 256 for dense
+ *                                          scenes: >= 48 faces per 16x16 tile)
  *     DIBR_SOFT_SEL     = n                candidates taken by the first selection pass of a soft-mask tile
  *     DIBR_SOFT_LOG_CAP = n                entries of the soft-mask pair log (default 2 per pixel + 65536); a small
  *                                          value forces the overflow (recompute) path — used by the tests

@@ -4,9 +4,9 @@
 // One CTA = one 16x16 tile.  Only tiles with at least one uncovered pixel do any work beyond the
 // face_idx read / soft write.  The reference keeps the FIRST `knum` faces in face order whose enlarged bbox
 // contains the pixel (:80-171), so order is semantic: the tile's candidate faces (enlarged-bbox tile list +
-// filtered coarse / "large" faces) are taken in passes of increasing face-index ranges — a pass holds the ~2*NT
-// lowest remaining ids, chosen by one histogram sweep (select_hi) — gathered into shared memory, sorted by face
-// index (chunk_rank_sort) and turned into coverage masks of the tile's columns and rows, stored transposed per
+// filtered coarse / "large" faces) are taken in passes of increasing face-index ranges — a pass holds the lowest
+// remaining ids that fit the shared-memory arrays (1024 / 2048), chosen by one histogram sweep (select_hi) — gathered
+// into shared memory, sorted by face index (bucket_sort / chunk_rank_sort) and turned into coverage masks of the tile's columns and rows, stored transposed per
 // chunk of 32 candidates (one word per column / row = the chunk's candidates covering it).
 //
 // Per pass: (A, once) compact the uncovered pixels (from the rasterizer's coverage map when it left one); (B) every
@@ -561,7 +561,9 @@ __device__ __forceinline__ void soft_tile(const SoftParams<T>& sp, const FaceLay
   // (config 5) take the selection path below.
   int lo = -1;
   bool first = true;
-  int target = sp.sel_first > 0 ? min(sp.sel_first, CAP) : min(2 * NT, CAP);
+  // (with the distribution sort a pass costs little per candidate: the first pass takes as many as fit — measured
+  //  at c3-64 with 256 / 512 / 1024 first: 1.644 / 1.585 / 1.580 ms; 128: 1.887)
+  int target = sp.sel_first > 0 ? min(sp.sel_first, CAP) : CAP;
   while (true) {
     // ---- gather the candidates with lo < id <= hi: tile list + filtered large faces.  A pass takes about `target`
     //      of the lowest remaining ids (the k-lists are the FIRST knum hits in face order, so a pixel is usually
