@@ -84,7 +84,10 @@ template <> __device__ __forceinline__ double log_prob<double>(const uint4& r) {
   return __longlong_as_double((long long)(((unsigned long long)r.w << 32) | r.z));
 }
 constexpr int LOG_SEGMENTS = 64;
-constexpr int LOG_CTAS_PER_SEGMENT = 32;
+#ifndef DIBR_LOG_CTAS_PER_SEGMENT
+#define DIBR_LOG_CTAS_PER_SEGMENT 64   // measured 16 / 32 / 64 / 128 at c3-64: 0.564 / 0.478 / 0.447 / 0.443 ms (c3-8: 0.083 / 0.073 / 0.071 / 0.075)
+#endif
+constexpr int LOG_CTAS_PER_SEGMENT = DIBR_LOG_CTAS_PER_SEGMENT;
 
 // dibr_soft_mask_cuda.cu:283-347 for one (pixel, face) pair; p = multiplied coordinates.
 // Gradients need 1e-4 relative, not bit-exactness (the reference accumulates them with unordered atomics): the
