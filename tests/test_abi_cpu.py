@@ -122,3 +122,30 @@ def test_product_never_imports_the_oracle():
             if f.endswith((".py", ".cu", ".cuh", ".h")):
                 text = open(os.path.join(dirpath, f)).read()
                 assert "import oracle" not in text and "from oracle" not in text and "oracle/" not in text, f
+
+
+def test_round2_entry_points_fail_loudly_without_gpu():
+    """The additions of round 2 (from-mesh entry, image L1, per-element Adam) have no CPU path either."""
+    import kaolin_b200 as kal
+    from kaolin_b200.metrics.render import image_l1
+    from kaolin_b200.multiview import PerElementAdam
+    v = torch.rand(1, 12, 3)
+    f = torch.tensor([[0, 1, 2], [2, 3, 4]], dtype=torch.long)
+    feats = torch.rand(2, 2, 3, 3)
+    proj = torch.tensor([2.4, 2.4, -1.0])
+    rot = torch.eye(3).repeat(2, 1, 1)
+    trans = torch.zeros(2, 3)
+    with pytest.raises(RuntimeError, match="CUDA"):
+        kal.render.mesh.dibr_rasterization_from_mesh(8, 8, v, f, feats, proj, rot, trans)
+    with pytest.raises(AssertionError):                       # prepare_vertices' own assertion (utils.py:160-166)
+        kal.render.mesh.dibr_rasterization_from_mesh(8, 8, v, f, feats, proj)
+    with pytest.raises(RuntimeError, match="CUDA"):
+        image_l1(torch.zeros(2, 4, 4, 3), torch.zeros(2, 4, 4, 3))
+    p = torch.zeros(4, requires_grad=True)
+    p.grad = torch.ones(4)
+    with pytest.raises(RuntimeError, match="CUDA"):
+        PerElementAdam([p]).step()
+    # the reference's module surface is unchanged; the additions are exported next to it
+    from kaolin_b200.render.mesh import dibr
+    assert dibr.__all__ == ["dibr_soft_mask", "dibr_rasterization"]
+    assert callable(kal.render.mesh.dibr_rasterization_from_mesh)
