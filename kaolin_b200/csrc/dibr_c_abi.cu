@@ -617,8 +617,16 @@ int prepare_impl(bool backward, const T* g_cam, const T* g_img, const T* g_nrm, 
   if (backward) {
     if (!g_cam && !g_img && !g_nrm) return DIBR_OK;                 // all-zero upstream: the memset is the answer
     { ProfScope ps(DIBR_KERNEL_PREPARE_BWD, s);
-      if (cam_grad) prepare_vertices_bwd_kernel<T, true><<<nb, 256, 0, s>>>(pp);
-      else prepare_vertices_bwd_kernel<T, false><<<nb, 256, 0, s>>>(pp); }
+      if (cam_grad) {
+        prepare_vertices_bwd_kernel<T, true><<<nb, 256, 0, s>>>(pp);
+      } else if (Bv == 1 && B >= 4 && g_vertices && F > 0) {
+        // one mesh, many cameras: the face's gradient summed over a chunk of views before it is scattered
+        const int vpt = B <= 32 ? 4 : 8;
+        prepare_vertices_bwd_shared_kernel<T><<<dim3((unsigned)((F + 255) / 256), (unsigned)((B + vpt - 1) / vpt)), 256, 0,
+                                                s>>>(pp, vpt);
+      } else {
+        prepare_vertices_bwd_kernel<T, false><<<nb, 256, 0, s>>>(pp);
+      } }
     LAUNCH_CHECK("prepare_vertices_bwd_kernel");
   } else {
     { ProfScope ps(DIBR_KERNEL_PREPARE_FWD, s); prepare_vertices_fwd_kernel<T><<<nb, 256, 0, s>>>(pp); }
